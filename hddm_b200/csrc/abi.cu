@@ -1,0 +1,656 @@
+// abi.cu -- the extern "C" boundary declared in include/hddm_b200.h.
+//
+// Host side of the drop-in: argument checks that the reference performs in Python/Cython
+// (ValueError / AssertionError conditions become status codes), staging of host buffers into a
+// grow-only device arena, kernel launches on one library stream, and the blocking copy-back the
+// reference's synchronous API implies.  No CPU evaluation path exists here: if CUDA is not
+// usable every entry point returns HDDM_ERR_CUDA.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "../../include/hddm_b200.h"
+#include "kernels.cuh"
+
+using namespace hddm;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* msg)
+{
+    snprintf(g_err, sizeof(g_err), "%s", msg);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                    \
+    do {                                                                                  \
+        cudaError_t e__ = (expr);                                                         \
+        if (e__ != cudaSuccess) {                                                         \
+            snprintf(g_err, sizeof(g_err), "CUDA error %s at %s:%d (%s)",                 \
+                     cudaGetErrorName(e__), __FILE__, __LINE__, cudaGetErrorString(e__)); \
+            return HDDM_ERR_CUDA;                                                         \
+        }                                                                                 \
+    } while (0)
+
+#define TRY(expr)                 \
+    do {                          \
+        int rc__ = (expr);        \
+        if (rc__) return rc__;    \
+    } while (0)
+
+struct Runtime {
+    std::mutex mu;
+    bool ready = false;
+    cudaStream_t stream = nullptr;
+    char* arena = nullptr;  // grow-only device scratch, carved per call
+    size_t arena_bytes = 0;
+};
+Runtime g_rt;
+
+int ensure_ready()
+{
+    if (g_rt.ready) return HDDM_OK;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        snprintf(g_err, sizeof(g_err), "no usable CUDA device (%s); hddm_b200 has no CPU fallback",
+                 e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return HDDM_ERR_CUDA;
+    }
+    CUDA_TRY(cudaStreamCreateWithFlags(&g_rt.stream, cudaStreamNonBlocking));
+    g_rt.ready = true;
+    return HDDM_OK;
+}
+
+int ensure_arena(size_t bytes)
+{
+    if (bytes <= g_rt.arena_bytes) return HDDM_OK;
+    if (g_rt.arena) {
+        CUDA_TRY(cudaStreamSynchronize(g_rt.stream));
+        CUDA_TRY(cudaFree(g_rt.arena));
+        g_rt.arena = nullptr;
+        g_rt.arena_bytes = 0;
+    }
+    const size_t want = bytes + bytes / 4 + (1 << 20);
+    CUDA_TRY(cudaMalloc(&g_rt.arena, want));
+    g_rt.arena_bytes = want;
+    return HDDM_OK;
+}
+
+size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
+
+// Two-phase arena layout: reserve() everything, ensure_arena(total), then at().
+struct Layout {
+    size_t total = 0;
+    size_t reserve(size_t bytes)
+    {
+        const size_t off = total;
+        total += align_up(bytes ? bytes : 1);
+        return off;
+    }
+    template <class T>
+    static T* at(size_t off) { return reinterpret_cast<T*>(g_rt.arena + off); }
+};
+
+int check_numerics(int n_st, int n_sz, int use_adaptive)
+{
+    if (use_adaptive && (n_st > HDDM_MAX_DEPTH || n_sz > HDDM_MAX_DEPTH))
+        return fail(HDDM_ERR_ARG, "adaptive recursion depth n_st/n_sz > 24 is not supported");
+    return HDDM_OK;
+}
+
+Numerics make_numerics(double err, int n_st, int n_sz, int use_adaptive, double simps_err)
+{
+    Numerics nm;
+    nm.err = err;
+    nm.simps_err = simps_err;
+    nm.n_st = n_st;
+    nm.n_sz = n_sz;
+    nm.use_adaptive = use_adaptive;
+    return nm;
+}
+
+int64_t chunks_for(int64_t max_len)
+{
+    const int64_t c = (max_len + kTrialsPerBlock - 1) / kTrialsPerBlock;
+    return c < 1 ? 1 : c;
+}
+
+bool out_of_support(double sv, double a, double z, double sz, double t, double st, double p_outlier)
+{  // src/wfpt.pyx:395-396 == src/cdfdif_wrapper.pyx:23-24
+    return (sv < 0) || (a <= 0) || (z < 0) || (z > 1) || (sz < 0) || (sz > 1) || (z + sz / 2. > 1) ||
+           (z - sz / 2. < 0) || (t - st / 2. < 0) || (t < 0) || (st < 0) ||
+           !((p_outlier >= 0) & (p_outlier <= 1));
+}
+
+// Host buffers to stage, and how each of the 9 parameters is addressed inside them.
+struct Upload {
+    const void* host;
+    size_t bytes;
+};
+struct ParSpec {
+    int upload;      // index into the uploads
+    int64_t offset;  // in doubles
+    int64_t set_stride, trial_stride;
+};
+
+// Core of every "sum of log densities" entry point.  x is either a host buffer (h_x) staged
+// into the arena or already device-resident (d_x).
+int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_seg,
+              const int32_t* h_cont, const Upload* uploads, int n_uploads, const ParSpec spec[kNumPar],
+              int64_t P, int mode, const Numerics& nm, double* logp, unsigned long long* evals)
+{
+    if (n < 0 || P < 0 || (n > 0 && !h_x && !d_x) || (P > 0 && !logp))
+        return fail(HDDM_ERR_ARG, "likelihood: bad buffer or size");
+    TRY(check_numerics(nm.n_st, nm.n_sz, nm.use_adaptive));
+    TRY(ensure_ready());
+    if (P == 0) return HDDM_OK;
+
+    int64_t max_len = n;
+    if (h_seg) {
+        max_len = 0;
+        for (int64_t p = 0; p < P; ++p) {
+            const int64_t len = h_seg[p + 1] - h_seg[p];
+            if (len < 0 || h_seg[p] < 0 || h_seg[p + 1] > n)
+                return fail(HDDM_ERR_ARG, "batch: segment offsets must be ascending within [0, n]");
+            if (len > max_len) max_len = len;
+        }
+    }
+    const int64_t chunks = chunks_for(max_len);
+    if (chunks > 65535) return fail(HDDM_ERR_ARG, "more than 65535*2048 trials per parameter set");
+    if (P > 2147483647LL) return fail(HDDM_ERR_ARG, "more than 2^31-1 parameter sets per launch");
+
+    Layout L;
+    const size_t off_x = h_x ? L.reserve((size_t)n * sizeof(double)) : 0;
+    const size_t off_cont = h_cont ? L.reserve((size_t)n * sizeof(int32_t)) : 0;
+    const size_t off_seg = h_seg ? L.reserve((size_t)(P + 1) * sizeof(int64_t)) : 0;
+    size_t off_up[8];
+    for (int u = 0; u < n_uploads; ++u) off_up[u] = L.reserve(uploads[u].bytes);
+    const size_t off_partial = L.reserve((size_t)P * chunks * sizeof(double));
+    const size_t off_logp = L.reserve((size_t)P * sizeof(double));
+    const size_t off_evals = L.reserve(sizeof(unsigned long long));
+    TRY(ensure_arena(L.total));
+
+    cudaStream_t s = g_rt.stream;
+    if (h_x && n > 0)
+        CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_x), h_x, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+    if (h_cont && n > 0)
+        CUDA_TRY(cudaMemcpyAsync(L.at<int32_t>(off_cont), h_cont, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    if (h_seg)
+        CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_seg), h_seg, (size_t)(P + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    for (int u = 0; u < n_uploads; ++u)
+        if (uploads[u].bytes)
+            CUDA_TRY(cudaMemcpyAsync(L.at<char>(off_up[u]), uploads[u].host, uploads[u].bytes, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemsetAsync(L.at<char>(off_evals), 0, sizeof(unsigned long long), s));
+
+    LikeArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = h_x ? L.at<double>(off_x) : d_x;
+    a.seg = h_seg ? L.at<int64_t>(off_seg) : nullptr;
+    a.cont = h_cont ? L.at<int32_t>(off_cont) : nullptr;
+    for (int k = 0; k < kNumPar; ++k) {
+        a.par[k] = L.at<double>(off_up[spec[k].upload]) + spec[k].offset;
+        a.set_stride[k] = spec[k].set_stride;
+        a.trial_stride[k] = spec[k].trial_stride;
+    }
+    a.n = n;
+    a.n_sets = P;
+    a.chunks = (int)chunks;
+    a.mode = mode;
+    a.nm = nm;
+    a.partial = L.at<double>(off_partial);
+    a.logp = L.at<double>(off_logp);
+    a.evals = L.at<unsigned long long>(off_evals);
+    CUDA_TRY(launch_like(a, s));
+    CUDA_TRY(cudaMemcpyAsync(logp, a.logp, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (evals) CUDA_TRY(cudaMemcpyAsync(evals, a.evals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return HDDM_OK;
+}
+
+int scalar_like(const double* h_x, const double* d_x, int64_t n, const double par[kNumPar], int mode,
+                const int32_t* h_cont, const Numerics& nm, double* logp)
+{
+    const Upload up[1] = {{par, kNumPar * sizeof(double)}};
+    ParSpec spec[kNumPar];
+    for (int k = 0; k < kNumPar; ++k) spec[k] = {0, k, 0, 0};
+    return like_impl(h_x, d_x, n, nullptr, h_cont, up, 1, spec, 1, mode, nm, logp, nullptr);
+}
+
+int batch_like(const double* h_x, const double* d_x, int64_t n, const int64_t* seg, const double* params,
+               int64_t P, const Numerics& nm, double* logp, unsigned long long* evals)
+{
+    if (P > 0 && !params) return fail(HDDM_ERR_ARG, "batch: null params");
+    const Upload up[1] = {{params, (size_t)P * kNumPar * sizeof(double)}};
+    ParSpec spec[kNumPar];
+    for (int k = 0; k < kNumPar; ++k) spec[k] = {0, k * P, 1, 0};
+    return like_impl(h_x, d_x, n, seg, nullptr, up, 1, spec, P, kModeWienerLike, nm, logp, evals);
+}
+
+int pdf_array_impl(const double* x, int64_t n, const double par[kNumPar], const Numerics& nm, int logp,
+                   double* y)
+{
+    if (n < 0 || (n > 0 && (!x || !y))) return fail(HDDM_ERR_ARG, "pdf_array: bad buffer");
+    TRY(check_numerics(nm.n_st, nm.n_sz, nm.use_adaptive));
+    TRY(ensure_ready());
+    if (n == 0) return HDDM_OK;
+    Layout L;
+    const size_t off_x = L.reserve((size_t)n * sizeof(double));
+    const size_t off_y = L.reserve((size_t)n * sizeof(double));
+    TRY(ensure_arena(L.total));
+    cudaStream_t s = g_rt.stream;
+    CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_x), x, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+    PdfArgs a;
+    a.x = L.at<double>(off_x);
+    a.y = L.at<double>(off_y);
+    a.n = n;
+    a.logp = logp;
+    a.evals = nullptr;
+    memcpy(a.par, par, sizeof(a.par));
+    a.nm = nm;
+    CUDA_TRY(launch_pdf_array(a, s));
+    CUDA_TRY(cudaMemcpyAsync(y, a.y, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return HDDM_OK;
+}
+
+}  // namespace
+
+struct hddm_trials {
+    double* d_x;
+    int64_t n;
+};
+
+extern "C" {
+
+int hddm_b200_version(void) { return 100; }
+
+const char* hddm_b200_last_error(void) { return g_err; }
+
+int hddm_b200_init(int device)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (device >= 0) CUDA_TRY(cudaSetDevice(device));
+    return ensure_ready();
+}
+
+int hddm_b200_device_count(int* count)
+{
+    if (!count) return fail(HDDM_ERR_ARG, "null count");
+    *count = 0;
+    CUDA_TRY(cudaGetDeviceCount(count));
+    return HDDM_OK;
+}
+
+int hddm_b200_synchronize(void)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    TRY(ensure_ready());
+    CUDA_TRY(cudaStreamSynchronize(g_rt.stream));
+    return HDDM_OK;
+}
+
+int hddm_b200_fp64_peak(int iters, double* flops, float* ms)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    TRY(ensure_ready());
+    if (!flops) return fail(HDDM_ERR_ARG, "null flops");
+    *flops = fp64_peak_probe(iters > 0 ? iters : 4096, ms, g_rt.stream);
+    CUDA_TRY(cudaGetLastError());
+    return *flops > 0 ? HDDM_OK : fail(HDDM_ERR_CUDA, "fp64 probe failed");
+}
+
+/* ---- wfpt module --------------------------------------------------------------------------- */
+
+int hddm_pdf_array(const double* x, int64_t n, double v, double sv, double a, double z, double sz,
+                   double t, double st, double err, int logp, int n_st, int n_sz, int use_adaptive,
+                   double simps_err, double p_outlier, double w_outlier, double* y)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, p_outlier, w_outlier};
+    return pdf_array_impl(x, n, par, make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, y);
+}
+
+int hddm_full_pdf(double x, double v, double sv, double a, double z, double sz, double t, double st,
+                  double err, int n_st, int n_sz, int use_adaptive, double simps_err, double* out)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!out) return fail(HDDM_ERR_ARG, "full_pdf: null out");
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, 0.0, 0.0};
+    return pdf_array_impl(&x, 1, par, make_numerics(err, n_st, n_sz, use_adaptive, simps_err), 0, out);
+}
+
+int hddm_wiener_like(const double* x, int64_t n, double v, double sv, double a, double z, double sz,
+                     double t, double st, double err, int n_st, int n_sz, int use_adaptive,
+                     double simps_err, double p_outlier, double w_outlier, double* logp)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, p_outlier, w_outlier};
+    return scalar_like(x, nullptr, n, par, kModeWienerLike, nullptr,
+                       make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp);
+}
+
+int hddm_wiener_like_multi(const double* x, int64_t n, const double* const par[7], const int64_t stride[7],
+                           double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                           double p_outlier, double w_outlier, double* logp)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!par || !stride) return fail(HDDM_ERR_ARG, "wiener_like_multi: null parameter table");
+    double scalars[kNumPar] = {0, 0, 0, 0, 0, 0, 0, p_outlier, w_outlier};
+    Upload up[8];
+    ParSpec spec[kNumPar];
+    int n_up = 1;
+    for (int k = 0; k < 7; ++k) {
+        if (!par[k]) return fail(HDDM_ERR_ARG, "wiener_like_multi: null parameter pointer");
+        if (stride[k] == 0) {
+            scalars[k] = par[k][0];
+            spec[k] = {0, k, 0, 0};
+        } else if (stride[k] == 1) {
+            up[n_up] = {par[k], (size_t)n * sizeof(double)};
+            spec[k] = {n_up, 0, 0, 1};
+            ++n_up;
+        } else {
+            return fail(HDDM_ERR_ARG, "wiener_like_multi: stride must be 0 (scalar) or 1 (per trial)");
+        }
+    }
+    spec[7] = {0, 7, 0, 0};
+    spec[8] = {0, 8, 0, 0};
+    up[0] = {scalars, sizeof(scalars)};
+    return like_impl(x, nullptr, n, nullptr, nullptr, up, n_up, spec, 1, kModeMulti,
+                     make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, nullptr);
+}
+
+int hddm_wiener_like_contaminant(const double* x, const int32_t* cont_x, int64_t n, double v, double sv,
+                                 double a, double z, double sz, double t, double st, double t_min,
+                                 double t_max, double err, int n_st, int n_sz, int use_adaptive,
+                                 double simps_err, double* logp)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (n > 0 && !cont_x) return fail(HDDM_ERR_ARG, "wiener_like_contaminant: null cont_x");
+    int n_cont = 0;  // `cdef int n_cont = np.sum(cont_x)`, src/wfpt.pyx:370
+    for (int64_t i = 0; i < n; ++i) n_cont += cont_x[i];
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, 0.0, 0.0};
+    TRY(scalar_like(x, nullptr, n, par, kModeContaminant, n > 0 ? cont_x : nullptr,
+                    make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp));
+    // src/wfpt.pyx:384 (never reached when a zero density returned -inf earlier, :377-379)
+    if (!(std::isinf(*logp) && *logp < 0)) *logp += n_cont * log(0.5 * 1. / (t_max - t_min));
+    return HDDM_OK;
+}
+
+int hddm_gen_cdf_using_pdf(const double* xgrid, int64_t m, double v, double sv, double a, double z,
+                           double sz, double t, double st, double err, int n_st, int n_sz, int use_adaptive,
+                           double simps_err, double p_outlier, double w_outlier, double* cdf)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (out_of_support(sv, a, z, sz, t, st, p_outlier))
+        return fail(HDDM_ERR_SUPPORT, "at least one of the parameters is out of the support");
+    if (m <= 0 || !xgrid || !cdf) return fail(HDDM_ERR_ARG, "gen_cdf_using_pdf: bad grid");
+    const Numerics nm = make_numerics(err, n_st, n_sz, use_adaptive, simps_err);
+    TRY(check_numerics(n_st, n_sz, use_adaptive));
+    TRY(ensure_ready());
+    Layout L;
+    const size_t off_x = L.reserve((size_t)m * sizeof(double));
+    const size_t off_y = L.reserve((size_t)m * sizeof(double));
+    TRY(ensure_arena(L.total));
+    cudaStream_t s = g_rt.stream;
+    CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_x), xgrid, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, s));
+    PdfArgs pa;
+    pa.x = L.at<double>(off_x);
+    pa.y = L.at<double>(off_y);
+    pa.n = m;
+    pa.logp = 0;
+    pa.evals = nullptr;
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, p_outlier, w_outlier};
+    memcpy(pa.par, par, sizeof(par));
+    pa.nm = nm;
+    CUDA_TRY(launch_pdf_array(pa, s));
+    CUDA_TRY(launch_cumtrapz_normalise(pa.y, m, s));
+    CUDA_TRY(cudaMemcpyAsync(cdf, pa.y, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return HDDM_OK;
+}
+
+int hddm_gen_rts_from_cdf(const double* xgrid, int64_t m, double v, double sv, double a, double z, double sz,
+                          double t, double st, const double* f, const double* u_delay, int64_t samples,
+                          double* rts, double* table)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (m <= 0 || samples < 0 || !xgrid || (samples > 0 && (!f || !rts)) || (st != 0 && samples > 0 && !u_delay))
+        return fail(HDDM_ERR_ARG, "gen_rts_from_cdf: bad buffer");
+    TRY(ensure_ready());
+    Layout L;
+    const size_t off_x = L.reserve((size_t)m * sizeof(double));
+    const size_t off_y = L.reserve((size_t)m * sizeof(double));
+    const size_t off_f = L.reserve((size_t)samples * sizeof(double));
+    const size_t off_u = L.reserve((size_t)samples * sizeof(double));
+    const size_t off_r = L.reserve((size_t)samples * sizeof(double));
+    TRY(ensure_arena(L.total));
+    cudaStream_t s = g_rt.stream;
+    CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_x), xgrid, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, s));
+    if (samples > 0) {
+        CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_f), f, (size_t)samples * sizeof(double), cudaMemcpyHostToDevice, s));
+        if (st != 0)
+            CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_u), u_delay, (size_t)samples * sizeof(double), cudaMemcpyHostToDevice, s));
+    }
+    // table of full_pdf(x[i], v, sv, a, z, sz, 0, 0, 1e-4) with the cpdef defaults n=2, adaptive,
+    // simps_err=1e-3 (src/wfpt.pyx:335, src/pdf.pxi:106-107)
+    PdfArgs pa;
+    pa.x = L.at<double>(off_x);
+    pa.y = L.at<double>(off_y);
+    pa.n = m;
+    pa.logp = 0;
+    pa.evals = nullptr;
+    const double par[kNumPar] = {v, sv, a, z, sz, 0.0, 0.0, 0.0, 0.0};
+    memcpy(pa.par, par, sizeof(par));
+    pa.nm = make_numerics(1e-4, 2, 2, 1, 1e-3);
+    CUDA_TRY(launch_pdf_array(pa, s));
+    CUDA_TRY(launch_cumsum_normalise(pa.y, m, s));
+    CUDA_TRY(launch_sample_rts(pa.x, pa.y, m, L.at<double>(off_f), L.at<double>(off_u), samples, t, st,
+                               L.at<double>(off_r), s));
+    if (samples > 0)
+        CUDA_TRY(cudaMemcpyAsync(rts, L.at<double>(off_r), (size_t)samples * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (table) CUDA_TRY(cudaMemcpyAsync(table, pa.y, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return HDDM_OK;
+}
+
+/* ---- cdfdif_wrapper module ------------------------------------------------------------------ */
+
+int hddm_dmat_cdf_array(const double* x, int64_t n, double v, double sv, double a, double z, double sz,
+                        double t, double st, double p_outlier, double w_outlier, double* y)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (n < 0 || (n > 0 && (!x || !y))) return fail(HDDM_ERR_ARG, "dmat_cdf_array: bad buffer");
+    if (p_outlier > 0 && n > 0) {  // src/cdfdif_wrapper.pyx:20-21
+        double peak = 0;
+        bool has_nan = false;
+        for (int64_t i = 0; i < n; ++i) {
+            const double m = fabs(x[i]);
+            has_nan |= (m != m);
+            if (m > peak) peak = m;
+        }
+        if (has_nan || !(peak < (1. / (2 * w_outlier))))
+            return fail(HDDM_ERR_RT_RANGE, "1. / (2*w_outlier) must be smaller than RT");
+    }
+    if (out_of_support(sv, a, z, sz, t, st, p_outlier))
+        return fail(HDDM_ERR_SUPPORT, "at least one of the parameters is out of the support");
+    TRY(ensure_ready());
+    if (n == 0) return HDDM_OK;
+    Layout L;
+    const size_t off_x = L.reserve((size_t)n * sizeof(double));
+    const size_t off_y = L.reserve((size_t)n * sizeof(double));
+    TRY(ensure_arena(L.total));
+    cudaStream_t s = g_rt.stream;
+    CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_x), x, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+    CdfArgs ca;
+    ca.x = L.at<double>(off_x);
+    ca.y = L.at<double>(off_y);
+    ca.n = n;
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, p_outlier, w_outlier};
+    memcpy(ca.par, par, sizeof(par));
+    CUDA_TRY(launch_cdf_array(ca, s));
+    CUDA_TRY(cudaMemcpyAsync(y, ca.y, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return HDDM_OK;
+}
+
+/* ---- batched likelihood ---------------------------------------------------------------------- */
+
+int hddm_wiener_like_batch(const double* x, int64_t n, const int64_t* seg, const double* params, int64_t P,
+                           double err, int n_st, int n_sz, int use_adaptive, double simps_err, double* logp,
+                           unsigned long long* evals)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    return batch_like(x, nullptr, n, seg, params, P, make_numerics(err, n_st, n_sz, use_adaptive, simps_err),
+                      logp, evals);
+}
+
+int hddm_wiener_like_multi_batch(const double* x, int64_t n, const double* v_trial, const double* params,
+                                 int64_t P, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                                 double* logp, unsigned long long* evals)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (P > 0 && (!params || (n > 0 && !v_trial))) return fail(HDDM_ERR_ARG, "multi_batch: null params");
+    const Upload up[2] = {{params, (size_t)P * kNumPar * sizeof(double)},
+                          {v_trial, (size_t)P * (size_t)n * sizeof(double)}};
+    ParSpec spec[kNumPar];
+    for (int k = 0; k < kNumPar; ++k) spec[k] = {0, k * P, 1, 0};
+    spec[0] = {1, 0, n, 1};
+    return like_impl(x, nullptr, n, nullptr, nullptr, up, 2, spec, P, kModeMulti,
+                     make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, evals);
+}
+
+/* ---- device-resident trials ------------------------------------------------------------------ */
+
+int hddm_trials_upload(const double* x, int64_t n, hddm_trials** out)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!out || n < 0 || (n > 0 && !x)) return fail(HDDM_ERR_ARG, "trials_upload: bad buffer");
+    TRY(ensure_ready());
+    hddm_trials* h = new (std::nothrow) hddm_trials{nullptr, n};
+    if (!h) return fail(HDDM_ERR_ARG, "trials_upload: out of host memory");
+    cudaError_t e = cudaMalloc(&h->d_x, (size_t)(n > 0 ? n : 1) * sizeof(double));
+    if (e == cudaSuccess && n > 0) {
+        e = cudaMemcpyAsync(h->d_x, x, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, g_rt.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(g_rt.stream);
+    }
+    if (e != cudaSuccess) {
+        if (h->d_x) cudaFree(h->d_x);
+        delete h;
+        CUDA_TRY(e);
+    }
+    *out = h;
+    return HDDM_OK;
+}
+
+int hddm_trials_free(hddm_trials* h)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!h) return HDDM_OK;
+    if (g_rt.ready) cudaStreamSynchronize(g_rt.stream);
+    cudaFree(h->d_x);
+    delete h;
+    return HDDM_OK;
+}
+
+int hddm_trials_wiener_like(const hddm_trials* h, double v, double sv, double a, double z, double sz, double t,
+                            double st, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                            double p_outlier, double w_outlier, double* logp)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!h) return fail(HDDM_ERR_ARG, "null trials handle");
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, p_outlier, w_outlier};
+    return scalar_like(nullptr, h->d_x, h->n, par, kModeWienerLike, nullptr,
+                       make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp);
+}
+
+int hddm_trials_wiener_like_batch(const hddm_trials* h, const int64_t* seg, const double* params, int64_t P,
+                                  double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                                  double* logp, unsigned long long* evals)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!h) return fail(HDDM_ERR_ARG, "null trials handle");
+    return batch_like(nullptr, h->d_x, h->n, seg, params, P,
+                      make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, evals);
+}
+
+/* ---- device-pointer entry points ------------------------------------------------------------- */
+
+int64_t hddm_wiener_like_batch_scratch(int64_t max_seg_len, int64_t P)
+{
+    return (P > 0 ? P : 0) * chunks_for(max_seg_len);
+}
+
+int hddm_wiener_like_batch_dev(const double* d_x, int64_t n, const int64_t* d_seg, int64_t max_seg_len,
+                               const double* d_params, int64_t P, double err, int n_st, int n_sz,
+                               int use_adaptive, double simps_err, double* d_logp, double* d_scratch,
+                               unsigned long long* d_evals, void* stream)
+{
+    if (n < 0 || P < 0 || (P > 0 && (!d_params || !d_logp || !d_scratch)) || (n > 0 && !d_x))
+        return fail(HDDM_ERR_ARG, "batch_dev: bad buffer or size");
+    TRY(check_numerics(n_st, n_sz, use_adaptive));
+    if (P == 0) return HDDM_OK;
+    const int64_t chunks = chunks_for(d_seg ? max_seg_len : n);
+    if (chunks > 65535) return fail(HDDM_ERR_ARG, "more than 65535*2048 trials per parameter set");
+    LikeArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = d_x;
+    a.seg = d_seg;
+    for (int k = 0; k < kNumPar; ++k) {
+        a.par[k] = d_params + k * P;
+        a.set_stride[k] = 1;
+        a.trial_stride[k] = 0;
+    }
+    a.n = n;
+    a.n_sets = P;
+    a.chunks = (int)chunks;
+    a.mode = kModeWienerLike;
+    a.nm = make_numerics(err, n_st, n_sz, use_adaptive, simps_err);
+    a.partial = d_scratch;
+    a.logp = d_logp;
+    a.evals = d_evals;
+    CUDA_TRY(launch_like(a, (cudaStream_t)stream));
+    return HDDM_OK;
+}
+
+int hddm_pdf_array_dev(const double* d_x, int64_t n, double v, double sv, double a, double z, double sz,
+                       double t, double st, double err, int logp, int n_st, int n_sz, int use_adaptive,
+                       double simps_err, double p_outlier, double w_outlier, double* d_y,
+                       unsigned long long* d_evals, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_x || !d_y))) return fail(HDDM_ERR_ARG, "pdf_array_dev: bad buffer");
+    TRY(check_numerics(n_st, n_sz, use_adaptive));
+    PdfArgs pa;
+    pa.x = d_x;
+    pa.y = d_y;
+    pa.n = n;
+    pa.logp = logp;
+    pa.evals = d_evals;
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, p_outlier, w_outlier};
+    memcpy(pa.par, par, sizeof(par));
+    pa.nm = make_numerics(err, n_st, n_sz, use_adaptive, simps_err);
+    CUDA_TRY(launch_pdf_array(pa, (cudaStream_t)stream));
+    return HDDM_OK;
+}
+
+int hddm_dmat_cdf_array_dev(const double* d_x, int64_t n, double v, double sv, double a, double z, double sz,
+                            double t, double st, double p_outlier, double w_outlier, double* d_y, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_x || !d_y))) return fail(HDDM_ERR_ARG, "dmat_cdf_array_dev: bad buffer");
+    if (out_of_support(sv, a, z, sz, t, st, p_outlier))
+        return fail(HDDM_ERR_SUPPORT, "at least one of the parameters is out of the support");
+    CdfArgs ca;
+    ca.x = d_x;
+    ca.y = d_y;
+    ca.n = n;
+    const double par[kNumPar] = {v, sv, a, z, sz, t, st, p_outlier, w_outlier};
+    memcpy(ca.par, par, sizeof(par));
+    CUDA_TRY(launch_cdf_array(ca, (cudaStream_t)stream));
+    return HDDM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,211 @@
+// cdfdif_kernels.cu -- full-DDM cumulative distribution (Tuerlinckx 2004) on the device.
+//
+// Mirrors the behaviour of src/cdfdif.c:59-221 behind src/cdfdif_wrapper.pyx:16-52.  Layout of
+// the work: one WARP per signed RT.  The 6 Gauss-Hermite drift nodes (branch "past the Ter
+// window") or the 36 (drift x start-point) node pairs (branch "inside the window") are spread
+// over lanes, so the lanes of a warp walk the Fourier series index v in lock step and the
+// 3-term stopping rule is evaluated warp-uniformly; node sums are reduced in the reference's
+// node order (m ascending, i ascending) so the result does not depend on lane scheduling.
+#include "kernels.cuh"
+
+namespace hddm {
+
+namespace {
+
+constexpr double kPiLong = 3.1415926535897932384626433832795028841971693993751;
+constexpr double kTiny = 1e-29;     // src/cdfdif.c:67
+constexpr double kNearZero = 1e-7;  // :68
+constexpr double kMinRt = 0.001;    // :69
+constexpr int kMaxTerms = 5000;     // :71
+
+__constant__ double c_gh_x[6] = {-2.3506049736744922818, -1.3358490740136970132, -.43607741192761650950,
+                                 .43607741192761650950,  1.3358490740136970132,  2.3506049736744922818};
+__constant__ double c_gh_w[6] = {.45300099055088421593e-2, .15706732032114842368, .72462959522439207571,
+                                 .72462959522439207571,    .15706732032114842368, .45300099055088421593e-2};
+__constant__ double c_gl_x[6] = {-.93246951420315193904, -.66120938646626381541, -.23861918608319693247,
+                                 .23861918608319712676,  .66120938646626459256,  .93246951420315160597};
+__constant__ double c_gl_w[6] = {.17132449237917049545, .36076157304813916138, .46791393457269092604,
+                                 .46791393457269092604, .36076157304813843973, .17132449237917132812};
+
+struct Hist {
+    double h0, h1, h2;
+    __device__ void push(double term)
+    {
+        h0 = h1;
+        h1 = h2;
+        h2 = h1 + term;
+    }
+    __device__ bool settled() const  // src/cdfdif.c:144-145, :177-178, :202-203
+    {
+        return (fabs(h0 - h1) < kTiny) && (fabs(h1 - h2) < kTiny) && (h2 > 0);
+    }
+};
+
+// Sum `val` held by lanes [0, count) in ascending lane order (fixed order => deterministic and
+// the reference's node order).
+__device__ __forceinline__ double ordered_lane_sum(double val, int count)
+{
+    double s = 0.0;
+    for (int l = 0; l < count; ++l) s += __shfl_sync(0xffffffffu, val, l);
+    return s;
+}
+
+}  // namespace
+
+// One warp evaluates cdfdif(|x|, x>0, par) and the wrapper's signed assembly + outlier mix.
+__global__ void __launch_bounds__(128) k_cdf_array(const CdfArgs q)
+{
+    const int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= q.n) return;
+    const int lane = threadIdx.x & 31;
+
+    // wrapper rescale to DMAT units, src/cdfdif_wrapper.pyx:36-42 (par: v sv a z sz t st po wo)
+    const double a = q.par[2] / 10.;
+    const double Ter = q.par[5];
+    const double eta = q.par[1] / 10. + 1e-10;
+    const double z = q.par[3] * (q.par[2] / 10.);
+    const double sZ = q.par[4] * (q.par[2] / 10.) + 1e-10;
+    const double st = q.par[6] + 1e-10;
+    const double nu = q.par[0] / 10.;
+
+    const double xs = q.x[i];
+    const double t = fabs(xs);
+    const int x = xs > 0 ? 1 : 0;
+    const double sx = (double)(2 * x - 1);  // +1 upper, -1 lower
+    const double a2 = a * a;
+    const double zc = (1 - x) * z + x * (a - z);
+    const double Z_U = zc + sZ / 2, Z_L = zc - sZ / 2;
+    const double lower_t = Ter - st / 2;
+
+    // node owned by this lane: m = drift node, ii = start-point node (36 pairs on lanes 0..35
+    // would not fit a warp: lanes take pair `lane` and, for lane < 4, also pair 32 + lane)
+    const int m6 = lane % 6;
+    const double gk = 1.41421356237309505 * c_gh_x[m6] * eta + nu;  // src/cdfdif.c:86
+    const double wgh = c_gh_w[m6] / 1.772453850905515882;           // :88
+
+    // ---- probability of the boundary, src/cdfdif.c:96-113: lane (i6 = lane/6, m6) for lane<36
+    double prob;
+    {
+        double sum_z = 0.0;
+        for (int i6 = 0; i6 < 6; ++i6) {
+            const double gz = (.5 * sZ * c_gl_x[i6]) + z;  // :92
+            double term;
+            if (fabs(gk) > kNearZero)
+                term = (exp(-200 * gz * gk) - 1) / (exp(-200 * a * gk) - 1) * wgh;
+            else
+                term = gz / a * wgh;
+            const double sum_nu = ordered_lane_sum(term, 6);  // lanes 0..5 hold m = 0..5
+            sum_z += sum_nu * c_gl_w[i6] / 2;
+        }
+        prob = sum_z;
+    }
+
+    double F = 0.0;
+    if (t - Ter + st / 2 > kMinRt) {  // :116
+        const double upper_t = t < Ter + st / 2 ? t : Ter + st / 2;
+        const double p1 = prob * (upper_t - lower_t) / st;
+        const double p0 = (1 - prob) * (upper_t - lower_t) / st;
+        const double base = p0 * (1 - x) + p1 * x;
+        if (t > Ter + st / 2) {  // :121-150, lanes 0..5 own the drift nodes
+            Hist s = {0, 0, 0};
+            const double log_w = log(wgh), two_log100 = 2 * log(100.0);
+            for (int v = 0; v < kMaxTerms; ++v) {
+                const double sifa = kPiLong * v / a;
+                double su, cu, sl, cl;
+                sincos(sifa * Z_U, &su, &cu);
+                sincos(sifa * Z_L, &sl, &cl);
+                const double denom = (100 * gk * gk + (kPiLong * kPiLong) * (v * v) / (100 * a2));
+                const double ld = 3 * log(denom);
+                const double upp = exp(sx * Z_U * gk * 100 - ld + log_w - two_log100);
+                const double low = exp(sx * Z_L * gk * 100 - ld + log_w - two_log100);
+                const double fact = upp * (sx * gk * su * 100 - sifa * cu) - low * (sx * gk * sl * 100 - sifa * cl);
+                const double exdif =
+                    exp((-.5 * denom * (t - upper_t)) + log(1 - exp(-.5 * denom * (upper_t - lower_t))));
+                const double sum_nu = ordered_lane_sum(fact * exdif, 6);
+                s.push(v * sum_nu);
+                if (s.settled()) break;
+            }
+            F = base - s.h2 * 4 * kPiLong / (a2 * sZ * st);
+        } else {  // :151-211, t inside the Ter window
+            // Every lane walks the series of one (m, i) pair at a time; pairs are assigned
+            // pair = round*32 + lane for round 0,1 (36 pairs).  Series lengths differ per pair, so
+            // lanes leave the v loop individually (no shuffles inside it).
+            double pair_val[2] = {0.0, 0.0};
+            const bool any_zero_drift = __any_sync(0xffffffffu, (lane < 6) && !(fabs(gk) > kNearZero));
+            for (int round = 0; round < 2; ++round) {
+                const int pair = round * 32 + lane;
+                if (pair >= 36) break;
+                const int m = pair / 6, i6 = pair % 6;
+                const double g = 1.41421356237309505 * c_gh_x[m] * eta + nu;
+                if (!(fabs(g) > kNearZero)) continue;  // handled by the zero-drift series below
+                const double gz = (.5 * sZ * c_gl_x[i6]) + z;
+                const double zzz = (a - gz) * x + gz * (1 - x);
+                const double f = (double)(1 - 2 * x);
+                const double sh = sinh(f * g * a / .01);
+                const double ser = -((a * a2) / (f * g * kPiLong * .01)) * sinh(zzz * f * g / .01) / (sh * sh) +
+                                   (zzz * a2) / (f * g * kPiLong * .01) * cosh((a - zzz) * f * g / .01) / sh;
+                Hist s = {0, 0, 0};
+                for (int v = 0; v < kMaxTerms; ++v) {
+                    const double sifa = kPiLong * v / a;
+                    const double denom = (g * g * 100 + (kPiLong * v) * (kPiLong * v) / (a2 * 100));
+                    s.push(v * sin(sifa * zzz) * exp(-.5 * denom * (t - lower_t) - 2 * log(denom)));
+                    if (s.settled()) break;
+                }
+                pair_val[round] = .5 * c_gl_w[i6] * (ser - 4 * s.h2) * (kPiLong / 100) / (a2 * st) *
+                                  exp(sx * zzz * g * 100);
+            }
+            double zero_branch = 0.0;
+            if (any_zero_drift) {  // :185-207 (warp-uniform; every lane computes the same value)
+                Hist s = {0, 0, 0};
+                const double su = -(Z_U * Z_U) / (12 * a2) + (Z_U * Z_U * Z_U) / (12 * a * a2) -
+                                  (Z_U * Z_U * Z_U * Z_U) / (48 * a2 * a2);
+                const double sl = -(Z_L * Z_L) / (12 * a2) + (Z_L * Z_L * Z_L) / (12 * a * a2) -
+                                  (Z_L * Z_L * Z_L * Z_L) / (48 * a2 * a2);
+                for (int v = 1; v < kMaxTerms; ++v) {
+                    const double sifa = kPiLong * v / a;
+                    const double denom = (kPiLong * v) * (kPiLong * v) / (a2 * 100);
+                    const double vd = (double)v;
+                    s.push(1 / (kPiLong * kPiLong * kPiLong * kPiLong * vd * vd * vd * vd) *
+                           (cos(sifa * Z_L) - cos(sifa * Z_U)) * exp(-.5 * denom * (t - lower_t)));
+                    if (s.settled()) break;
+                }
+                zero_branch = 400 * a2 * a * (sl - su - s.h2) / (st * sZ);
+            }
+            // assemble in the reference's order: for m: sum_z = sum_i pair(m,i); sum_nu += sum_z*w_gh[m]
+            double sum_nu = 0.0;
+            for (int m = 0; m < 6; ++m) {
+                const double g = 1.41421356237309505 * c_gh_x[m] * eta + nu;
+                double sum_z = 0.0;
+                if (fabs(g) > kNearZero) {
+                    for (int i6 = 0; i6 < 6; ++i6) {
+                        const int pair = m * 6 + i6;
+                        sum_z += __shfl_sync(0xffffffffu, pair_val[pair >> 5], pair & 31);
+                    }
+                } else {
+                    sum_z = zero_branch;
+                }
+                sum_nu += sum_z * (c_gh_w[m] / 1.772453850905515882);
+            }
+            F = base - sum_nu;
+        }
+    }
+    F = F > kTiny ? F : 0;  // :218
+
+    if (lane == 0) {  // src/cdfdif_wrapper.pyx:46-51
+        const double sgn = (double)((xs > 0) - (xs < 0));
+        double y = (1 - prob) + sgn * F;
+        const double po = q.par[7], wo = q.par[8];
+        y = y * (1 - po) + (xs + (1. / (2 * wo))) * wo * po;
+        q.y[i] = y;
+    }
+}
+
+cudaError_t launch_cdf_array(const CdfArgs& a, cudaStream_t stream)
+{
+    if (a.n <= 0) return cudaSuccess;
+    const int warps_per_block = 4;
+    k_cdf_array<<<(unsigned)((a.n + warps_per_block - 1) / warps_per_block), 128, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace hddm

@@ -1,0 +1,85 @@
+// kernels.cuh -- launch interfaces shared by the kernel translation units and the C-ABI (abi.cu).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+
+namespace hddm {
+
+constexpr int kMaxDepth = 24;  // max n_st / n_sz for the adaptive explicit stack (HDDM_MAX_DEPTH)
+
+struct Numerics {
+    double err;
+    double simps_err;
+    int n_st;
+    int n_sz;
+    int use_adaptive;
+};
+
+// Parameter order used everywhere: v, sv, a, z, sz, t, st, p_outlier, w_outlier.
+constexpr int kNumPar = 9;
+constexpr int kTrialsPerBlock = 2048;  // one CTA reduces this many trials of one parameter set
+constexpr int kLikeThreads = 256;
+
+enum LikeMode : int {
+    kModeWienerLike = 0,  // src/wfpt.pyx:54-76   outlier mix, p==0 -> -inf
+    kModeMulti = 1,       // src/wfpt.pyx:244-274 +-999 sentinels, no zero guard
+    kModeContaminant = 2  // src/wfpt.pyx:357-386 skip cont_x != 0, p==0 -> -inf, no mix
+};
+
+// One launch evaluates `n_sets` parameter sets.  Parameter k of (set p, trial i) is read from
+// par[k][p * set_stride[k] + i * trial_stride[k]] (i = absolute index into x):
+//   scalar set                -> both strides 0
+//   batch of sets (SoA [9][P]) -> set_stride 1, trial_stride 0
+//   regression (per trial)    -> trial_stride 1 (set_stride = n for a batch of regressions)
+// Set p sees trials [seg[p], seg[p+1]) of x, or all n trials when seg == nullptr.
+struct LikeArgs {
+    const double* x;
+    const int64_t* seg;
+    const int32_t* cont;  // contaminant flags (mode 2) or nullptr
+    const double* par[kNumPar];
+    int64_t set_stride[kNumPar];
+    int64_t trial_stride[kNumPar];
+    int64_t n;
+    int64_t n_sets;
+    int chunks;  // ceil(max segment length / kTrialsPerBlock)
+    int mode;
+    Numerics nm;
+    double* partial;             // [n_sets * chunks]
+    double* logp;                // [n_sets]
+    unsigned long long* evals;   // device counter of pdf_sv evaluations (may be nullptr)
+};
+
+cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream);
+
+struct PdfArgs {
+    const double* x;
+    double* y;
+    int64_t n;
+    double par[kNumPar];
+    int logp;
+    Numerics nm;
+    unsigned long long* evals;
+};
+cudaError_t launch_pdf_array(const PdfArgs& a, cudaStream_t stream);
+
+// cdfdif (src/cdfdif.c:59-221 + src/cdfdif_wrapper.pyx:36-51): y[i] for signed RT x[i].
+struct CdfArgs {
+    const double* x;
+    double* y;
+    int64_t n;
+    double par[kNumPar];
+};
+cudaError_t launch_cdf_array(const CdfArgs& a, cudaStream_t stream);
+
+// In-place table post-processing for gen_cdf_using_pdf / gen_rts_from_cdf (src/wfpt.pyx:333-353,
+// :405-412): one CTA scans a table of m densities.
+cudaError_t launch_cumtrapz_normalise(double* table, int64_t m, cudaStream_t stream);
+cudaError_t launch_cumsum_normalise(double* table, int64_t m, cudaStream_t stream);
+cudaError_t launch_sample_rts(const double* xgrid, const double* table, int64_t m, const double* f,
+                              const double* u_delay, int64_t samples, double t, double st,
+                              double* rts, cudaStream_t stream);
+
+double fp64_peak_probe(int iters, float* ms_out, cudaStream_t stream);
+
+}  // namespace hddm

@@ -1,0 +1,207 @@
+// wfpt_kernels.cu -- likelihood kernels: one thread per (trial, parameter set).
+//
+// k_like_partial   grid (n_sets, chunks): CTA (p, c) evaluates trials
+//                  [lo_p + c*2048, lo_p + (c+1)*2048) of set p, thread j takes trials
+//                  j, j+256, ... (coalesced 8-byte loads of x and of per-trial parameters),
+//                  sums log-densities in that order, then a fixed xor-shuffle tree per warp and
+//                  a fixed-order sum over the 8 warps -> partial[p*chunks + c].
+// k_like_final     one warp per set adds the chunk partials in ascending order (lane-strided,
+//                  then the same shuffle tree) and applies the reference's -inf rule.
+// No atomics on floating point anywhere: results are bit-reproducible run to run and independent
+// of how sets are sharded over GPUs.
+#include "kernels.cuh"
+#include "wfpt_device.cuh"
+
+namespace hddm {
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    return v;
+}
+
+__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v)
+{
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    return v;
+}
+
+__device__ __forceinline__ double load_par(const LikeArgs& a, int k, int64_t p, int64_t i)
+{
+    return __ldg(a.par[k] + p * a.set_stride[k] + i * a.trial_stride[k]);
+}
+
+__global__ void __launch_bounds__(kLikeThreads) k_like_partial(const LikeArgs a)
+{
+    const int64_t p = blockIdx.x;
+    const int chunk = blockIdx.y;
+    const int64_t lo = a.seg ? a.seg[p] : 0;
+    const int64_t hi = a.seg ? a.seg[p + 1] : a.n;
+    const int64_t begin = lo + (int64_t)chunk * kTrialsPerBlock;
+    const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
+    // src/wfpt.pyx:50-51,63-64: p_outlier outside [0,1] -> -inf before any trial is looked at
+    const bool range_ok = (a.mode == kModeMulti) || ((p_out >= 0) & (p_out <= 1));
+    if (begin >= hi || !range_ok) {  // (ragged batch: shorter sets have empty trailing chunks)
+        if (threadIdx.x == 0) a.partial[p * a.chunks + chunk] = range_ok ? 0.0 : -INFINITY;
+        return;
+    }
+    const int64_t end = begin + kTrialsPerBlock < hi ? begin + kTrialsPerBlock : hi;
+
+    // Set-uniform parameters are read once; per-trial ones (trial_stride != 0) inside the loop.
+    double par[7];
+    bool per_trial = false;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        par[k] = load_par(a, k, p, 0);
+        per_trial |= a.trial_stride[k] != 0;
+    }
+
+    double acc = 0.0;
+    unsigned long long evals = 0;
+    bool hit_zero = false;
+    for (int64_t i = begin + threadIdx.x; i < end; i += kLikeThreads) {
+        const double x = __ldg(a.x + i);
+        if (per_trial) {
+#pragma unroll
+            for (int k = 0; k < 7; ++k)
+                if (a.trial_stride[k] != 0) par[k] = load_par(a, k, p, i);
+        }
+        double d;
+        if (a.mode == kModeMulti) {
+            if (fabs(x) != 999.) {  // src/wfpt.pyx:261-266
+                d = full_pdf(x, par[0], par[1], par[2], par[3], par[4], par[5], par[6], a.nm, evals);
+                d = d * (1 - p_out) + w_out * p_out;
+            } else if (x == 999.) {  // :267-268
+                d = prob_ub(par[0], par[2], par[3]);
+            } else {  // :269-270
+                d = 1 - prob_ub(par[0], par[2], par[3]);
+            }
+            acc += log(d);
+        } else {
+            if (a.mode == kModeContaminant && a.cont[i] != 0) continue;  // src/wfpt.pyx:374
+            d = full_pdf(x, par[0], par[1], par[2], par[3], par[4], par[5], par[6], a.nm, evals);
+            d = d * (1 - p_out) + w_out * p_out;  // src/wfpt.pyx:70 (contaminant: p_out = 0)
+            hit_zero |= (d == 0);                 // :71-72, :377-379
+            acc += log(d);
+        }
+    }
+
+    __shared__ double warp_part[kLikeThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    acc = warp_sum(acc);
+    if (lane == 0) warp_part[warp] = acc;
+    const int any_zero = __syncthreads_or(hit_zero ? 1 : 0);
+    if (a.evals) {
+        evals = warp_sum_u64(evals);
+        if (lane == 0) atomicAdd(a.evals, evals);
+    }
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kLikeThreads / 32; ++w) s += warp_part[w];
+        if (a.mode != kModeMulti && any_zero) s = -INFINITY;
+        a.partial[p * a.chunks + chunk] = s;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_like_final(const LikeArgs a)
+{
+    const int64_t p = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (p >= a.n_sets) return;
+    const int lane = threadIdx.x & 31;
+    const double* row = a.partial + p * a.chunks;
+    double s = 0.0;
+    bool neg_inf = false;
+    for (int c = lane; c < a.chunks; c += 32) {
+        const double v = row[c];
+        neg_inf |= (v == -INFINITY);
+        s += v;
+    }
+    s = warp_sum(s);
+    neg_inf = __any_sync(0xffffffffu, neg_inf);
+    // wiener_like returns -inf at the FIRST zero density whatever the running sum holds
+    // (src/wfpt.pyx:71-72): a -inf partial (only produced by that rule) overrides NaN.
+    if (a.mode != kModeMulti && neg_inf) s = -INFINITY;
+    if (lane == 0) a.logp[p] = s;
+}
+
+cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
+{
+    if (a.n_sets <= 0) return cudaSuccess;
+    dim3 grid((unsigned)a.n_sets, (unsigned)a.chunks);
+    k_like_partial<<<grid, kLikeThreads, 0, stream>>>(a);
+    const int sets_per_block = 128 / 32;
+    k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+// pdf_array (src/wfpt.pyx:32-48): per-trial density, outlier mix, optional log.
+__global__ void __launch_bounds__(kLikeThreads) k_pdf_array(const PdfArgs a)
+{
+    unsigned long long evals = 0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
+        double d = full_pdf(__ldg(a.x + i), a.par[0], a.par[1], a.par[2], a.par[3], a.par[4],
+                            a.par[5], a.par[6], a.nm, evals);
+        d = d * (1 - a.par[7]) + (a.par[8] * a.par[7]);
+        a.y[i] = a.logp == 1 ? log(d) : d;
+    }
+    if (a.evals) {
+        evals = warp_sum_u64(evals);
+        if ((threadIdx.x & 31) == 0) atomicAdd(a.evals, evals);
+    }
+}
+
+cudaError_t launch_pdf_array(const PdfArgs& a, cudaStream_t stream)
+{
+    if (a.n <= 0) return cudaSuccess;
+    int64_t blocks = (a.n + kLikeThreads - 1) / kLikeThreads;
+    if (blocks > 148 * 64) blocks = 148 * 64;
+    k_pdf_array<<<(unsigned)blocks, kLikeThreads, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+// Register-resident dependent-FMA chains: the FP64 roofline denominator, measured on the box
+// (MEASURED_PEAKS.json has no FP64 entry).  8 independent chains per thread.
+__global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters)
+{
+    double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5,
+           a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 0.999999, c = 1e-7;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+            a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+        }
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+}
+
+// Returns achieved FP64 FLOP/s (2 per FMA) of the probe; *ms_out = kernel time.
+double fp64_peak_probe(int iters, float* ms_out, cudaStream_t stream)
+{
+    const int blocks = 148 * 8, threads = 256;
+    double* buf = nullptr;
+    if (cudaMalloc(&buf, sizeof(double) * blocks * threads) != cudaSuccess) return -1.0;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    k_fp64_peak<<<blocks, threads, 0, stream>>>(buf, 64);  // warm-up
+    cudaEventRecord(e0, stream);
+    k_fp64_peak<<<blocks, threads, 0, stream>>>(buf, iters);
+    cudaEventRecord(e1, stream);
+    cudaEventSynchronize(e1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(buf);
+    if (ms_out) *ms_out = ms;
+    const double fmas = (double)blocks * threads * (double)iters * 64.0;
+    return 2.0 * fmas / (ms * 1e-3);
+}
+
+}  // namespace hddm

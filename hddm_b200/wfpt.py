@@ -1,0 +1,237 @@
+"""Drop-in for the reference's `wfpt` extension module (hddm.wfpt, /root/reference/src/wfpt.pyx).
+
+Same function names, positional order, keyword names and defaults; same return types and error
+behaviour (-inf for zero probability, ValueError out of support).  Every function forwards to the
+CUDA library through the C ABI of include/hddm_b200.h -- nothing is computed in Python except
+what the reference itself does in numpy (grid construction with np.linspace / np.arange, the
+uniforms of np.random, split_cdf's pure-numpy reshuffle).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import as_rt_buffer, check, dptr, lib
+
+__all__ = ["full_pdf", "pdf_array", "wiener_like", "wiener_like_multi", "wiener_like_contaminant",
+           "gen_cdf_using_pdf", "gen_rts_from_cdf", "split_cdf", "wiener_like_batch",
+           "wiener_like_multi_batch", "Trials"]
+
+_PARAM_NAMES = ("v", "sv", "a", "z", "sz", "t", "st")
+
+
+def full_pdf(x, v, sv, a, z, sz, t, st, err, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3):
+    """src/pdf.pxi:104-146 (cpdef full_pdf)."""
+    out = C.c_double()
+    check(lib().hddm_full_pdf(x, v, sv, a, z, sz, t, st, err, n_st, n_sz, int(bool(use_adaptive)),
+                              simps_err, C.byref(out)))
+    return out.value
+
+
+def pdf_array(x, v, sv, a, z, sz, t, st, err=1e-4, logp=0, n_st=2, n_sz=2, use_adaptive=1,
+              simps_err=1e-3, p_outlier=0, w_outlier=0):
+    """src/wfpt.pyx:32-48."""
+    x = as_rt_buffer(x)
+    y = np.empty(x.shape[0], dtype=np.double)
+    check(lib().hddm_pdf_array(dptr(x), x.shape[0], v, sv, a, z, sz, t, st, err, int(bool(logp)), n_st,
+                               n_sz, int(bool(use_adaptive)), simps_err, p_outlier, w_outlier, dptr(y)))
+    return y
+
+
+def wiener_like(x, v, sv, a, z, sz, t, st, err, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-8,
+                p_outlier=0, w_outlier=0.1):
+    """src/wfpt.pyx:54-76."""
+    x = as_rt_buffer(x)
+    out = C.c_double()
+    check(lib().hddm_wiener_like(dptr(x), x.shape[0], v, sv, a, z, sz, t, st, err, n_st, n_sz,
+                                 int(bool(use_adaptive)), simps_err, p_outlier, w_outlier, C.byref(out)))
+    return out.value
+
+
+def wiener_like_multi(x, v, sv, a, z, sz, t, st, err, multi=None, n_st=10, n_sz=10, use_adaptive=1,
+                      simps_err=1e-3, p_outlier=0, w_outlier=0):
+    """src/wfpt.pyx:244-274.  Parameters named in `multi` are per-trial float64 arrays."""
+    x = as_rt_buffer(x)
+    if multi is None:
+        # src/wfpt.pyx:253-254 passes the whole array to the scalar full_pdf and cannot succeed
+        raise TypeError("only size-1 arrays can be converted to Python scalars")
+    values = dict(zip(_PARAM_NAMES, (v, sv, a, z, sz, t, st)))
+    multi = set(multi)
+    keep, ptrs, strides = [], (C.POINTER(C.c_double) * 7)(), (C.c_int64 * 7)()
+    for k, name in enumerate(_PARAM_NAMES):
+        if name in multi:
+            arr = np.ascontiguousarray(np.asarray(values[name], dtype=np.float64))
+            if arr.ndim != 1 or arr.shape[0] < x.shape[0]:
+                raise IndexError("per-trial parameter '%s' is shorter than x" % name)
+            strides[k] = 1
+        else:
+            arr = np.array([values[name]], dtype=np.float64)
+            strides[k] = 0
+        keep.append(arr)
+        ptrs[k] = dptr(arr)
+    out = C.c_double()
+    check(lib().hddm_wiener_like_multi(dptr(x), x.shape[0], ptrs, strides, err, n_st, n_sz,
+                                       int(bool(use_adaptive)), simps_err, p_outlier, w_outlier,
+                                       C.byref(out)))
+    return out.value
+
+
+def wiener_like_contaminant(x, cont_x, v, sv, a, z, sz, t, st, t_min, t_max, err, n_st=10, n_sz=10,
+                            use_adaptive=1, simps_err=1e-8):
+    """src/wfpt.pyx:357-386.  cont_x must be an int32 array (np.ndarray[int, ndim=1])."""
+    x = as_rt_buffer(x)
+    if not isinstance(cont_x, np.ndarray):
+        raise TypeError("Argument 'cont_x' has incorrect type")
+    if cont_x.dtype != np.int32 or cont_x.ndim != 1:
+        raise ValueError("Buffer dtype mismatch, expected 'int' but got '%s'" % cont_x.dtype)
+    cont_x = np.ascontiguousarray(cont_x)
+    out = C.c_double()
+    check(lib().hddm_wiener_like_contaminant(dptr(x), cont_x.ctypes.data_as(_lib.c_ip), x.shape[0], v, sv,
+                                             a, z, sz, t, st, t_min, t_max, err, n_st, n_sz,
+                                             int(bool(use_adaptive)), simps_err, C.byref(out)))
+    return out.value
+
+
+def gen_cdf_using_pdf(v, sv, a, z, sz, t, st, err, N=500, time=5., n_st=2, n_sz=2, use_adaptive=1,
+                      simps_err=1e-3, p_outlier=0, w_outlier=0):
+    """src/wfpt.pyx:389-414.  Returns (x, cdf_array); ValueError out of support."""
+    x = np.linspace(-time, time, 2 * N + 1)
+    cdf = np.empty(x.shape[0], dtype=np.double)
+    check(lib().hddm_gen_cdf_using_pdf(dptr(x), x.shape[0], v, sv, a, z, sz, t, st, err, n_st, n_sz,
+                                       int(bool(use_adaptive)), simps_err, p_outlier, w_outlier, dptr(cdf)))
+    return x, cdf
+
+
+def gen_rts_from_cdf(v, sv, a, z, sz, t, st, samples=1000, cdf_lb=-6, cdf_ub=6, dt=1e-2,
+                     f=None, u_delay=None):
+    """src/wfpt.pyx:323-354.  The uniforms come from numpy's global RNG in the reference's draw
+    order (f, then the delay uniforms when st != 0) unless passed explicitly (NEW, for parity
+    tests and device-side pipelines)."""
+    x = np.arange(cdf_lb, cdf_ub, dt)
+    if f is None:
+        f = np.random.rand(samples)
+    f = np.ascontiguousarray(f, dtype=np.float64)
+    if st != 0:
+        if u_delay is None:
+            u_delay = np.random.rand(samples)
+        u_delay = np.ascontiguousarray(u_delay, dtype=np.float64)
+        up = dptr(u_delay)
+    else:
+        up = None
+    rts = np.empty(samples, dtype=np.double)
+    check(lib().hddm_gen_rts_from_cdf(dptr(x), x.shape[0], v, sv, a, z, sz, t, st, dptr(f), up, samples,
+                                      dptr(rts), None))
+    return rts
+
+
+def split_cdf(x, data):
+    """src/wfpt.pyx:417-433 (pure numpy in the reference too; `/` is Python-2 integer division)."""
+    N = (len(data) - 1) // 2
+    x_lb = -x[:N][::-1]
+    lb = data[:N][::-1]
+    lb = np.cumsum(np.concatenate([np.array([0]), -np.diff(lb)]))
+    x_ub = x[N + 1:]
+    ub = data[N + 1:]
+    ub -= ub[0]
+    return (x_lb, lb, x_ub, ub)
+
+
+# ---- NEW: batched entry points -------------------------------------------------------------------
+
+def _pack_params(params, P=None):
+    """Accept float64 [9, P] (rows v, sv, a, z, sz, t, st, p_outlier, w_outlier) or a dict of
+    scalars/arrays with those names (p_outlier default 0, w_outlier default 0.1)."""
+    if isinstance(params, dict):
+        names = _PARAM_NAMES + ("p_outlier", "w_outlier")
+        defaults = {"p_outlier": 0.0, "w_outlier": 0.1}
+        cols = [np.atleast_1d(np.asarray(params.get(n, defaults.get(n)), dtype=np.float64)) for n in names]
+        P = max(c.shape[0] for c in cols)
+        params = np.stack([np.broadcast_to(c, (P,)) for c in cols])
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    if params.ndim != 2 or params.shape[0] != 9:
+        raise ValueError("params must be float64 [9, P]: v, sv, a, z, sz, t, st, p_outlier, w_outlier")
+    return params
+
+
+def wiener_like_batch(x, params, seg=None, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3,
+                      return_evals=False):
+    """P parameter sets against their trials in ONE launch; returns float64[P] of wiener_like values
+    (src/wfpt.pyx:54-76 semantics per set, including -inf).  seg: int64[P+1] trial offsets per set
+    (ragged: subjects x proposals), or None when every set sees all of x."""
+    x = as_rt_buffer(x)
+    params = _pack_params(params)
+    P = params.shape[1]
+    segp = None
+    if seg is not None:
+        seg = np.ascontiguousarray(seg, dtype=np.int64)
+        if seg.shape != (P + 1,):
+            raise ValueError("seg must have P+1 entries")
+        segp = seg.ctypes.data_as(_lib.c_lp)
+    out = np.empty(P, dtype=np.double)
+    evals = C.c_ulonglong(0)
+    check(lib().hddm_wiener_like_batch(dptr(x), x.shape[0], segp, dptr(params), P, err, n_st, n_sz,
+                                       int(bool(use_adaptive)), simps_err, dptr(out), C.byref(evals)))
+    return (out, evals.value) if return_evals else out
+
+
+def wiener_like_multi_batch(x, v_trial, params, err=1e-4, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-3,
+                            return_evals=False):
+    """Regression layout: v_trial float64 [P, n] per-trial drift for each of P sets, the other eight
+    parameters per set in params [9, P] (row 0 ignored); wiener_like_multi semantics per set."""
+    x = as_rt_buffer(x)
+    params = _pack_params(params)
+    P = params.shape[1]
+    v_trial = np.ascontiguousarray(v_trial, dtype=np.float64)
+    if v_trial.shape != (P, x.shape[0]):
+        raise ValueError("v_trial must be [P, n]")
+    out = np.empty(P, dtype=np.double)
+    evals = C.c_ulonglong(0)
+    check(lib().hddm_wiener_like_multi_batch(dptr(x), x.shape[0], dptr(v_trial), dptr(params), P, err, n_st,
+                                             n_sz, int(bool(use_adaptive)), simps_err, dptr(out),
+                                             C.byref(evals)))
+    return (out, evals.value) if return_evals else out
+
+
+class Trials(object):
+    """Device-resident signed RTs of one observed node: uploaded once, reused by every logp call of
+    the MCMC loop (the reference re-reads `x['rt'].values` on every call, hddm/likelihoods.py:54)."""
+
+    def __init__(self, x):
+        x = as_rt_buffer(x)
+        self.n = x.shape[0]
+        self._h = C.c_void_p()
+        check(lib().hddm_trials_upload(dptr(x), self.n, C.byref(self._h)))
+
+    def wiener_like(self, v, sv, a, z, sz, t, st, err, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-8,
+                    p_outlier=0, w_outlier=0.1):
+        out = C.c_double()
+        check(lib().hddm_trials_wiener_like(self._h, v, sv, a, z, sz, t, st, err, n_st, n_sz,
+                                            int(bool(use_adaptive)), simps_err, p_outlier, w_outlier,
+                                            C.byref(out)))
+        return out.value
+
+    def wiener_like_batch(self, params, seg=None, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3,
+                          return_evals=False):
+        params = _pack_params(params)
+        P = params.shape[1]
+        segp = None
+        if seg is not None:
+            seg = np.ascontiguousarray(seg, dtype=np.int64)
+            segp = seg.ctypes.data_as(_lib.c_lp)
+        out = np.empty(P, dtype=np.double)
+        evals = C.c_ulonglong(0)
+        check(lib().hddm_trials_wiener_like_batch(self._h, segp, dptr(params), P, err, n_st, n_sz,
+                                                  int(bool(use_adaptive)), simps_err, dptr(out),
+                                                  C.byref(evals)))
+        return (out, evals.value) if return_evals else out
+
+    def close(self):
+        if self._h:
+            lib().hddm_trials_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,157 @@
+/*
+ * hddm_b200.h -- C ABI of libhddm_b200.so: the B200 (sm_100a) implementation of HDDM's Wiener
+ * first-passage-time hot path.  This is the drop-in boundary: each entry point below replaces
+ * one Python-visible function of the reference's two native extension modules
+ *     wfpt            (/root/reference/src/wfpt.pyx, built by setup.py:6)
+ *     cdfdif_wrapper  (/root/reference/src/cdfdif_wrapper.pyx + src/cdfdif.c, setup.py:7)
+ * with plain pointers and sizes (no Python, numpy or torch types).  INTEGRATION.md shows the
+ * ctypes binding a maintainer adds on the reference side; hddm_b200/wfpt.py is that binding.
+ *
+ * Conventions
+ *   - all arithmetic is FP64; RTs are signed (negative = lower boundary, hddm/utils.py:15-37);
+ *   - parameter order is the reference's: v, sv, a, z, sz, t, st, then the numerics
+ *     err, n_st, n_sz, use_adaptive, simps_err, then p_outlier, w_outlier;
+ *   - every function returns an int status (HDDM_OK = 0); nothing throws across the ABI;
+ *     hddm_b200_last_error() describes the last non-zero status of the calling thread;
+ *   - "host" entry points take host pointers, copy to the current CUDA device, run the kernels
+ *     on the library's stream and block until the result is back in the caller's buffer;
+ *   - "_dev" entry points take device pointers and a cudaStream_t (as void*), enqueue only;
+ *   - there is NO CPU fallback: without a usable CUDA device every call returns HDDM_ERR_CUDA.
+ */
+#ifndef HDDM_B200_H
+#define HDDM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HDDM_OK 0
+#define HDDM_ERR_CUDA 1      /* CUDA runtime / no device: Python side raises RuntimeError        */
+#define HDDM_ERR_ARG 2       /* malformed argument (null pointer, negative size, depth > 24)      */
+#define HDDM_ERR_SUPPORT 3   /* parameters out of support: reference raises ValueError            */
+                             /*   (src/wfpt.pyx:395-398, src/cdfdif_wrapper.pyx:23-25)            */
+#define HDDM_ERR_RT_RANGE 4  /* max|x| >= 1/(2 w_outlier) with p_outlier > 0: AssertionError      */
+                             /*   (src/cdfdif_wrapper.pyx:20-21)                                  */
+
+#define HDDM_MAX_DEPTH 24    /* largest n_st / n_sz accepted when use_adaptive != 0              */
+
+/* ---- runtime ------------------------------------------------------------------------------ */
+int hddm_b200_version(void);
+const char *hddm_b200_last_error(void);
+/* Bind the calling process to CUDA device `device` (-1: keep the current one) and create the
+ * library stream.  Called lazily by every other entry point. */
+int hddm_b200_init(int device);
+int hddm_b200_device_count(int *count);
+int hddm_b200_synchronize(void);
+/* FP64 roofline denominator measured on this device: achieved FLOP/s (2 per FMA) of a
+ * register-resident dependent-FMA probe, and its duration in ms. */
+int hddm_b200_fp64_peak(int iters, double *flops, float *ms);
+
+/* ---- wfpt module (src/wfpt.pyx) ----------------------------------------------------------- */
+
+/* full_pdf, src/pdf.pxi:104-146 (cpdef, Python-visible).  out[0] = density. */
+int hddm_full_pdf(double x, double v, double sv, double a, double z, double sz, double t, double st,
+                  double err, int n_st, int n_sz, int use_adaptive, double simps_err, double *out);
+
+/* pdf_array, src/wfpt.pyx:32-48.  y[i] = full_pdf(x[i]) * (1-p_outlier) + w_outlier*p_outlier,
+ * log taken when logp == 1. */
+int hddm_pdf_array(const double *x, int64_t n, double v, double sv, double a, double z, double sz,
+                   double t, double st, double err, int logp, int n_st, int n_sz, int use_adaptive,
+                   double simps_err, double p_outlier, double w_outlier, double *y);
+
+/* wiener_like, src/wfpt.pyx:54-76.  logp[0] = sum of log mixed densities; -inf when any mixed
+ * density is exactly 0 or p_outlier is outside [0,1]; 0.0 for n == 0. */
+int hddm_wiener_like(const double *x, int64_t n, double v, double sv, double a, double z, double sz,
+                     double t, double st, double err, int n_st, int n_sz, int use_adaptive,
+                     double simps_err, double p_outlier, double w_outlier, double *logp);
+
+/* wiener_like_multi, src/wfpt.pyx:244-274.  par[k] / stride[k] for k = v, sv, a, z, sz, t, st:
+ * stride 0 broadcasts par[k][0], stride 1 reads one value per trial (the `multi` names).
+ * x == +999 / -999 are missing-response sentinels (prob_ub / 1 - prob_ub, no outlier mix);
+ * no zero-density guard (log(0) = -inf flows into the sum). */
+int hddm_wiener_like_multi(const double *x, int64_t n, const double *const par[7],
+                           const int64_t stride[7], double err, int n_st, int n_sz, int use_adaptive,
+                           double simps_err, double p_outlier, double w_outlier, double *logp);
+
+/* wiener_like_contaminant, src/wfpt.pyx:357-386.  cont_x is int32[n]. */
+int hddm_wiener_like_contaminant(const double *x, const int32_t *cont_x, int64_t n, double v,
+                                 double sv, double a, double z, double sz, double t, double st,
+                                 double t_min, double t_max, double err, int n_st, int n_sz,
+                                 int use_adaptive, double simps_err, double *logp);
+
+/* gen_cdf_using_pdf, src/wfpt.pyx:389-414, on the caller's grid xgrid = linspace(-time, time,
+ * 2N+1).  cdf[0] keeps the raw density, cdf[1:] = cumtrapz, all divided by cdf[m-1].
+ * HDDM_ERR_SUPPORT mirrors the reference's ValueError. */
+int hddm_gen_cdf_using_pdf(const double *xgrid, int64_t m, double v, double sv, double a, double z,
+                           double sz, double t, double st, double err, int n_st, int n_sz,
+                           int use_adaptive, double simps_err, double p_outlier, double w_outlier,
+                           double *cdf);
+
+/* gen_rts_from_cdf, src/wfpt.pyx:323-354, on the caller's grid xgrid = arange(lb, ub, dt) with the
+ * caller's uniforms: f[samples], and u_delay[samples] when st != 0 (the reference draws them from
+ * numpy's global RNG in that order).  table (optional, m doubles) receives the normalised table. */
+int hddm_gen_rts_from_cdf(const double *xgrid, int64_t m, double v, double sv, double a, double z,
+                          double sz, double t, double st, const double *f, const double *u_delay,
+                          int64_t samples, double *rts, double *table);
+
+/* ---- cdfdif_wrapper module (src/cdfdif_wrapper.pyx, src/cdfdif.c) -------------------------- */
+
+/* dmat_cdf_array, src/cdfdif_wrapper.pyx:16-52 -> cdfdif, src/cdfdif.c:59-221. */
+int hddm_dmat_cdf_array(const double *x, int64_t n, double v, double sv, double a, double z,
+                        double sz, double t, double st, double p_outlier, double w_outlier, double *y);
+
+/* ---- NEW: batched likelihood (no reference counterpart; north_star's batched entry point) --- */
+
+/* P parameter sets in one launch, each with wiener_like semantics (src/wfpt.pyx:54-76).
+ * params is SoA float64 [9][P]: rows v, sv, a, z, sz, t, st, p_outlier, w_outlier.
+ * seg == NULL: every set is evaluated against all n trials; otherwise seg is int64[P+1] and set p
+ * sees x[seg[p] .. seg[p+1]) (ragged: subjects x their own trials x many proposals).
+ * evals (optional) receives the number of pdf_sv evaluations the launch made. */
+int hddm_wiener_like_batch(const double *x, int64_t n, const int64_t *seg, const double *params,
+                           int64_t P, double err, int n_st, int n_sz, int use_adaptive,
+                           double simps_err, double *logp, unsigned long long *evals);
+
+/* Same with per-trial drift (regression layout): v is float64[P][n] (row p = set p), the other
+ * eight rows of params as above (row 0 of params is ignored).  wiener_like_multi semantics
+ * (src/wfpt.pyx:244-274) per set, against all n trials. */
+int hddm_wiener_like_multi_batch(const double *x, int64_t n, const double *v_trial,
+                                 const double *params, int64_t P, double err, int n_st, int n_sz,
+                                 int use_adaptive, double simps_err, double *logp,
+                                 unsigned long long *evals);
+
+/* ---- device-resident trials (one upload per observed node, reused every MCMC step) --------- */
+typedef struct hddm_trials hddm_trials; /* opaque */
+int hddm_trials_upload(const double *x, int64_t n, hddm_trials **out);
+int hddm_trials_free(hddm_trials *h);
+int hddm_trials_wiener_like(const hddm_trials *h, double v, double sv, double a, double z, double sz,
+                            double t, double st, double err, int n_st, int n_sz, int use_adaptive,
+                            double simps_err, double p_outlier, double w_outlier, double *logp);
+int hddm_trials_wiener_like_batch(const hddm_trials *h, const int64_t *seg, const double *params,
+                                  int64_t P, double err, int n_st, int n_sz, int use_adaptive,
+                                  double simps_err, double *logp, unsigned long long *evals);
+
+/* ---- device-pointer entry points (enqueue only; used under torch.distributed sharding) ----- */
+
+/* Elements (doubles) of scratch the batched launch needs for P sets whose longest segment has
+ * max_seg_len trials. */
+int64_t hddm_wiener_like_batch_scratch(int64_t max_seg_len, int64_t P);
+/* All pointers are device pointers; d_seg may be NULL; d_evals may be NULL (a device counter that
+ * is ADDED to).  stream is a cudaStream_t. */
+int hddm_wiener_like_batch_dev(const double *d_x, int64_t n, const int64_t *d_seg, int64_t max_seg_len,
+                               const double *d_params, int64_t P, double err, int n_st, int n_sz,
+                               int use_adaptive, double simps_err, double *d_logp, double *d_scratch,
+                               unsigned long long *d_evals, void *stream);
+int hddm_pdf_array_dev(const double *d_x, int64_t n, double v, double sv, double a, double z,
+                       double sz, double t, double st, double err, int logp, int n_st, int n_sz,
+                       int use_adaptive, double simps_err, double p_outlier, double w_outlier,
+                       double *d_y, unsigned long long *d_evals, void *stream);
+int hddm_dmat_cdf_array_dev(const double *d_x, int64_t n, double v, double sv, double a, double z,
+                            double sz, double t, double st, double p_outlier, double w_outlier,
+                            double *d_y, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HDDM_B200_H */

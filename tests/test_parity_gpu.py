@@ -1,0 +1,270 @@
+"""GPU parity tests: the CUDA path, called through the reference-shaped Python API -> C ABI,
+against (a) the committed golden fixtures produced by the compiled unmodified reference and the
+reference's own MATLAB vectors, and (b) the C oracle on the same seeded inputs.
+Tolerances (north_star): 1e-10 relative per-trial density / log-density, 1e-9 relative summed
+log-likelihood; exact class equality for 0, -inf, NaN."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from tests.util import (ATOL_LOG, RTOL_SUM, RTOL_TRIAL, assert_parity, draw_params, draw_rts,
+                        sweep_inputs)
+
+pytestmark = pytest.mark.gpu
+
+HDDM = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
+
+
+@pytest.fixture(scope="module")
+def W(gpu):
+    from hddm_b200 import wfpt
+    return wfpt
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import oracle
+    oracle.build()
+    return oracle
+
+
+def test_matlab_golden_vectors(W, golden_dir):
+    """hddm/tests/test_likelihoods.py:49-56 (test_pdf_no_matlab): 9 decimals vs Navarro&Fuss wfpt.m."""
+    vals = json.load(open(os.path.join(golden_dir, "matlab_wfpt.json")))["vals"]
+    assert len(vals) == 20
+    for r in vals:
+        got = W.full_pdf(-r["rt"], r["v"], 0, r["a"], r["z"], 0, r["t"], 0, r["err"], 0)
+        np.testing.assert_array_almost_equal(r["matlab_wfpt"], got, 9)
+
+
+def test_full_pdf_fixture(W, golden_dir):
+    """Every (sv,sz,st) quadrant x 7 numerics settings + the support/failure-mode zeros
+    (hddm/tests/test_likelihoods.py:225-262), outputs of the compiled reference."""
+    d = np.load(os.path.join(golden_dir, "ref_full_pdf.npz"))
+    rows, want = d["rows"], d["out"]
+    got = np.array([W.full_pdf(r[0], *r[1:8], r[8], int(r[9]), int(r[10]), int(r[11]), r[12]) for r in rows])
+    worst = assert_parity(got, want, RTOL_TRIAL, what="full_pdf fixture")
+    print("full_pdf fixture: %d cases, max rel err %.2e" % (len(want), worst))
+
+
+def test_likelihood_fixtures(W, golden_dir):
+    d = np.load(os.path.join(golden_dir, "ref_likelihoods.npz"))
+    for k in range(int(d["wl_n"])):
+        p = d["wl_p_%d" % k]
+        got = W.wiener_like(d["wl_x_%d" % k], *p[:7], p[7], int(p[8]), int(p[9]), int(p[10]), p[11], p[12], p[13])
+        assert_parity(got, d["wl_y_%d" % k], RTOL_SUM, what="wiener_like[%d]" % k)
+    # the reference's own -inf case (hddm/tests/test_likelihoods.py:97)
+    assert W.wiener_like(np.array([1., 2., 3., 0.]), 1, 0, 2, .5, 0, 0, 0, 1e-4) == -np.inf
+    assert float(d["wl_zero_rt"]) == -np.inf
+    for k in range(int(d["pa_n"])):
+        p = d["pa_p_%d" % k]
+        got = W.pdf_array(d["pa_x_%d" % k], *p[:7], p[7], int(p[8]), int(p[9]), int(p[10]), int(p[11]), p[12],
+                          p[13], p[14])
+        assert_parity(got, d["pa_y_%d" % k], RTOL_TRIAL, atol=ATOL_LOG if int(p[8]) else 0.0,
+                      what="pdf_array[%d]" % k)
+    names = ("v", "sv", "a", "z", "sz", "t", "st")
+    for k in range(int(d["wm_n"])):
+        cols, multi = d["wm_cols_%d" % k], [names[j] for j in d["wm_multi_%d" % k]]
+        args = [cols[:, j].copy() if names[j] in multi else cols[0, j] for j in range(7)]
+        got = W.wiener_like_multi(d["wm_x_%d" % k], *args, 1e-4, set(multi), 10, 10, 1, 1e-3, 0.05, 0.1)
+        assert_parity(got, d["wm_y_%d" % k], RTOL_SUM, what="wiener_like_multi[%d]" % k)
+    for k in range(int(d["wc_n"])):
+        got = W.wiener_like_contaminant(d["wc_x_%d" % k], d["wc_c_%d" % k], *d["wc_p_%d" % k], 0.1, 5.0, 1e-4,
+                                        10, 10, 1, 1e-6)
+        assert_parity(got, d["wc_y_%d" % k], RTOL_SUM, what="contaminant[%d]" % k)
+
+
+def test_cdf_fixtures(W, gpu, golden_dir):
+    from hddm_b200 import cdfdif_wrapper as CW
+    d = np.load(os.path.join(golden_dir, "ref_cdf.npz"))
+    for k in range(int(d["cd_n"])):
+        p = d["cd_p_%d" % k]
+        got = CW.dmat_cdf_array(d["cd_x_%d" % k], *p[:7], p[7], p[8])
+        # CDF values: 1e-10 relative, plus 1e-14 absolute for values that cancel to ~0
+        assert_parity(got, d["cd_y_%d" % k], RTOL_TRIAL, atol=1e-14, what="dmat_cdf_array[%d]" % k)
+    for j in range(int(d["gc_n"])):
+        x, c = W.gen_cdf_using_pdf(*d["gc_p_%d" % j], 1e-4, 500, 5., 2, 2, 1, 1e-3, 0.05, 0.1)
+        assert np.array_equal(x, d["gc_x_%d" % j])
+        assert_parity(c, d["gc_y_%d" % j], RTOL_TRIAL, what="gen_cdf_using_pdf[%d]" % j)
+        parts = W.split_cdf(x.copy(), c.copy())
+        for m, arr in enumerate(parts):
+            assert_parity(arr, d["gc_split%d_%d" % (m, j)], 1e-9, atol=1e-12, what="split_cdf")
+    for j in range(int(d["gr_n"])):
+        p = d["gr_p_%d" % j]
+        got = W.gen_rts_from_cdf(*p, 400, -4.0, 4.0, 1e-3, f=d["gr_f_%d" % j], u_delay=d["gr_u_%d" % j])
+        want = d["gr_y_%d" % j]
+        # the table lookup is discrete: a last-ulp difference in the normalised table can move a
+        # sample by one grid step (dt = 1e-3); require exact agreement on >= 99.5 % and <= 1 step elsewhere
+        close = np.abs(got - want) <= 1e-12
+        assert close.mean() >= 0.995, close.mean()
+        assert np.max(np.abs(got - want)) <= 1e-3 + 1e-12
+        # same global-RNG draw order as the reference (f first, then the delays)
+        np.random.seed(4242 + j)
+        again = W.gen_rts_from_cdf(*p, 400, -4.0, 4.0, 1e-3)
+        assert np.array_equal(again, got)
+
+
+def test_cdf_guards(gpu):
+    from hddm_b200 import cdfdif_wrapper as CW
+    x = np.array([0.5, -0.7, 6.0])
+    with pytest.raises(AssertionError):   # src/cdfdif_wrapper.pyx:20-21
+        CW.dmat_cdf_array(x, 1., .5, 2., .5, .2, .3, .1, 0.05, 0.1)
+    with pytest.raises(ValueError):       # :23-25
+        CW.dmat_cdf_array(x, 1., .5, 2., .95, .2, .3, .1, 0.0, 0.1)
+    with pytest.raises(ValueError):
+        CW.dmat_cdf_array(x, 1., .5, 0.0, .5, .2, .3, .1, 0.0, 0.1)
+
+
+@pytest.mark.parametrize("quadrant", range(8))
+def test_per_trial_vs_oracle(W, O, quadrant):
+    """>= 1e5 (trial, set) pairs per quadrant, both boundaries, onset-mixed RTs (sweep S-B)."""
+    rng = np.random.default_rng(9100 + quadrant)
+    T, P = 4000, 32
+    par = draw_params(rng, P, quadrant & 1, quadrant & 2, quadrant & 4)
+    x = draw_rts(rng, T, 0.30)
+    worst = 0.0
+    for p in range(P):
+        args = list(par[:, p])
+        want = O.pdf_array(x, *args, logp=1, p_outlier=0.05, w_outlier=0.1, **HDDM)
+        got = W.pdf_array(x, *args, logp=1, p_outlier=0.05, w_outlier=0.1, **HDDM)
+        worst = max(worst, assert_parity(got, want, RTOL_TRIAL, atol=ATOL_LOG, what="quadrant %d set %d" % (quadrant, p)))
+        want = O.pdf_array(x, *args, **HDDM)
+        got = W.pdf_array(x, *args, **HDDM)
+        worst = max(worst, assert_parity(got, want, RTOL_TRIAL, what="density quadrant %d set %d" % (quadrant, p)))
+    print("quadrant %d: max rel err %.2e" % (quadrant, worst))
+
+
+@pytest.mark.parametrize("numerics", [dict(err=1e-4, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-3),
+                                      dict(err=1e-4, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-8),
+                                      dict(err=1e-7, n_st=6, n_sz=4, use_adaptive=0, simps_err=0.0),
+                                      dict(err=1e-10, n_st=4, n_sz=4, use_adaptive=1, simps_err=1e-5)])
+def test_numerics_settings_vs_oracle(W, O, numerics):
+    rng = np.random.default_rng(9200)
+    T = 400 if numerics["simps_err"] == 1e-8 else 3000
+    par = draw_params(rng, 6)
+    x = draw_rts(rng, T, 0.30)
+    for p in range(6):
+        args = list(par[:, p])
+        assert_parity(W.pdf_array(x, *args, **numerics), O.pdf_array(x, *args, **numerics), RTOL_TRIAL,
+                      what="numerics %r" % numerics)
+
+
+@pytest.mark.parametrize("onset", [0.70, 0.30])
+def test_batch_vs_oracle_and_eval_count(W, O, onset):
+    """Batched entry point: summed parity 1e-9 AND identical pdf_sv evaluation counts (decision parity:
+    same series/recursion tree as the reference)."""
+    x, params = sweep_inputs(3000, 48, onset=onset)
+    got, evals = W.wiener_like_batch(x, params, return_evals=True, **HDDM)
+    O.pdfsv_calls(reset=True)
+    want = O.wiener_like_batch(x, params, **HDDM)
+    want_evals = O.pdfsv_calls(reset=True)
+    assert_parity(got, want, RTOL_SUM, what="batch onset %.2f" % onset)
+    assert evals == want_evals, (evals, want_evals)
+    # each set equals the scalar entry point bit for bit (same kernel, same order)
+    for p in (0, 17, 47):
+        one = W.wiener_like(x, *params[:7, p], p_outlier=params[7, p], w_outlier=params[8, p], **HDDM)
+        assert one == got[p]
+
+
+def test_batch_ragged_segments(W, O):
+    """20 subjects x ~200 trials x several proposals each (config C2 shape) in one launch."""
+    rng = np.random.default_rng(9300)
+    lens = rng.integers(150, 260, 20)
+    reps = 5
+    xs = [draw_rts(rng, int(n), 0.45) for n in lens]
+    x = np.concatenate([np.concatenate([xi] * 1) for xi in xs])
+    starts = np.concatenate([[0], np.cumsum(lens)])
+    par = draw_params(rng, 20 * reps)
+    params = np.concatenate([par, np.full((1, 20 * reps), 0.05), np.full((1, 20 * reps), 0.1)])
+    # proposals of the same subject share the subject's trials: segments may repeat, so lay the
+    # trials out once per proposal (seg must be ascending) -- the host API takes one flat x
+    xx = np.concatenate([xs[s] for s in range(20) for _ in range(reps)])
+    seg = np.concatenate([[0], np.cumsum([len(xs[s]) for s in range(20) for _ in range(reps)])])
+    got = W.wiener_like_batch(xx, params, seg=seg, **HDDM)
+    want = O.wiener_like_batch(xx, params, seg=seg, **HDDM)
+    assert_parity(got, want, RTOL_SUM, what="ragged batch")
+    assert x.size == starts[-1]
+
+
+def test_multi_batch_vs_oracle(W, O):
+    rng = np.random.default_rng(9400)
+    T, P = 1500, 8
+    x = draw_rts(rng, T, 0.75)
+    x[::97] = 999.0
+    x[5::131] = -999.0
+    par = draw_params(rng, P)
+    params = np.concatenate([par, np.full((1, P), 0.05), np.full((1, P), 0.1)])
+    v_trial = rng.uniform(-3, 3, (P, T))
+    got = W.wiener_like_multi_batch(x, v_trial, params)
+    want = np.array([O.wiener_like_multi(x, v_trial[p], *par[1:, p], 1e-4, multi=["v"], p_outlier=0.05, w_outlier=0.1)
+                     for p in range(P)])
+    assert_parity(got, want, RTOL_SUM, what="multi batch")
+
+
+def test_edge_cases(W, O):
+    args = (1., .5, 2., .5, .2, .3, .1)
+    assert W.wiener_like(np.empty(0), *args, 1e-4) == 0.0                       # empty -> 0.0
+    assert W.pdf_array(np.empty(0), *args).shape == (0,)
+    assert W.wiener_like(np.array([1.0, 2.0]), *args, 1e-4, p_outlier=1.5) == -np.inf   # src/wfpt.pyx:63-64
+    assert W.wiener_like(np.empty(0), *args, 1e-4, p_outlier=-0.1) == -np.inf
+    assert np.isnan(W.wiener_like(np.array([1.0, np.nan]), *args, 1e-4, **{k: HDDM[k] for k in ("n_st", "n_sz")}))
+    # zero density without / with the outlier floor
+    x = np.array([0.5, 0.2])
+    assert W.wiener_like(x, 1., 0., 2., .5, 0., .3, 0., 1e-4, p_outlier=0) == -np.inf
+    got = W.wiener_like(x, 1., 0., 2., .5, 0., .3, 0., 1e-4, p_outlier=.05, w_outlier=.1)
+    assert_parity(got, O.wiener_like(x, 1., 0., 2., .5, 0., .3, 0., 1e-4, p_outlier=.05, w_outlier=.1), RTOL_SUM)
+    # strided view == contiguous copy; wrong dtype / ndim / type rejected like the Cython buffer
+    big = draw_rts(np.random.default_rng(1), 600, 0.5)
+    assert W.wiener_like(big[::2], *args, 1e-4, **{k: HDDM[k] for k in ("n_st", "n_sz", "simps_err")}) == \
+        W.wiener_like(big[::2].copy(), *args, 1e-4, **{k: HDDM[k] for k in ("n_st", "n_sz", "simps_err")})
+    with pytest.raises(ValueError):
+        W.wiener_like(big.astype(np.float32), *args, 1e-4)
+    with pytest.raises(ValueError):
+        W.wiener_like(big.reshape(2, -1), *args, 1e-4)
+    with pytest.raises(TypeError):
+        W.wiener_like(list(big), *args, 1e-4)
+    with pytest.raises(ValueError):   # src/wfpt.pyx:395-398
+        W.gen_cdf_using_pdf(1., .5, 2., .95, .2, .3, .1, 1e-4)
+    # more than one 2048-trial chunk, non-multiple length
+    xl = draw_rts(np.random.default_rng(2), 5000, 0.5)
+    assert_parity(W.wiener_like(xl, *args, 1e-4, **{k: HDDM[k] for k in ("n_st", "n_sz", "simps_err")}),
+                  O.wiener_like(xl, *args, 1e-4, **{k: HDDM[k] for k in ("n_st", "n_sz", "simps_err")}), RTOL_SUM)
+
+
+def test_device_resident_trials(W, O):
+    x = draw_rts(np.random.default_rng(3), 777, 0.6)
+    tr = W.Trials(x)
+    args = (0.7, 1.1, 1.4, .45, .3, .35, .2)
+    a = tr.wiener_like(*args, 1e-4, 2, 2, 1, 1e-3, 0.05, 0.1)
+    b = W.wiener_like(x, *args, 1e-4, 2, 2, 1, 1e-3, 0.05, 0.1)
+    assert a == b
+    assert_parity(a, O.wiener_like(x, *args, 1e-4, 2, 2, 1, 1e-3, 0.05, 0.1), RTOL_SUM)
+    tr.close()
+
+
+def test_full_size_properties(W, O):
+    """BASELINE config C4 shape at a size the GPU finishes in seconds (T=1e5 x P=1024; the oracle
+    would need ~10 min), checked through size-independent properties: bit-reproducibility, invariance
+    to how sets are grouped into launches (what sharding over GPUs does), additivity over trial
+    segments, and oracle parity on a random subsample of sets."""
+    x, params = sweep_inputs(100000, 1024)
+    a, evals = W.wiener_like_batch(x, params, return_evals=True, **HDDM)
+    b = W.wiener_like_batch(x, params, **HDDM)
+    assert np.array_equal(a, b)                                  # deterministic
+    perm = np.random.default_rng(5).permutation(1024)
+    c = W.wiener_like_batch(x, np.ascontiguousarray(params[:, perm]), **HDDM)
+    assert np.array_equal(c, a[perm])                            # order / sharding of sets is irrelevant
+    halves = np.concatenate([W.wiener_like_batch(x, np.ascontiguousarray(params[:, :512]), **HDDM),
+                             W.wiener_like_batch(x, np.ascontiguousarray(params[:, 512:]), **HDDM)])
+    assert np.array_equal(halves, a)
+    # additivity: logp(all trials) == logp(first 40960) + logp(rest) to summation rounding
+    s1 = W.wiener_like_batch(x[:40960].copy(), params, **HDDM)
+    s2 = W.wiener_like_batch(x[40960:].copy(), params, **HDDM)
+    assert_parity(s1 + s2, a, 1e-12, what="additivity")
+    mean_evals = evals / (100000 * 1024)
+    assert 24.0 < mean_evals < 26.0, mean_evals                  # 24.9 on sweep S-A
+    for p in (3, 500, 1023):
+        want = O.wiener_like(x, *params[:7, p], p_outlier=0.05, w_outlier=0.1, **HDDM)
+        assert_parity(a[p], want, RTOL_SUM, what="subsample set %d" % p)

@@ -1,0 +1,59 @@
+"""Shared parity helpers.  Tolerances are the north_star's: 1e-10 relative per-trial (log-)density,
+1e-9 relative summed log-likelihood, FP64; 0 / +-inf / NaN must match as exact classes."""
+import numpy as np
+
+RTOL_TRIAL = 1e-10
+RTOL_SUM = 1e-9
+ATOL_LOG = 1e-13  # absolute floor for log-densities that happen to be ~0 (|log p| < 1e-3)
+
+
+def assert_parity(got, want, rtol, atol=0.0, what=""):
+    got = np.atleast_1d(np.asarray(got, dtype=np.float64))
+    want = np.atleast_1d(np.asarray(want, dtype=np.float64))
+    assert got.shape == want.shape, (what, got.shape, want.shape)
+    nan_g, nan_w = np.isnan(got), np.isnan(want)
+    assert np.array_equal(nan_g, nan_w), "%s: NaN classes differ at %s" % (what, np.where(nan_g != nan_w)[0][:10])
+    inf_w = np.isinf(want)
+    assert np.array_equal(got[inf_w], want[inf_w]), "%s: inf classes differ" % what
+    assert not np.isinf(got[~inf_w & ~nan_w]).any(), "%s: unexpected inf" % what
+    zero_w = want == 0
+    assert np.array_equal(got == 0, zero_w), "%s: exact-zero classes differ at %s" % (
+        what, np.where((got == 0) != zero_w)[0][:10])
+    m = ~(nan_w | inf_w | zero_w)
+    if m.any():
+        err = np.abs(got[m] - want[m])
+        lim = rtol * np.abs(want[m]) + atol
+        worst = np.argmax(err - lim)
+        assert (err <= lim).all(), "%s: max rel err %.3e (limit %.1e) at %d: got %r want %r" % (
+            what, np.max(err / np.abs(want[m])), rtol, np.where(m)[0][worst], got[m][worst], want[m][worst])
+    return float(np.max(np.abs(got[m] - want[m]) / np.abs(want[m]))) if m.any() else 0.0
+
+
+PNAMES = ("v", "sv", "a", "z", "sz", "t", "st")
+
+
+def draw_params(rng, n, sv_on=True, sz_on=True, st_on=True):
+    """Ranges of hddm/generate.py:38-46; draw order of SURVEY.md 8(d): sv, sz, st, z, v, t, a."""
+    sv = rng.uniform(0, 2.5, n) if sv_on else np.zeros(n)
+    sz = rng.uniform(0, 0.4, n) if sz_on else np.zeros(n)
+    st = rng.uniform(0, 0.35, n) if st_on else np.zeros(n)
+    z = rng.uniform(0.4, 0.6, n)
+    v = rng.uniform(-4, 4, n)
+    t = rng.uniform(0.2, 0.5, n)
+    a = rng.uniform(0.5, 2.0, n)
+    return np.stack([v, sv, a, z, sz, t, st], axis=0)  # [7, n]
+
+
+def draw_rts(rng, n, onset):
+    g = rng.gamma(2.0, 0.25, n)
+    sgn = np.where(rng.random(n) < 0.6, 1.0, -1.0)
+    return (onset + g) * sgn
+
+
+def sweep_inputs(T, P, onset=0.70, seed=20261104, p_outlier=0.05, w_outlier=0.1):
+    """The C4 sweep of SURVEY.md 8(d): S-A onset 0.70, S-B onset 0.30.  Returns x[T], params[9,P]."""
+    rng = np.random.default_rng(seed)
+    par7 = draw_params(rng, P)
+    x = draw_rts(rng, T, onset)
+    params = np.concatenate([par7, np.full((1, P), p_outlier), np.full((1, P), w_outlier)], axis=0)
+    return x, np.ascontiguousarray(params)
