@@ -36,6 +36,7 @@ HDDM = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
 P_OUT, W_OUT = 0.05, 0.1
 FLOP_PER_PDFSV = 300.0   # fixed accounting of the reference's operation sequence
 FLOP_PER_EVAL_TAIL = 28.0
+SETS_PER_CORE = 64       # CPU sample: 20000 trials x 64 sets per core ~ 8-10 s of work per core
 METRIC = "full-DDM wfpt log-density evals/sec (trial x param)"
 UNIT = "evals/s"
 
@@ -101,13 +102,14 @@ class CpuArm(object):
         self.sample = "first %d trials x first %d parameter sets of the workload, %d sets per process" % (
             self.x.size, self.sets, int(math.ceil(self.sets / self.cores)))
 
-    def step(self):
-        per = int(math.ceil(self.sets / self.cores))
-        jobs = [(self.kind, self.x, self.params, lo, min(lo + per, self.sets)) for lo in range(0, self.sets, per)]
+    def step(self, sets=None):
+        sets = self.sets if sets is None else min(sets, self.sets)
+        per = int(math.ceil(sets / self.cores))
+        jobs = [(self.kind, self.x, self.params, lo, min(lo + per, sets)) for lo in range(0, sets, per)]
         t0 = time.perf_counter()
         res = self.pool.map(_cpu_worker, jobs)
         wall = time.perf_counter() - t0
-        return wall, self.x.size * self.sets, res
+        return wall, self.x.size * sets, res
 
     def close(self):
         self.pool.close()
@@ -120,9 +122,9 @@ def run_reference(args):
         return 0
     onset = 0.70 if args.sweep == "A" else 0.30
     x, params = sweep_inputs(args.trials, args.sets, onset, 20261104)
-    arm = CpuArm(x, params, t_sample=min(args.trials, 20000), sets_per_core=2)
+    arm = CpuArm(x, params, t_sample=min(args.trials, 20000), sets_per_core=SETS_PER_CORE)
     for _ in range(max(args.warmup, 1)):
-        arm.step()
+        arm.step(sets=arm.cores)  # spins the worker processes up; one set each
     total_t, total_e = 0.0, 0
     for _ in range(args.steps):
         w, e, _ = arm.step()
@@ -295,8 +297,10 @@ def run_ours(args):
         achieved = alg_flop / (k_ms * 1e-3) / 1e12
         cpu = None
         try:
-            arm = CpuArm(x, params, t_sample=min(T, 20000), sets_per_core=2)
-            arm.step()
+            if args.no_cpu:
+                raise RuntimeError("skipped (--no-cpu)")
+            arm = CpuArm(x, params, t_sample=min(T, 20000), sets_per_core=SETS_PER_CORE)
+            arm.step(sets=arm.cores)
             w, e, res = arm.step()
             arm.close()
             cpu = {"value": e / w, "unit": UNIT, "cores": arm.cores, "kind": arm.kind, "sample": arm.sample}
@@ -335,6 +339,7 @@ def main():
     ap.add_argument("--trials", type=int, default=100000)
     ap.add_argument("--sets", type=int, default=10000)
     ap.add_argument("--sweep", default="A", choices=["A", "B"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -9,8 +9,8 @@ import os
 import numpy as np
 import pytest
 
-from tests.util import (ATOL_LOG, RTOL_SUM, RTOL_TRIAL, assert_parity, draw_params, draw_rts,
-                        sweep_inputs)
+from tests.util import (ATOL_LOG, RTOL_SUM, RTOL_TRIAL, assert_parity, cdf_noise_band, draw_params,
+                        draw_rts, sweep_inputs)
 
 pytestmark = pytest.mark.gpu
 
@@ -76,14 +76,24 @@ def test_likelihood_fixtures(W, golden_dir):
         assert_parity(got, d["wc_y_%d" % k], RTOL_SUM, what="contaminant[%d]" % k)
 
 
-def test_cdf_fixtures(W, gpu, golden_dir):
+def test_cdf_fixtures(W, O, gpu, golden_dir):
     from hddm_b200 import cdfdif_wrapper as CW
     d = np.load(os.path.join(golden_dir, "ref_cdf.npz"))
     for k in range(int(d["cd_n"])):
         p = d["cd_p_%d" % k]
-        got = CW.dmat_cdf_array(d["cd_x_%d" % k], *p[:7], p[7], p[8])
-        # CDF values: 1e-10 relative, plus 1e-14 absolute for values that cancel to ~0
-        assert_parity(got, d["cd_y_%d" % k], RTOL_TRIAL, atol=1e-14, what="dmat_cdf_array[%d]" % k)
+        x, want = d["cd_x_%d" % k], d["cd_y_%d" % k]
+        got = CW.dmat_cdf_array(x, *p[:7], p[7], p[8])
+        assert np.array_equal(O.dmat_cdf_array(x, *p[:7], p[7], p[8]), want)   # oracle == reference, bit for bit
+        # 1e-10 relative, widened only where the REFERENCE's own result is ill-conditioned (its change
+        # under a 1-ulp parameter change, see cdf_noise_band): sz/st -> 1e-10 epsilon configurations.
+        band = cdf_noise_band(O, x, p[:7], p[7], p[8])
+        err = np.abs(got - want)
+        lim = RTOL_TRIAL * np.abs(want) + 1e-14 + 64 * band
+        assert (err <= lim).all(), "dmat_cdf_array[%d]: err %r lim %r" % (k, err[err > lim], lim[err > lim])
+        if p[4] >= 1e-2 and p[6] >= 1e-2:   # full DDM: the plain 1e-10 bar must hold by itself
+            assert_parity(got, want, RTOL_TRIAL, atol=1e-14, what="dmat_cdf_array[%d]" % k)
+        print("cdf case %d (sz=%.3g st=%.3g): max rel err %.2e, reference noise band %.2e" % (
+            k, p[4], p[6], np.max(err / np.abs(want)), np.max(band / np.abs(want))))
     for j in range(int(d["gc_n"])):
         x, c = W.gen_cdf_using_pdf(*d["gc_p_%d" % j], 1e-4, 500, 5., 2, 2, 1, 1e-3, 0.05, 0.1)
         assert np.array_equal(x, d["gc_x_%d" % j])

@@ -57,3 +57,22 @@ def sweep_inputs(T, P, onset=0.70, seed=20261104, p_outlier=0.05, w_outlier=0.1)
     x = draw_rts(rng, T, onset)
     params = np.concatenate([par7, np.full((1, P), p_outlier), np.full((1, P), w_outlier)], axis=0)
     return x, np.ascontiguousarray(params)
+
+
+def cdf_noise_band(O, x, p, po, wo):
+    """Conditioning of the reference's own dmat_cdf_array at these inputs: the largest change of its
+    output under a ONE-ulp change of v, a, z or t.  With sz or st below ~1e-3 the wrapper substitutes
+    1e-10 epsilons (src/cdfdif_wrapper.pyx:36-42) and cdfdif differences series evaluated 1e-10 apart
+    (src/cdfdif.c:135-140,148), so the reference result itself is only defined to ~1e-7 relative there;
+    for the full DDM (sz, st >= 1e-2) the band is ~1e-14 and the 1e-10 bar is the binding one."""
+    y0 = O.dmat_cdf_array(x, *p, po, wo)
+    band = np.zeros_like(y0)
+    for j in (0, 2, 3, 5):
+        for s in (1.0, -1.0):
+            q = np.array(p, dtype=np.float64)
+            q[j] = np.nextafter(q[j], q[j] + s)
+            try:
+                band = np.maximum(band, np.abs(O.dmat_cdf_array(x, *q, po, wo) - y0))
+            except ValueError:
+                pass
+    return band
