@@ -31,6 +31,8 @@ SIGNATURES = {
     "hddm_b200_device_count": (_i, [C.POINTER(_i)]),
     "hddm_b200_synchronize": (_i, []),
     "hddm_b200_fp64_peak": (_i, [_i, c_dp, C.POINTER(C.c_float)]),
+    "hddm_b200_set_kernel": (_i, [_i]),
+    "hddm_series_table": (_i, [_d, c_dp, c_ip, C.POINTER(_i)]),
     "hddm_full_pdf": (_i, [_d] * 8 + _NUM + [c_dp]),
     "hddm_pdf_array": (_i, [c_dp, _l] + [_d] * 7 + [_d, _i, _i, _i, _i, _d, _d, _d, c_dp]),
     "hddm_wiener_like": (_i, [c_dp, _l] + [_d] * 7 + _NUM + [_d, _d, c_dp]),

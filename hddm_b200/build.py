@@ -14,11 +14,11 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
 LIB = os.path.join(HERE, "libhddm_b200.so")
-SOURCES = ["abi.cu", "wfpt_kernels.cu", "cdfdif_kernels.cu", "gen_kernels.cu"]
-HEADERS = ["kernels.cuh", "wfpt_device.cuh", os.path.join(ROOT, "include", "hddm_b200.h")]
+SOURCES = ["abi.cu", "wfpt_kernels.cu", "cdfdif_kernels.cu", "gen_kernels.cu", "series_table.cu"]
+HEADERS = ["kernels.cuh", "wfpt_device.cuh", "wfpt_fast.cuh", os.path.join(ROOT, "include", "hddm_b200.h")]
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
-              "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]
+              "-Xcompiler", "-fPIC", "-shared", "-cudart", "static", "--threads", "0"]
 
 
 def _nvcc():

@@ -304,6 +304,24 @@ int hddm_b200_fp64_peak(int iters, double* flops, float* ms)
     return *flops > 0 ? HDDM_OK : fail(HDDM_ERR_CUDA, "fp64 probe failed");
 }
 
+int hddm_b200_set_kernel(int which)
+{
+    if (which != 0 && which != 1) return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto) or 1 (generic)");
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    g_kernel_choice = which;
+    return HDDM_OK;
+}
+
+int hddm_series_table(double err, double* thr, int* code, int* n_thr)
+{
+    if (!thr || !code || !n_thr) return fail(HDDM_ERR_ARG, "series_table: null output");
+    const SeriesTable& t = series_table_for(err);
+    *n_thr = t.n_thr;
+    for (int i = 0; i < t.n_thr; ++i) thr[i] = t.thr[i];
+    for (int i = 0; i <= t.n_thr; ++i) code[i] = t.code[i];
+    return HDDM_OK;
+}
+
 /* ---- wfpt module --------------------------------------------------------------------------- */
 
 int hddm_pdf_array(const double* x, int64_t n, double v, double sv, double a, double z, double sz,

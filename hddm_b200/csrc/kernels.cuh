@@ -16,6 +16,25 @@ struct Numerics {
     int use_adaptive;
 };
 
+// Navarro-Fuss series selection as a function of normalised time tt for ONE value of err
+// (src/pdf.pxi:36-54,60).  The reference recomputes two logs and four square roots per pdf_sv
+// call only to arrive at a (branch, K) pair that is piecewise constant in tt; the host finds the
+// break points once per err by evaluating the reference's own formulas (series_table.cu) and
+// the kernels look the pair up: region r = #{i : tt >= thr[i]}, code[r] = +K (small-time
+// series, K terms) or -K (large-time series, K terms).  n_thr < 0: no table (too many regions
+// or K out of range) and the device evaluates the formulas directly.
+constexpr int kMaxRegions = 32;
+struct SeriesTable {
+    double thr[kMaxRegions - 1];
+    short code[kMaxRegions];
+    int n_thr;
+    int max_small_k;  // largest K of any small-time region
+    int max_large_k;  // largest K of any large-time region
+    double err;
+};
+// Host: cached per err; thread-safe.
+const SeriesTable& series_table_for(double err);
+
 // Parameter order used everywhere: v, sv, a, z, sz, t, st, p_outlier, w_outlier.
 constexpr int kNumPar = 9;
 constexpr int kTrialsPerBlock = 2048;  // one CTA reduces this many trials of one parameter set
@@ -45,12 +64,14 @@ struct LikeArgs {
     int chunks;  // ceil(max segment length / kTrialsPerBlock)
     int mode;
     Numerics nm;
+    SeriesTable tab;
     double* partial;             // [n_sets * chunks]
     double* logp;                // [n_sets]
     unsigned long long* evals;   // device counter of pdf_sv evaluations (may be nullptr)
 };
 
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream);
+extern int g_kernel_choice;  // 0 auto, 1 generic evaluator only
 
 struct PdfArgs {
     const double* x;
@@ -59,6 +80,7 @@ struct PdfArgs {
     double par[kNumPar];
     int logp;
     Numerics nm;
+    SeriesTable tab;
     unsigned long long* evals;
 };
 cudaError_t launch_pdf_array(const PdfArgs& a, cudaStream_t stream);

@@ -24,6 +24,7 @@ constexpr double kPiSq = 9.869604401089358;  // pow(M_PI, 2.0) in double
 struct Core {
     double v, sv, a, a_sq, err;
     double sv_sq, v_sq;
+    const SeriesTable* tab;    // shared-memory copy of the launch's table
     unsigned long long evals;  // pdf_sv evaluations made (the reference's unit of work)
 };
 
@@ -35,9 +36,19 @@ struct Series {
     bool small_time;
 };
 
-__device__ __forceinline__ Series select_series(double tt, double err)
+// (branch, K) from the host-built table: +K small-time, <= 0 large-time with -code terms.
+__device__ __forceinline__ int series_code(const SeriesTable& T, double tt)
 {
-    Series s;
+    int code = T.code[0];
+    for (int i = 0; i < T.n_thr; ++i)
+        if (tt >= T.thr[i]) code = T.code[i + 1];
+    return code;
+}
+
+// The reference's formulas evaluated on the device: only when the host could not build a table
+// for this err (more than kMaxRegions regions, K out of range, non-finite err).
+__device__ __noinline__ int series_code_direct(double tt, double err)
+{
     double kl, ks;
     const double root_tt = sqrt(tt);
     const double kl_floor = 1. / (kPi * root_tt);
@@ -56,17 +67,25 @@ __device__ __forceinline__ Series select_series(double tt, double err)
     } else {  // :46-47
         ks = 2.0;
     }
-    if (ks < kl) {  // :51-54
-        const int K = (int)ceil(ks);
+    if (ks < kl) return (int)ceil(ks);  // :51-52
+    return -(int)ceil(kl);              // :59-60
+}
+
+__device__ __forceinline__ Series select_series(double tt, const Core& c)
+{
+    Series s;
+    const int code = c.tab->n_thr >= 0 ? series_code(*c.tab, tt) : series_code_direct(tt, c.err);
+    if (code > 0) {  // src/pdf.pxi:51-54
+        const int K = code;
         s.small_time = true;
-        s.k_lo = (int)(-floor((K - 1) / 2.));
-        s.k_hi = (int)ceil((K - 1) / 2.);
+        s.k_lo = -((K - 1) / 2);  // -floor((K-1)/2.)
+        s.k_hi = K / 2;           // ceil((K-1)/2.)
         s.arg_scale = 0.5 / tt;
         s.out_scale = 1.0 / sqrt((2.0 * kPi) * (tt * tt * tt));
     } else {  // :59-60
         s.small_time = false;
         s.k_lo = 1;
-        s.k_hi = (int)ceil(kl);
+        s.k_hi = -code;
         s.arg_scale = -kPiSq * tt / 2.0;
         s.out_scale = kPi;
     }
@@ -105,7 +124,7 @@ __device__ __forceinline__ NodeCtx make_node(const Core& c, double x_t)
     NodeCtx n;
     n.live = !(x_t <= 0.0);  // NaN falls through as in the reference (x<=0 is false for NaN)
     if (n.live) {
-        n.ser = select_series(x_t / c.a_sq, c.err);
+        n.ser = select_series(x_t / c.a_sq, c);
         n.vx = c.v_sq * x_t;
         if (c.sv == 0.0) {
             n.inv_den = 0.0;
@@ -211,7 +230,7 @@ __device__ __forceinline__ double fixed_simpson(F&& f, double lo, double hi, int
 // st/sz < 1e-3 -> 0, then the four-way dispatch.  `evals` returns the number of pdf_sv calls.
 static __device__ __noinline__ double full_pdf(double x, double v, double sv, double a, double z, double sz,
                                         double t, double st, const Numerics& nm,
-                                        unsigned long long& evals)
+                                        const SeriesTable* tab, unsigned long long& evals)
 {
     if ((z < 0) || (z > 1) || (a < 0) || (t < 0) || (st < 0) || (sv < 0) || (sz < 0) || (sz > 1) ||
         ((fabs(x) - (t - st / 2.)) < 0) || (z + sz / 2. > 1) || (z - sz / 2. < 0) || (t - st / 2. < 0))
@@ -226,7 +245,7 @@ static __device__ __noinline__ double full_pdf(double x, double v, double sv, do
 
     Core c;
     c.v = v; c.sv = sv; c.a = a; c.a_sq = a * a; c.err = nm.err;
-    c.sv_sq = sv * sv; c.v_sq = v * v; c.evals = 0;
+    c.sv_sq = sv * sv; c.v_sq = v * v; c.tab = tab; c.evals = 0;
     double out;
 
     if (sz == 0 && st == 0) {  // :129

@@ -11,8 +11,11 @@
 // of how sets are sharded over GPUs.
 #include "kernels.cuh"
 #include "wfpt_device.cuh"
+#include "wfpt_fast.cuh"
 
 namespace hddm {
+
+int g_kernel_choice = 0;  // 0: pick per launch; 1: always the generic evaluator (tests, A/B runs)
 
 __device__ __forceinline__ double warp_sum(double v)
 {
@@ -33,8 +36,14 @@ __device__ __forceinline__ double load_par(const LikeArgs& a, int k, int64_t p, 
     return __ldg(a.par[k] + p * a.set_stride[k] + i * a.trial_stride[k]);
 }
 
-__global__ void __launch_bounds__(kLikeThreads) k_like_partial(const LikeArgs a)
+// KMAX > 0: the table-driven evaluator of wfpt_fast.cuh (z, sz uniform per set, adaptive
+// integration, large-time series of at most KMAX terms).  KMAX == 0: the generic evaluator of
+// wfpt_device.cuh (any per-trial parameter, fixed-grid Simpson, no table).
+template <int KMAX>
+__global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
+    k_like_partial(const __grid_constant__ LikeArgs a)
 {
+    __shared__ WTable<(KMAX > 0 ? KMAX : 1)> wt[2];
     const int64_t p = blockIdx.x;
     const int chunk = blockIdx.y;
     const int64_t lo = a.seg ? a.seg[p] : 0;
@@ -58,6 +67,15 @@ __global__ void __launch_bounds__(kLikeThreads) k_like_partial(const LikeArgs a)
         per_trial |= a.trial_stride[k] != 0;
     }
 
+    if (KMAX > 0) build_wtables<(KMAX > 0 ? KMAX : 1)>(wt, par[3], par[4]);
+
+    auto density = [&](double x, unsigned long long& ev) {
+        if (KMAX > 0)
+            return full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(x, par[0], par[1], par[2], par[3], par[4], par[5],
+                                                        par[6], a.nm, &a.tab, wt, ev);
+        return full_pdf(x, par[0], par[1], par[2], par[3], par[4], par[5], par[6], a.nm, &a.tab, ev);
+    };
+
     double acc = 0.0;
     unsigned long long evals = 0;
     bool hit_zero = false;
@@ -71,7 +89,7 @@ __global__ void __launch_bounds__(kLikeThreads) k_like_partial(const LikeArgs a)
         double d;
         if (a.mode == kModeMulti) {
             if (fabs(x) != 999.) {  // src/wfpt.pyx:261-266
-                d = full_pdf(x, par[0], par[1], par[2], par[3], par[4], par[5], par[6], a.nm, evals);
+                d = density(x, evals);
                 d = d * (1 - p_out) + w_out * p_out;
             } else if (x == 999.) {  // :267-268
                 d = prob_ub(par[0], par[2], par[3]);
@@ -81,7 +99,7 @@ __global__ void __launch_bounds__(kLikeThreads) k_like_partial(const LikeArgs a)
             acc += log(d);
         } else {
             if (a.mode == kModeContaminant && a.cont[i] != 0) continue;  // src/wfpt.pyx:374
-            d = full_pdf(x, par[0], par[1], par[2], par[3], par[4], par[5], par[6], a.nm, evals);
+            d = density(x, evals);
             d = d * (1 - p_out) + w_out * p_out;  // src/wfpt.pyx:70 (contaminant: p_out = 0)
             hit_zero |= (d == 0);                 // :71-72, :377-379
             acc += log(d);
@@ -130,21 +148,40 @@ __global__ void __launch_bounds__(128) k_like_final(const LikeArgs a)
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
 {
     if (a.n_sets <= 0) return cudaSuccess;
+    LikeArgs b = a;
+    b.tab = series_table_for(a.nm.err);
     dim3 grid((unsigned)a.n_sets, (unsigned)a.chunks);
-    k_like_partial<<<grid, kLikeThreads, 0, stream>>>(a);
+    // z (3) and sz (4) must be uniform per set for the shared start-point tables
+    const bool fast = g_kernel_choice != 1 && a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 &&
+                      b.tab.max_large_k <= 8 && a.trial_stride[3] == 0 && a.trial_stride[4] == 0;
+    if (fast && b.tab.max_large_k <= 4)
+        k_like_partial<4><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (fast)
+        k_like_partial<8><<<grid, kLikeThreads, 0, stream>>>(b);
+    else
+        k_like_partial<0><<<grid, kLikeThreads, 0, stream>>>(b);
     const int sets_per_block = 128 / 32;
-    k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(a);
+    k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(b);
     return cudaGetLastError();
 }
 
 // pdf_array (src/wfpt.pyx:32-48): per-trial density, outlier mix, optional log.
-__global__ void __launch_bounds__(kLikeThreads) k_pdf_array(const PdfArgs a)
+template <int KMAX>
+__global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
+    k_pdf_array(const __grid_constant__ PdfArgs a)
 {
+    __shared__ WTable<(KMAX > 0 ? KMAX : 1)> wt[2];
+    if (KMAX > 0) build_wtables<(KMAX > 0 ? KMAX : 1)>(wt, a.par[3], a.par[4]);
     unsigned long long evals = 0;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
-        double d = full_pdf(__ldg(a.x + i), a.par[0], a.par[1], a.par[2], a.par[3], a.par[4],
-                            a.par[5], a.par[6], a.nm, evals);
+        double d;
+        if (KMAX > 0)
+            d = full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(__ldg(a.x + i), a.par[0], a.par[1], a.par[2], a.par[3],
+                                                     a.par[4], a.par[5], a.par[6], a.nm, &a.tab, wt, evals);
+        else
+            d = full_pdf(__ldg(a.x + i), a.par[0], a.par[1], a.par[2], a.par[3], a.par[4], a.par[5],
+                         a.par[6], a.nm, &a.tab, evals);
         d = d * (1 - a.par[7]) + (a.par[8] * a.par[7]);
         a.y[i] = a.logp == 1 ? log(d) : d;
     }
@@ -159,7 +196,16 @@ cudaError_t launch_pdf_array(const PdfArgs& a, cudaStream_t stream)
     if (a.n <= 0) return cudaSuccess;
     int64_t blocks = (a.n + kLikeThreads - 1) / kLikeThreads;
     if (blocks > 148 * 64) blocks = 148 * 64;
-    k_pdf_array<<<(unsigned)blocks, kLikeThreads, 0, stream>>>(a);
+    PdfArgs b = a;
+    b.tab = series_table_for(a.nm.err);
+    const bool fast = g_kernel_choice != 1 && a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 &&
+                      b.tab.max_large_k <= 8;
+    if (fast && b.tab.max_large_k <= 4)
+        k_pdf_array<4><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+    else if (fast)
+        k_pdf_array<8><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+    else
+        k_pdf_array<0><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
     return cudaGetLastError();
 }
 

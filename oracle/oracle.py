@@ -35,6 +35,8 @@ def lib():
         d, i, l = C.c_double, C.c_int, C.c_int64
         L.wo_ftt_01w.restype = d
         L.wo_ftt_01w.argtypes = [d, d, d]
+        L.wo_series_code.restype = i
+        L.wo_series_code.argtypes = [d, d]
         L.wo_prob_ub.restype = d
         L.wo_prob_ub.argtypes = [d, d, d]
         L.wo_pdf_sv.restype = d
@@ -81,6 +83,10 @@ def _p(a):
 
 def ftt_01w(tt, w, err):
     return lib().wo_ftt_01w(tt, w, err)
+
+
+def series_code(tt, err):
+    return lib().wo_series_code(tt, err)
 
 
 def prob_ub(v, a, z):

@@ -81,6 +81,28 @@ double wo_ftt_01w(double tt, double w, double err)
     return dens;
 }
 
+/* src/pdf.pxi:36-54,60  the (branch, K) decision of ftt_01w alone: +K small-time series with K
+ * terms, -K large-time series with K terms (0: large-time, empty sum).  Same expressions as
+ * wo_ftt_01w above; exists so tests can check the CUDA path's host-built selection table. */
+int wo_series_code(double tt, double err)
+{
+    double kl, ks;
+    if (M_PI * tt * err < 1.0) {
+        kl = sqrt(-2.0 * log(M_PI * tt * err) / (pow(M_PI, 2.0) * tt));
+        kl = dmax(kl, 1. / (M_PI * sqrt(tt)));
+    } else {
+        kl = 1. / (M_PI * sqrt(tt));
+    }
+    if (2.0 * sqrt(2.0 * M_PI * tt) * err < 1.0) {
+        ks = 2.0 + sqrt(-2.0 * tt * log(2.0 * sqrt(2.0 * M_PI * tt) * err));
+        ks = dmax(ks, sqrt(tt) + 1.0);
+    } else {
+        ks = 2.0;
+    }
+    if (ks < kl) return (int)ceil(ks);
+    return -(int)ceil(kl);
+}
+
 /* src/pdf.pxi:67-72  prob_ub -- probability of absorbing at the upper boundary */
 double wo_prob_ub(double v, double a, double z)
 {

@@ -23,6 +23,16 @@ def W(gpu):
     return wfpt
 
 
+@pytest.fixture(autouse=True, params=["auto", "generic"])
+def evaluator(request, gpu):
+    """Every parity test runs twice: with the per-launch choice (table-driven evaluator of
+    csrc/wfpt_fast.cuh where it applies) and with the generic evaluator forced.  Both are CUDA."""
+    from hddm_b200 import _lib
+    _lib.check(_lib.lib().hddm_b200_set_kernel(1 if request.param == "generic" else 0))
+    yield request.param
+    _lib.check(_lib.lib().hddm_b200_set_kernel(0))
+
+
 @pytest.fixture(scope="module")
 def O():
     from oracle import oracle
@@ -211,6 +221,37 @@ def test_multi_batch_vs_oracle(W, O):
     want = np.array([O.wiener_like_multi(x, v_trial[p], *par[1:, p], 1e-4, multi=["v"], p_outlier=0.05, w_outlier=0.1)
                      for p in range(P)])
     assert_parity(got, want, RTOL_SUM, what="multi batch")
+
+
+@pytest.mark.parametrize("multi", [("v", "t"), ("a", "sv", "st"), ("z",), ("sz", "v"), ("v", "sv", "a", "z", "sz", "t", "st")])
+def test_multi_per_trial_parameters(W, O, multi):
+    """wiener_like_multi with any subset of parameters per trial (src/wfpt.pyx:256-260); z or sz per
+    trial takes the generic evaluator, everything else the table-driven one."""
+    rng = np.random.default_rng(9500 + len(multi))
+    T = 1200
+    x = draw_rts(rng, T, 0.55)
+    x[::53] = 999.0
+    x[7::61] = -999.0
+    base = dict(zip(("v", "sv", "a", "z", "sz", "t", "st"), draw_params(rng, 1)[:, 0]))
+    lo_hi = dict(v=(-4, 4), sv=(0, 2.5), a=(0.5, 2.0), z=(0.4, 0.6), sz=(0, 0.4), t=(0.2, 0.5), st=(0, 0.35))
+    vals = dict(base)
+    for name in multi:
+        vals[name] = rng.uniform(*lo_hi[name], T)
+    args = [vals[k] for k in ("v", "sv", "a", "z", "sz", "t", "st")]
+    for nm in (dict(n_st=2, n_sz=2, simps_err=1e-3), dict(n_st=10, n_sz=10, simps_err=1e-3)):
+        got = W.wiener_like_multi(x, *args, 1e-4, multi=list(multi), p_outlier=0.05, w_outlier=0.1, **nm)
+        want = O.wiener_like_multi(x, *args, 1e-4, multi=list(multi), p_outlier=0.05, w_outlier=0.1, **nm)
+        assert_parity(got, want, RTOL_SUM, what="multi %r" % (multi,))
+
+
+def test_small_sz_st_thresholds(W, O):
+    """sz, st just below / above the 1e-3 cut of src/pdf.pxi:122-125, and z at the support edge."""
+    x = draw_rts(np.random.default_rng(9600), 2000, 0.4)
+    for sz, st in ((0.0009999, 0.2), (0.001, 0.2), (0.2, 0.0009999), (0.2, 0.001), (0.0005, 0.0005), (0.001, 0.001)):
+        for z in (0.5, 0.1 + sz / 2, 1 - sz / 2):
+            args = (1.3, 0.9, 1.2, z, sz, 0.3, st)
+            assert_parity(W.pdf_array(x, *args, **HDDM), O.pdf_array(x, *args, **HDDM), RTOL_TRIAL,
+                          what="sz=%g st=%g z=%g" % (sz, st, z))
 
 
 def test_edge_cases(W, O):
