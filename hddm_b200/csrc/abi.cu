@@ -306,7 +306,7 @@ int hddm_b200_fp64_peak(int iters, double* flops, float* ms)
 
 int hddm_b200_set_kernel(int which)
 {
-    if (which != 0 && which != 1) return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto) or 1 (generic)");
+    if (which < 0 || which > 2) return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto), 1 (generic) or 2 (no grid)");
     std::lock_guard<std::mutex> lock(g_rt.mu);
     g_kernel_choice = which;
     return HDDM_OK;

@@ -1,0 +1,413 @@
+// wfpt_grid.cuh -- v3 evaluator of full_pdf for the headline case: every parameter except the drift
+// is uniform over the CTA's parameter set and integration is adaptive.
+//
+// The reference's recursion (src/integrate.pxi:114-206) always evaluates its first level: 5 decision
+// times t' (lb, ub, c, d, e of the outer Simpson rule) x 5 start points w, and its stop tests almost
+// always accept that level (mean 24.9 pdf_sv per eval).  This file makes that 5 x 5
+// grid cheap; everything deeper, and every trial outside the "comfortable" range defined below, goes
+// through the v2 walk of wfpt_fast.cuh unchanged.
+//
+// Per parameter set (GridSet, shared memory, built once per CTA):
+//   * start-point tables of wfpt_fast.cuh (abscissae by the reference's midpoint recursion, sin(k pi w));
+//   * the five first-level decision-time offsets tn[j] (same midpoint recursion, src/integrate.pxi:153-155,
+//     :187-198) and rho[j] = exp(pi^2 (tn[j]-tn[0]) / (2 a^2)): the large-time q = exp(-pi^2 tt/2) of
+//     node j is q_0 * rho[j], one exp per trial instead of five;
+//   * the break points of the (branch, K) decision mapped from normalised time to decision time:
+//     xthr[i] = the smallest double X with fl(X / a^2) >= thr[i], so `x_t >= xthr[i]` (an integer
+//     compare of bit patterns, off the FP64 pipe) decides exactly as the reference's tt = x/a^2 does;
+//   * S w_i^2 and 2 a w_i of the sv-marginal exponent at the five start points.
+// Per (time node, start point): K FMAs (large-time) or K table-driven exps (small-time), one
+// table-driven exp for the sv marginal.  exp is a branch-free 64-entry-table / degree-5 evaluation
+// (10 FP64 instructions, < 1 ulp + 2e-17) -- the libdevice exp was the dominant cost of v2.
+// DECISIONS (support test, branch, K, every Simpson stop test) remain the reference's.
+#pragma once
+#include "wfpt_fast.cuh"
+
+namespace hddm {
+
+constexpr int kExpTab = 64;
+constexpr int kThrWin = 8;  // thresholds of the series decision that can fall inside the comfortable range
+
+// 2^(i/64), correctly rounded.
+__device__ const double g_exp2_tab[kExpTab] = {
+    0x1.0000000000000p+0, 0x1.02c9a3e778061p+0, 0x1.059b0d3158574p+0, 0x1.0874518759bc8p+0,
+    0x1.0b5586cf9890fp+0, 0x1.0e3ec32d3d1a2p+0, 0x1.11301d0125b51p+0, 0x1.1429aaea92de0p+0,
+    0x1.172b83c7d517bp+0, 0x1.1a35beb6fcb75p+0, 0x1.1d4873168b9aap+0, 0x1.2063b88628cd6p+0,
+    0x1.2387a6e756238p+0, 0x1.26b4565e27cddp+0, 0x1.29e9df51fdee1p+0, 0x1.2d285a6e4030bp+0,
+    0x1.306fe0a31b715p+0, 0x1.33c08b26416ffp+0, 0x1.371a7373aa9cbp+0, 0x1.3a7db34e59ff7p+0,
+    0x1.3dea64c123422p+0, 0x1.4160a21f72e2ap+0, 0x1.44e086061892dp+0, 0x1.486a2b5c13cd0p+0,
+    0x1.4bfdad5362a27p+0, 0x1.4f9b2769d2ca7p+0, 0x1.5342b569d4f82p+0, 0x1.56f4736b527dap+0,
+    0x1.5ab07dd485429p+0, 0x1.5e76f15ad2148p+0, 0x1.6247eb03a5585p+0, 0x1.6623882552225p+0,
+    0x1.6a09e667f3bcdp+0, 0x1.6dfb23c651a2fp+0, 0x1.71f75e8ec5f74p+0, 0x1.75feb564267c9p+0,
+    0x1.7a11473eb0187p+0, 0x1.7e2f336cf4e62p+0, 0x1.82589994cce13p+0, 0x1.868d99b4492edp+0,
+    0x1.8ace5422aa0dbp+0, 0x1.8f1ae99157736p+0, 0x1.93737b0cdc5e5p+0, 0x1.97d829fde4e50p+0,
+    0x1.9c49182a3f090p+0, 0x1.a0c667b5de565p+0, 0x1.a5503b23e255dp+0, 0x1.a9e6b5579fdbfp+0,
+    0x1.ae89f995ad3adp+0, 0x1.b33a2b84f15fbp+0, 0x1.b7f76f2fb5e47p+0, 0x1.bcc1e904bc1d2p+0,
+    0x1.c199bdd85529cp+0, 0x1.c67f12e57d14bp+0, 0x1.cb720dcef9069p+0, 0x1.d072d4a07897cp+0,
+    0x1.d5818dcfba487p+0, 0x1.da9e603db3285p+0, 0x1.dfc97337b9b5fp+0, 0x1.e502ee78b3ff6p+0,
+    0x1.ea4afa2a490dap+0, 0x1.efa1bee615a27p+0, 0x1.f50765b6e4540p+0, 0x1.fa7c1819e90d8p+0};
+
+// exp(x) for -700 <= x <= 700 (CLAMP: any x <= 700; results below 2^-1000 come out as ~2^-1000 * m,
+// used only where such a term is added to one that is larger by hundreds of orders of magnitude).
+// x = (64 n' + i) ln2/64 + r, |r| <= ln2/128: exp(x) = 2^n' * T[i] * (1 + r + r^2/2 + ... + r^5/120).
+template <bool CLAMP>
+__device__ __forceinline__ double exp_tab(double x, const double* __restrict__ T)
+{
+    const double magic = 6755399441055744.0;  // 1.5 * 2^52: adding it leaves rint(.) in the low word
+    const double t = fma(x, 0x1.71547652b82fep+6, magic);
+    const int n = __double2loint(t);
+    const double nd = t - magic;
+    double r = fma(nd, -0x1.62e42fefa39efp-7, x);
+    r = fma(nd, -0x1.abc9e3b39803fp-62, r);
+    const double r2 = r * r;
+    double c = fma(r, 1.0 / 120.0, 1.0 / 24.0);
+    c = fma(c, r, 1.0 / 6.0);
+    c = fma(c, r, 0.5);
+    const double p = fma(r2, c, r);
+    const double tv = T[n & (kExpTab - 1)];
+    const double m = fma(tv, p, tv);
+    int e = n >> 6;
+    if (CLAMP) e = max(e, -1000);
+    return __hiloint2double(__double2hiint(m) + (e << 20), __double2loint(m));
+}
+
+// 1/sqrt(y), y normal and positive: MUFU seed (~2^-20) + one cubic step (error ~ 5/16 e^3 < 1e-17).
+__device__ __forceinline__ double rsqrt_fast(double y)
+{
+    double s;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(s) : "d"(y));
+    const double e = fma(-(y * s), s, 1.0);
+    const double c = fma(0.375, e, 0.5);
+    return fma(s * e, c, s);
+}
+
+// 1/y, y normal and positive: MUFU seed + one cubic step.
+__device__ __forceinline__ double rcp_fast(double y)
+{
+    double s;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(s) : "d"(y));
+    const double e = fma(-y, s, 1.0);
+    return fma(fma(e, e, e), s, s);
+}
+
+template <int KMAX>
+struct GridSet {
+    WTable<KMAX> wt[2];
+    double etab[kExpTab];
+    double tn[5];          // decision-time nodes of the first outer level, ascending: lb, d, c, e, ub
+    double rho[5];         // exp(pi^2 (tn[j] - tn[0]) / (2 a^2))
+    double sw2[2][5];      // (a sv w_i)^2 at start points i (table nodes 4 i), per boundary
+    double aw2[2][5];      // 2 a w_i
+    unsigned long long xwin[kThrWin];  // bit patterns of xthr inside the window, padded with +inf
+    int code[kMaxRegions];
+    int region0;           // thresholds below the window (always passed)
+    int ok;                // 0: the grid evaluator cannot be used for this set
+    double xt_lo, xt_hi;   // comfortable decision-time range [a^2/512, 128 a^2]
+    double a, sv, t, st, sz;  // st, sz after the 1e-3 snap of src/pdf.pxi:122-125
+    double a_sq, inv_a_sq, sv_sq, qk;  // qk = -pi^2 / (2 a^2)
+    double inv_zt, inv_st; // 1/(ub_z - lb_z) (1 when sz == 0), 1/(ub_t - lb_t)
+    double zw, zw6, zw12;  // ub_z - lb_z, and that / 6, / 12 (src/integrate.pxi:99-100,137)
+    double tw, tw6, tw12;  // ub_t - lb_t, / 6, / 12
+};
+
+// Smallest double X with fl(X / a_sq) >= thr (thr and thr * a_sq normal and positive).
+__device__ __forceinline__ double xt_threshold(double thr, double a_sq)
+{
+    double X = thr * a_sq;
+    for (int it = 0; it < 8 && X / a_sq >= thr; ++it) X = __longlong_as_double(__double_as_longlong(X) - 1);
+    for (int it = 0; it < 16 && X / a_sq < thr; ++it) X = __longlong_as_double(__double_as_longlong(X) + 1);
+    return X;
+}
+
+// Block-cooperative build.  par = v, sv, a, z, sz, t, st of the set (v unused).
+template <int KMAX>
+__device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par[7], const SeriesTable& tab)
+{
+    build_wtables<KMAX>(G.wt, par[3], par[4]);  // ends with __syncthreads()
+    const int tid = threadIdx.x;
+    const double a = par[2], sv = par[1];
+    const double a_sq = a * a;
+    const double st = par[6] < 1e-3 ? 0.0 : par[6];
+    const double sz = par[4] < 1e-3 ? 0.0 : par[4];
+    const double tt_lo = 1.0 / 512.0, tt_hi = 128.0;
+    if (tid < kExpTab) G.etab[tid] = g_exp2_tab[tid];
+    if (tid == 64) {
+        const double lo = par[5] - st / 2., hi = par[5] + st / 2.;
+        const double c = (lo + hi) / 2.;
+        G.tn[0] = lo; G.tn[4] = hi; G.tn[2] = c;
+        G.tn[1] = (lo + c) / 2.; G.tn[3] = (c + hi) / 2.;
+        G.a = a; G.sv = sv; G.t = par[5]; G.st = st; G.sz = sz;
+        G.a_sq = a_sq; G.inv_a_sq = 1.0 / a_sq; G.sv_sq = sv * sv; G.qk = -kPiSq / (2.0 * a_sq);
+        G.zw = G.wt[0].w[16] - G.wt[0].w[0];
+        G.zw6 = G.zw / 6.0; G.zw12 = G.zw / 12.0;
+        G.tw = hi - lo; G.tw6 = G.tw / 6.0; G.tw12 = G.tw / 12.0;
+        G.inv_zt = sz == 0 ? 1.0 : 1.0 / G.zw;
+        G.inv_st = st == 0 ? 1.0 : 1.0 / (hi - lo);
+        G.xt_lo = tt_lo * a_sq;  // exact (power of two) unless it leaves the normal range
+        G.xt_hi = tt_hi * a_sq;
+        // window of thresholds inside (tt_lo, tt_hi]
+        int r0 = 0, nwin = 0;
+        for (int i = 0; i < tab.n_thr; ++i) {
+            if (tab.thr[i] <= tt_lo) r0++;
+            else if (tab.thr[i] <= tt_hi) nwin++;
+        }
+        G.region0 = r0;
+        // a in a sane range keeps every product below normal and finite
+        G.ok = (nwin <= kThrWin) && (a_sq >= 1e-100) && (a_sq <= 1e100) && (tab.n_thr >= 0) ? 1 : 0;
+    }
+    if (tid >= 96 && tid < 96 + kMaxRegions) G.code[tid - 96] = tid - 96 <= tab.n_thr ? tab.code[tid - 96] : 0;
+    if (tid >= 128 && tid < 128 + 10) {
+        const int b = (tid - 128) / 5, i = (tid - 128) % 5;
+        const double w = G.wt[b].w[4 * i];
+        const double asw = (a * sv) * w;
+        G.sw2[b][i] = asw * asw;
+        G.aw2[b][i] = (2.0 * a) * w;
+    }
+    __syncthreads();
+    if (tid < 5) G.rho[tid] = exp(-G.qk * (G.tn[tid] - G.tn[0]));
+    if (tid >= 32 && tid < 32 + kThrWin) {
+        const int k = tid - 32, i = G.region0 + k;
+        double X = __longlong_as_double(0x7ff0000000000000LL);
+        if (G.ok && i < tab.n_thr && tab.thr[i] <= tt_hi) X = xt_threshold(tab.thr[i], a_sq);
+        G.xwin[k] = (unsigned long long)__double_as_longlong(X);
+    }
+    __syncthreads();
+}
+
+// (branch, K) code for a positive decision time inside the comfortable range.
+template <int KMAX>
+__device__ __forceinline__ int grid_code(const GridSet<KMAX>& G, double xt)
+{
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(xt);
+    int r = G.region0;
+#pragma unroll
+    for (int k = 0; k < kThrWin; ++k) r += bits >= G.xwin[k] ? 1 : 0;
+    return G.code[r];
+}
+
+// Per-trial constants of the grid evaluator (after the boundary flip).
+struct GridTrial {
+    double v, v_sq;
+    int b;
+};
+
+// pdf_sv(xt, v, sv, a, w_i) / ZT at the NW first-level start points (NW = 5: table nodes 0,4,..,16;
+// NW = 1: the set's own start point) of one decision time xt inside the comfortable range.
+// `code` is the series decision at xt, `q` the large-time exp(-pi^2 tt / 2) (unused for small-time).
+template <int KMAX, int NW>
+__device__ __forceinline__ void grid_node(const GridSet<KMAX>& G, const GridTrial& c, double xt, int code,
+                                          double q, double f[NW])
+{
+    const WTable<KMAX>& T = G.wt[c.b];
+    double p[NW];
+#pragma unroll
+    for (int i = 0; i < NW; ++i) p[i] = 0.0;
+    double post;
+    if (code > 0) {  // small-time, src/pdf.pxi:51-57
+        const double inv_tt = G.a_sq * rcp_fast(xt);
+        const double arg = 0.5 * inv_tt;
+        const int K = code;
+        for (int k = -((K - 1) / 2); k <= K / 2; ++k) {
+            const double two_k = (double)(2 * k);
+#pragma unroll
+            for (int i = 0; i < NW; ++i) {
+                const double u = T.w[NW == 5 ? 4 * i : 8] + two_k;
+                p[i] = fma(u, exp_tab<true>(-(u * u) * arg, G.etab), p[i]);
+            }
+        }
+        // 1/sqrt(2 pi tt^3) = inv_tt * sqrt(inv_tt / (2 pi))
+        post = inv_tt * (inv_tt * rsqrt_fast((2.0 * kPi) * inv_tt));
+    } else {  // large-time, :59-63: terms k q^(k^2) sin(k pi w)
+        const int K = -code;
+        const double q2 = q * q;
+        double odd = q, pw = q;
+#pragma unroll
+        for (int k = 1; k <= KMAX; ++k) {
+            if (k <= K) {
+                if (k > 1) {
+                    odd *= q2;
+                    pw *= odd;
+                }
+                const double e = (double)k * pw;
+#pragma unroll
+                for (int i = 0; i < NW; ++i) p[i] = fma(e, T.s[k - 1][NW == 5 ? 4 * i : 8], p[i]);
+            }
+        }
+        post = kPi;
+    }
+    // sv marginal, src/pdf.pxi:85,102
+    double r = 1.0, d = 0.5;
+    const bool sv_zero = G.sv == 0.0;
+    if (!sv_zero) {
+        r = rsqrt_fast(fma(G.sv_sq, xt, 1.0));
+        d = 0.5 * (r * r);
+    }
+    const double scale = (post * r) * (G.inv_a_sq * G.inv_zt);
+    const double vx = c.v_sq * xt;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) {
+        const int m = NW == 5 ? i : 2;
+        const double ci = fma(-G.aw2[c.b][m], c.v, G.sw2[c.b][m]);
+        double val = (p[i] * scale) * exp_tab<false>((ci - vx) * d, G.etab);
+        if (!sv_zero && p[i] < 0.0) val = __longlong_as_double(0x7ff8000000000000LL);  // log(p < 0)
+        f[i] = val;
+    }
+}
+
+// Rare: the inner z-integration at decision time xt did not converge on its first level; continue
+// with the v2 walk from the five values already known.
+template <int KMAX>
+__device__ __noinline__ double grid_refine_z(const GridSet<KMAX>& G, const GridTrial& c, double xt,
+                                             const SeriesTable* tab, const double f[5], double coarse,
+                                             double tol, int levels, unsigned long long& evals)
+{
+    TrialCtx tc;
+    tc.a_sq = G.a_sq; tc.inv_a_sq = 1.0 / G.a_sq; tc.sv_sq = G.sv_sq; tc.v_sq = c.v_sq;
+    tc.asv = G.a * G.sv; tc.av2 = (2.0 * G.a) * c.v; tc.tab = tab; tc.sv_zero = G.sv == 0.0;
+    tc.inv_zt = 1.0 / G.zw;
+    const TimeNode n = make_time_node(tc, xt);
+    return refine_z<KMAX>(tc, G.wt[c.b], n, f, coarse, tol, levels, evals);
+}
+
+// Rare: the outer t-integration did not converge on its first level; continue with the v2 walk.
+template <int KMAX>
+__device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridTrial& c, double ax,
+                                             const Numerics& nm, const SeriesTable* tab, const double F[5],
+                                             double coarse, unsigned long long& evals)
+{
+    TrialCtx tc;
+    tc.a_sq = G.a_sq; tc.inv_a_sq = 1.0 / G.a_sq; tc.sv_sq = G.sv_sq; tc.v_sq = c.v_sq;
+    tc.asv = G.a * G.sv; tc.av2 = (2.0 * G.a) * c.v; tc.tab = tab; tc.sv_zero = G.sv == 0.0;
+    const WTable<KMAX>& T = G.wt[c.b];
+    const bool over_z = G.sz != 0;
+    tc.inv_zt = over_z ? 1.0 / G.zw : 1.0;
+    if (over_z) {
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const double w = T.w[4 * i], t1 = tc.asv * w;
+            tc.c5[i] = t1 * t1 - tc.av2 * w;
+        }
+    }
+    const double width = G.tw;
+    auto g = [&](double tn, int) {
+        return (over_z ? inner_z<KMAX>(tc, T, ax - tn, nm.simps_err, nm.n_sz, evals)
+                       : single_z<KMAX>(tc, T, ax - tn, evals)) / width;
+    };
+    Span top;
+    top.lo = G.tn[0]; top.hi = G.tn[4]; top.coarse = coarse;
+    top.f_lo = F[0]; top.f_hi = F[4]; top.f_mid = F[2];
+    top.tol = nm.simps_err; top.levels = nm.n_st; top.ilo = 0; top.ihi = kPosWidth;
+    Span stack[kMaxDepth];
+    return simpson_walk(g, top, true, F[1], F[3], stack);
+}
+
+// full_pdf (src/pdf.pxi:104-146) for one trial of the CTA's set.  par = raw v, sv, a, z, sz, t, st of
+// the set; v may differ per trial.  Returns through the v2 evaluator when the trial is outside the
+// comfortable range (normalised time outside [2^-9, 128], extreme drift, NaN).
+template <int KMAX>
+__device__ __forceinline__ double full_pdf_grid(double x, double v, const double par[7], const GridSet<KMAX>& G,
+                                                const Numerics& nm, const SeriesTable* tab,
+                                                unsigned long long& evals)
+{
+    const double sv = par[1], a = par[2], z = par[3], sz = par[4], t = par[5], st = par[6];
+    const double ax = fabs(x);
+    if ((z < 0) || (z > 1) || (a < 0) || (t < 0) || (st < 0) || (sv < 0) || (sz < 0) || (sz > 1) ||
+        ((ax - (t - st / 2.)) < 0) || (z + sz / 2. > 1) || (z - sz / 2. < 0) || (t - st / 2. < 0))
+        return 0.0;
+    GridTrial c;
+    c.b = x > 0 ? 1 : 0;
+    c.v = c.b ? -v : v;
+    c.v_sq = c.v * c.v;
+
+    const double xt_max = ax - G.tn[0];
+    // exponent of the sv marginal lies in [-(2 a |v| + v^2 x_t) / 2, w^2 / (2 tt) + a |v|]
+    bool ok = G.ok && (xt_max <= G.xt_hi) && (fma(c.v_sq, xt_max, (2.0 * G.a) * fabs(c.v)) <= 800.0) &&
+              (nm.simps_err >= 0.0);
+    unsigned int n_eval = 0;
+    unsigned long long extra = 0;
+    double out = 0.0;
+    if (ok) {
+        const bool over_z = G.sz != 0;
+        const double q0 = exp_tab<false>(G.qk * xt_max, G.etab);
+        if (G.st == 0) {  // src/pdf.pxi:129,137-141: one decision time
+            const double xt = ax - G.t;
+            if (xt <= 0.0) {
+                n_eval = over_z ? 5 : 1;  // src/pdf.pxi:92-93
+            } else if (xt < G.xt_lo) {
+                ok = false;
+            } else {
+                const int code = grid_code(G, xt);
+                if (over_z) {
+                    double f[5];
+                    grid_node<KMAX, 5>(G, c, xt, code, q0, f);
+                    n_eval = 5;
+                    const double coarse = G.zw6 * ((f[0] + 4.0 * f[2]) + f[4]);
+                    const double left = G.zw12 * ((f[0] + 4.0 * f[1]) + f[2]);
+                    const double right = G.zw12 * ((f[2] + 4.0 * f[3]) + f[4]);
+                    const double fine = left + right;
+                    if (nm.n_sz <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err)
+                        out = fma(fine - coarse, 1.0 / 15.0, fine);
+                    else
+                        out = grid_refine_z<KMAX>(G, c, xt, tab, f, coarse, nm.simps_err, nm.n_sz, extra);
+                } else {
+                    double f[1];
+                    grid_node<KMAX, 1>(G, c, xt, code, q0, f);
+                    n_eval = 1;
+                    out = f[0];
+                }
+            }
+        } else {  // :131-134, :143-146: five decision times, then the outer Simpson level
+            double F[5];
+            // the decision is monotone in x_t: if both ends agree every node does
+            const int code_hi = grid_code(G, xt_max);
+            int j_last = 4;
+            while (j_last > 0 && !(ax - G.tn[j_last] > 0.0)) --j_last;
+            const int code_lo = grid_code(G, ax - G.tn[j_last]);
+            const bool uniform = code_hi == code_lo;
+#pragma unroll 1
+            for (int j = 0; j < 5; ++j) {
+                const double xt = ax - G.tn[j];
+                n_eval += over_z ? 5 : 1;
+                double val = 0.0;
+                if (xt > 0.0) {
+                    if (xt < G.xt_lo) ok = false;
+                    const int code = uniform ? code_hi : grid_code(G, xt);
+                    const double q = q0 * G.rho[j];
+                    if (over_z) {
+                        double f[5];
+                        grid_node<KMAX, 5>(G, c, xt, code, q, f);
+                        const double coarse = G.zw6 * ((f[0] + 4.0 * f[2]) + f[4]);
+                        const double left = G.zw12 * ((f[0] + 4.0 * f[1]) + f[2]);
+                        const double right = G.zw12 * ((f[2] + 4.0 * f[3]) + f[4]);
+                        const double fine = left + right;
+                        if (nm.n_sz <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err)
+                            val = fma(fine - coarse, 1.0 / 15.0, fine);
+                        else if (ok)
+                            val = grid_refine_z<KMAX>(G, c, xt, tab, f, coarse, nm.simps_err, nm.n_sz, extra);
+                    } else {
+                        double f[1];
+                        grid_node<KMAX, 1>(G, c, xt, code, q, f);
+                        val = f[0];
+                    }
+                }
+                F[j] = val * G.inv_st;
+            }
+            if (ok) {
+                const double coarse = G.tw6 * ((F[0] + 4.0 * F[2]) + F[4]);
+                const double left = G.tw12 * ((F[0] + 4.0 * F[1]) + F[2]);
+                const double right = G.tw12 * ((F[2] + 4.0 * F[3]) + F[4]);
+                const double fine = left + right;
+                if (nm.n_st <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err)
+                    out = fma(fine - coarse, 1.0 / 15.0, fine);
+                else
+                    out = grid_refine_t<KMAX>(G, c, ax, nm, tab, F, coarse, extra);
+            }
+        }
+    }
+    if (!ok)  // outside the comfortable range: the v2 evaluator handles every corner
+        return full_pdf_fast<KMAX>(x, v, sv, a, z, sz, t, st, nm, tab, G.wt, evals);
+    evals += n_eval + extra;
+    return out;
+}
+
+}  // namespace hddm

@@ -12,10 +12,11 @@
 #include "kernels.cuh"
 #include "wfpt_device.cuh"
 #include "wfpt_fast.cuh"
+#include "wfpt_grid.cuh"
 
 namespace hddm {
 
-int g_kernel_choice = 0;  // 0: pick per launch; 1: always the generic evaluator (tests, A/B runs)
+int g_kernel_choice = 0;  // 0: pick per launch; 1: always the generic evaluator; 2: never the grid evaluator
 
 __device__ __forceinline__ double warp_sum(double v)
 {
@@ -39,11 +40,14 @@ __device__ __forceinline__ double load_par(const LikeArgs& a, int k, int64_t p, 
 // KMAX > 0: the table-driven evaluator of wfpt_fast.cuh (z, sz uniform per set, adaptive
 // integration, large-time series of at most KMAX terms).  KMAX == 0: the generic evaluator of
 // wfpt_device.cuh (any per-trial parameter, fixed-grid Simpson, no table).
-template <int KMAX>
+// GRID: additionally sv, a, t, st uniform per set -> the v3 grid evaluator of wfpt_grid.cuh.
+template <int KMAX, bool GRID>
 __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     k_like_partial(const __grid_constant__ LikeArgs a)
 {
-    __shared__ WTable<(KMAX > 0 ? KMAX : 1)> wt[2];
+    constexpr int KT = KMAX > 0 ? KMAX : 1;
+    __shared__ GridSet<KT> gs;
+    WTable<KT>* wt = gs.wt;
     const int64_t p = blockIdx.x;
     const int chunk = blockIdx.y;
     const int64_t lo = a.seg ? a.seg[p] : 0;
@@ -67,9 +71,13 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         per_trial |= a.trial_stride[k] != 0;
     }
 
-    if (KMAX > 0) build_wtables<(KMAX > 0 ? KMAX : 1)>(wt, par[3], par[4]);
+    if (GRID)
+        build_gridset<KT>(gs, par, a.tab);
+    else if (KMAX > 0)
+        build_wtables<KT>(wt, par[3], par[4]);
 
     auto density = [&](double x, unsigned long long& ev) {
+        if (GRID) return full_pdf_grid<KT>(x, par[0], par, gs, a.nm, &a.tab, ev);
         if (KMAX > 0)
             return full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(x, par[0], par[1], par[2], par[3], par[4], par[5],
                                                         par[6], a.nm, &a.tab, wt, ev);
@@ -154,29 +162,43 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     // z (3) and sz (4) must be uniform per set for the shared start-point tables
     const bool fast = g_kernel_choice != 1 && a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 &&
                       b.tab.max_large_k <= 8 && a.trial_stride[3] == 0 && a.trial_stride[4] == 0;
-    if (fast && b.tab.max_large_k <= 4)
-        k_like_partial<4><<<grid, kLikeThreads, 0, stream>>>(b);
+    bool uniform = true;  // everything but the drift is uniform per set
+    for (int k = 1; k < 7; ++k) uniform &= a.trial_stride[k] == 0;
+    const bool gridk = fast && uniform && g_kernel_choice != 2;
+    if (gridk && b.tab.max_large_k <= 4)
+        k_like_partial<4, true><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (gridk)
+        k_like_partial<8, true><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (fast && b.tab.max_large_k <= 4)
+        k_like_partial<4, false><<<grid, kLikeThreads, 0, stream>>>(b);
     else if (fast)
-        k_like_partial<8><<<grid, kLikeThreads, 0, stream>>>(b);
+        k_like_partial<8, false><<<grid, kLikeThreads, 0, stream>>>(b);
     else
-        k_like_partial<0><<<grid, kLikeThreads, 0, stream>>>(b);
+        k_like_partial<0, false><<<grid, kLikeThreads, 0, stream>>>(b);
     const int sets_per_block = 128 / 32;
     k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(b);
     return cudaGetLastError();
 }
 
 // pdf_array (src/wfpt.pyx:32-48): per-trial density, outlier mix, optional log.
-template <int KMAX>
+template <int KMAX, bool GRID>
 __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     k_pdf_array(const __grid_constant__ PdfArgs a)
 {
-    __shared__ WTable<(KMAX > 0 ? KMAX : 1)> wt[2];
-    if (KMAX > 0) build_wtables<(KMAX > 0 ? KMAX : 1)>(wt, a.par[3], a.par[4]);
+    constexpr int KT = KMAX > 0 ? KMAX : 1;
+    __shared__ GridSet<KT> gs;
+    WTable<KT>* wt = gs.wt;
+    if (GRID)
+        build_gridset<KT>(gs, a.par, a.tab);
+    else if (KMAX > 0)
+        build_wtables<KT>(wt, a.par[3], a.par[4]);
     unsigned long long evals = 0;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
         double d;
-        if (KMAX > 0)
+        if (GRID)
+            d = full_pdf_grid<KT>(__ldg(a.x + i), a.par[0], a.par, gs, a.nm, &a.tab, evals);
+        else if (KMAX > 0)
             d = full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(__ldg(a.x + i), a.par[0], a.par[1], a.par[2], a.par[3],
                                                      a.par[4], a.par[5], a.par[6], a.nm, &a.tab, wt, evals);
         else
@@ -200,12 +222,17 @@ cudaError_t launch_pdf_array(const PdfArgs& a, cudaStream_t stream)
     b.tab = series_table_for(a.nm.err);
     const bool fast = g_kernel_choice != 1 && a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 &&
                       b.tab.max_large_k <= 8;
-    if (fast && b.tab.max_large_k <= 4)
-        k_pdf_array<4><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+    const bool gridk = fast && g_kernel_choice != 2;
+    if (gridk && b.tab.max_large_k <= 4)
+        k_pdf_array<4, true><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+    else if (gridk)
+        k_pdf_array<8, true><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+    else if (fast && b.tab.max_large_k <= 4)
+        k_pdf_array<4, false><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
     else if (fast)
-        k_pdf_array<8><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+        k_pdf_array<8, false><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
     else
-        k_pdf_array<0><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+        k_pdf_array<0, false><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
     return cudaGetLastError();
 }
 

@@ -48,9 +48,10 @@ int hddm_b200_synchronize(void);
 /* FP64 roofline denominator measured on this device: achieved FLOP/s (2 per FMA) of a
  * register-resident dependent-FMA probe, and its duration in ms. */
 int hddm_b200_fp64_peak(int iters, double *flops, float *ms);
-/* Evaluator selection for the likelihood kernels: 0 = per launch (table-driven evaluator when z and
- * sz are uniform per parameter set and integration is adaptive, else the generic one), 1 = always
- * the generic evaluator.  Both run on the GPU; this exists for A/B parity tests and profiling. */
+/* Evaluator selection for the likelihood kernels: 0 = per launch (the grid evaluator when every
+ * parameter but the drift is uniform per set and integration is adaptive; else the table-driven walk
+ * when z and sz are uniform per set; else the generic one), 1 = always the generic evaluator, 2 = never
+ * the grid evaluator.  All run on the GPU; this exists for A/B parity tests and profiling. */
 int hddm_b200_set_kernel(int which);
 /* The (branch, K) decision of ftt_01w (src/pdf.pxi:36-54,60) as the piecewise-constant function of
  * normalised time the kernels look up: region r = #{i < n_thr[0] : tt >= thr[i]}, code[r] = +K

@@ -23,12 +23,13 @@ def W(gpu):
     return wfpt
 
 
-@pytest.fixture(autouse=True, params=["auto", "generic"])
+@pytest.fixture(autouse=True, params=["auto", "walk", "generic"])
 def evaluator(request, gpu):
-    """Every parity test runs twice: with the per-launch choice (table-driven evaluator of
-    csrc/wfpt_fast.cuh where it applies) and with the generic evaluator forced.  Both are CUDA."""
+    """Every parity test runs three times: with the per-launch choice (the grid evaluator of
+    csrc/wfpt_grid.cuh where it applies), with the grid evaluator disabled (table-driven walk of
+    csrc/wfpt_fast.cuh) and with the generic evaluator forced.  All three are CUDA."""
     from hddm_b200 import _lib
-    _lib.check(_lib.lib().hddm_b200_set_kernel(1 if request.param == "generic" else 0))
+    _lib.check(_lib.lib().hddm_b200_set_kernel({"auto": 0, "generic": 1, "walk": 2}[request.param]))
     yield request.param
     _lib.check(_lib.lib().hddm_b200_set_kernel(0))
 
