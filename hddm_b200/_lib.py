@@ -32,6 +32,9 @@ SIGNATURES = {
     "hddm_b200_synchronize": (_i, []),
     "hddm_b200_fp64_peak": (_i, [_i, c_dp, C.POINTER(C.c_float)]),
     "hddm_b200_set_kernel": (_i, [_i]),
+    "hddm_b200_set_sort": (_i, [_i]),
+    "hddm_sort_trials_scratch": (_l, [_l, _l]),
+    "hddm_sort_trials_dev": (_i, [_v, _l, _v, _l, _v, _v, _l, _v]),
     "hddm_series_table": (_i, [_d, c_dp, c_ip, C.POINTER(_i)]),
     "hddm_full_pdf": (_i, [_d] * 8 + _NUM + [c_dp]),
     "hddm_pdf_array": (_i, [c_dp, _l] + [_d] * 7 + [_d, _i, _i, _i, _i, _d, _d, _d, c_dp]),

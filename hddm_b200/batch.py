@@ -33,7 +33,7 @@ def shard_sizes(n_sets, world_size):
 class DeviceSweep(object):
     """Trials resident in HBM + reusable scratch for repeated batched launches on one GPU."""
 
-    def __init__(self, x, device=None, seg=None):
+    def __init__(self, x, device=None, seg=None, sort=True):
         import torch
         self.torch = torch
         if not torch.cuda.is_available():
@@ -52,6 +52,19 @@ class DeviceSweep(object):
         self._logp = None
         self.evals = torch.zeros(1, dtype=torch.int64, device=self.device)
         self.lib = _lib.lib()
+        if sort and self.n >= 64:
+            # one-time layout step: trials ordered by |rt| (within segments) so that the lanes of a warp
+            # take the same series branch; the per-set sums are order-independent up to rounding
+            n_seg = 0 if self.seg is None else int(self.seg.numel()) - 1
+            nbytes = int(self.lib.hddm_sort_trials_scratch(self.n, n_seg))
+            scratch = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            xs = torch.empty_like(self.x)
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            _lib.check(self.lib.hddm_sort_trials_dev(
+                self.x.data_ptr(), self.n, self.seg.data_ptr() if self.seg is not None else None, n_seg,
+                xs.data_ptr(), scratch.data_ptr(), nbytes, C.c_void_p(stream)))
+            torch.cuda.current_stream(self.device).synchronize()
+            self.x = xs
 
     def _ensure(self, P):
         torch = self.torch

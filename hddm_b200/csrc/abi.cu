@@ -10,6 +10,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <vector>
 
 #include "../../include/hddm_b200.h"
 #include "kernels.cuh"
@@ -164,8 +165,15 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     if (chunks > 65535) return fail(HDDM_ERR_ARG, "more than 65535*2048 trials per parameter set");
     if (P > 2147483647LL) return fail(HDDM_ERR_ARG, "more than 2^31-1 parameter sets per launch");
 
+    // Shared-parameter sums are order-independent: lay the trials out by |rt| (sort_kernels.cu).
+    bool sortable = g_sort_trials && h_x && mode == kModeWienerLike && !h_cont && n >= kSortMin;
+    for (int k = 0; k < 7; ++k) sortable = sortable && spec[k].trial_stride == 0;
+    const size_t sort_bytes = sortable ? sort_trials_scratch_bytes(n, h_seg ? P : 0) : 0;
+
     Layout L;
     const size_t off_x = h_x ? L.reserve((size_t)n * sizeof(double)) : 0;
+    const size_t off_xs = sortable ? L.reserve((size_t)n * sizeof(double)) : 0;
+    const size_t off_sort = sortable ? L.reserve(sort_bytes) : 0;
     const size_t off_cont = h_cont ? L.reserve((size_t)n * sizeof(int32_t)) : 0;
     const size_t off_seg = h_seg ? L.reserve((size_t)(P + 1) * sizeof(int64_t)) : 0;
     size_t off_up[8];
@@ -191,6 +199,11 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     memset(&a, 0, sizeof(a));
     a.x = h_x ? L.at<double>(off_x) : d_x;
     a.seg = h_seg ? L.at<int64_t>(off_seg) : nullptr;
+    if (sortable) {
+        CUDA_TRY(sort_trials(L.at<double>(off_x), L.at<double>(off_xs), n, a.seg, h_seg ? P : 0,
+                             L.at<char>(off_sort), sort_bytes, s));
+        a.x = L.at<double>(off_xs);
+    }
     a.cont = h_cont ? L.at<int32_t>(off_cont) : nullptr;
     for (int k = 0; k < kNumPar; ++k) {
         a.par[k] = L.at<double>(off_up[spec[k].upload]) + spec[k].offset;
@@ -263,6 +276,9 @@ int pdf_array_impl(const double* x, int64_t n, const double par[kNumPar], const 
 struct hddm_trials {
     double* d_x;
     int64_t n;
+    double* d_sorted;              // trials ordered by |rt| within the segments of `sorted_seg`
+    std::vector<int64_t> sorted_seg;  // empty: one segment covering everything
+    bool has_sorted;
 };
 
 extern "C" {
@@ -309,6 +325,13 @@ int hddm_b200_set_kernel(int which)
     if (which < 0 || which > 2) return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto), 1 (generic) or 2 (no grid)");
     std::lock_guard<std::mutex> lock(g_rt.mu);
     g_kernel_choice = which;
+    return HDDM_OK;
+}
+
+int hddm_b200_set_sort(int on)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    g_sort_trials = on ? 1 : 0;
     return HDDM_OK;
 }
 
@@ -549,7 +572,7 @@ int hddm_trials_upload(const double* x, int64_t n, hddm_trials** out)
     std::lock_guard<std::mutex> lock(g_rt.mu);
     if (!out || n < 0 || (n > 0 && !x)) return fail(HDDM_ERR_ARG, "trials_upload: bad buffer");
     TRY(ensure_ready());
-    hddm_trials* h = new (std::nothrow) hddm_trials{nullptr, n};
+    hddm_trials* h = new (std::nothrow) hddm_trials{nullptr, n, nullptr, {}, false};
     if (!h) return fail(HDDM_ERR_ARG, "trials_upload: out of host memory");
     cudaError_t e = cudaMalloc(&h->d_x, (size_t)(n > 0 ? n : 1) * sizeof(double));
     if (e == cudaSuccess && n > 0) {
@@ -571,9 +594,48 @@ int hddm_trials_free(hddm_trials* h)
     if (!h) return HDDM_OK;
     if (g_rt.ready) cudaStreamSynchronize(g_rt.stream);
     cudaFree(h->d_x);
+    if (h->d_sorted) cudaFree(h->d_sorted);
     delete h;
     return HDDM_OK;
 }
+
+}  // extern "C"
+
+namespace {
+// The handle's trials ordered by |rt| within `seg` (P+1 offsets, or nullptr), cached until the
+// segmentation changes.  Falls back to the caller's order for short vectors or when disabled.
+int sorted_view(hddm_trials* h, const int64_t* seg, int64_t P, const double** out)
+{
+    *out = h->d_x;
+    if (!g_sort_trials || h->n < kSortMin) return HDDM_OK;
+    const size_t n_off = seg ? (size_t)P + 1 : 0;
+    if (seg)
+        for (int64_t p = 0; p < P; ++p)
+            if (seg[p] < 0 || seg[p + 1] < seg[p] || seg[p + 1] > h->n)
+                return fail(HDDM_ERR_ARG, "batch: segment offsets must be ascending within [0, n]");
+    const bool same = h->has_sorted && h->sorted_seg.size() == n_off &&
+                      (n_off == 0 || memcmp(h->sorted_seg.data(), seg, n_off * sizeof(int64_t)) == 0);
+    if (!same) {
+        if (!h->d_sorted) CUDA_TRY(cudaMalloc(&h->d_sorted, (size_t)h->n * sizeof(double)));
+        const size_t bytes = sort_trials_scratch_bytes(h->n, seg ? P : 0);
+        Layout L;
+        const size_t off_seg = L.reserve(n_off * sizeof(int64_t));
+        const size_t off_sort = L.reserve(bytes);
+        TRY(ensure_arena(L.total));
+        cudaStream_t s = g_rt.stream;
+        if (seg) CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_seg), seg, n_off * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+        CUDA_TRY(sort_trials(h->d_x, h->d_sorted, h->n, seg ? L.at<int64_t>(off_seg) : nullptr, seg ? P : 0,
+                             L.at<char>(off_sort), bytes, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+        h->sorted_seg.assign(seg, seg + n_off);
+        h->has_sorted = true;
+    }
+    *out = h->d_sorted;
+    return HDDM_OK;
+}
+}  // namespace
+
+extern "C" {
 
 int hddm_trials_wiener_like(const hddm_trials* h, double v, double sv, double a, double z, double sz, double t,
                             double st, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
@@ -582,7 +644,10 @@ int hddm_trials_wiener_like(const hddm_trials* h, double v, double sv, double a,
     std::lock_guard<std::mutex> lock(g_rt.mu);
     if (!h) return fail(HDDM_ERR_ARG, "null trials handle");
     const double par[kNumPar] = {v, sv, a, z, sz, t, st, p_outlier, w_outlier};
-    return scalar_like(nullptr, h->d_x, h->n, par, kModeWienerLike, nullptr,
+    const double* dx = nullptr;
+    TRY(ensure_ready());
+    TRY(sorted_view(const_cast<hddm_trials*>(h), nullptr, 0, &dx));
+    return scalar_like(nullptr, dx, h->n, par, kModeWienerLike, nullptr,
                        make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp);
 }
 
@@ -592,11 +657,29 @@ int hddm_trials_wiener_like_batch(const hddm_trials* h, const int64_t* seg, cons
 {
     std::lock_guard<std::mutex> lock(g_rt.mu);
     if (!h) return fail(HDDM_ERR_ARG, "null trials handle");
-    return batch_like(nullptr, h->d_x, h->n, seg, params, P,
+    if (P < 0) return fail(HDDM_ERR_ARG, "batch: negative P");
+    const double* dx = nullptr;
+    TRY(ensure_ready());
+    TRY(sorted_view(const_cast<hddm_trials*>(h), seg, P, &dx));
+    return batch_like(nullptr, dx, h->n, seg, params, P,
                       make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, evals);
 }
 
 /* ---- device-pointer entry points ------------------------------------------------------------- */
+
+int64_t hddm_sort_trials_scratch(int64_t n, int64_t n_seg)
+{
+    return (int64_t)sort_trials_scratch_bytes(n, n_seg);
+}
+
+int hddm_sort_trials_dev(const double* d_x, int64_t n, const int64_t* d_seg, int64_t n_seg, double* d_sorted,
+                         void* d_scratch, int64_t scratch_bytes, void* stream)
+{
+    if (n < 0 || n_seg < 0 || (n > 0 && (!d_x || !d_sorted || !d_scratch)) || (n_seg > 0 && !d_seg) || d_x == d_sorted)
+        return fail(HDDM_ERR_ARG, "sort_trials_dev: bad buffer");
+    CUDA_TRY(sort_trials(d_x, d_sorted, n, d_seg, n_seg, d_scratch, (size_t)scratch_bytes, (cudaStream_t)stream));
+    return HDDM_OK;
+}
 
 int64_t hddm_wiener_like_batch_scratch(int64_t max_seg_len, int64_t P)
 {

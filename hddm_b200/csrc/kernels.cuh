@@ -104,4 +104,12 @@ cudaError_t launch_sample_rts(const double* xgrid, const double* table, int64_t 
 
 double fp64_peak_probe(int iters, float* ms_out, cudaStream_t stream);
 
+// Trials ordered by |rt| (sort_kernels.cu): a one-time layout step so that the lanes of a warp take the
+// same series branch.  n_seg > 0: within each segment [d_seg[s], d_seg[s+1]).
+size_t sort_trials_scratch_bytes(int64_t n, int64_t n_seg);
+cudaError_t sort_trials(const double* d_x, double* d_sorted, int64_t n, const int64_t* d_seg, int64_t n_seg,
+                        void* d_scratch, size_t scratch_bytes, cudaStream_t stream);
+constexpr int64_t kSortMin = 64;  // shorter trial vectors are evaluated in the caller's order
+extern int g_sort_trials;         // 1 (default): order trials by |rt| where the entry point allows it
+
 }  // namespace hddm

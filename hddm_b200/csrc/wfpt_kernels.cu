@@ -16,6 +16,7 @@
 
 namespace hddm {
 
+int g_sort_trials = 1;
 int g_kernel_choice = 0;  // 0: pick per launch; 1: always the generic evaluator; 2: never the grid evaluator
 
 __device__ __forceinline__ double warp_sum(double v)

@@ -53,6 +53,11 @@ int hddm_b200_fp64_peak(int iters, double *flops, float *ms);
  * when z and sz are uniform per set; else the generic one), 1 = always the generic evaluator, 2 = never
  * the grid evaluator.  All run on the GPU; this exists for A/B parity tests and profiling. */
 int hddm_b200_set_kernel(int which);
+/* Trial layout: 1 (default) = entry points whose result is a sum over trials with set-uniform
+ * parameters (wiener_like, wiener_like_batch, the trials handle) evaluate the trials ordered by |rt|
+ * (within each segment), so the lanes of a warp share the series branch; 0 = caller's order.  The sum
+ * is the same up to rounding and deterministic either way. */
+int hddm_b200_set_sort(int on);
 /* The (branch, K) decision of ftt_01w (src/pdf.pxi:36-54,60) as the piecewise-constant function of
  * normalised time the kernels look up: region r = #{i < n_thr[0] : tt >= thr[i]}, code[r] = +K
  * (small-time series, K terms) or -K (large-time).  thr holds >= 31 doubles, code >= 32 ints.
@@ -144,6 +149,13 @@ int hddm_trials_wiener_like_batch(const hddm_trials *h, const int64_t *seg, cons
                                   double simps_err, double *logp, unsigned long long *evals);
 
 /* ---- device-pointer entry points (enqueue only; used under torch.distributed sharding) ----- */
+
+/* One-time layout step for a device-resident trial vector that many launches will reuse: d_sorted =
+ * the trials of d_x ordered by |rt| (within each segment [d_seg[s], d_seg[s+1]) when n_seg > 0).
+ * hddm_sort_trials_scratch gives the BYTES of d_scratch needed.  d_sorted must not alias d_x. */
+int64_t hddm_sort_trials_scratch(int64_t n, int64_t n_seg);
+int hddm_sort_trials_dev(const double *d_x, int64_t n, const int64_t *d_seg, int64_t n_seg,
+                         double *d_sorted, void *d_scratch, int64_t scratch_bytes, void *stream);
 
 /* Elements (doubles) of scratch the batched launch needs for P sets whose longest segment has
  * max_seg_len trials. */
