@@ -91,17 +91,22 @@ __device__ __forceinline__ double rcp_fast(double y)
 }
 
 template <int KMAX>
-struct GridSet {
+struct alignas(16) GridSet {
+    double s5[2][KMAX][6];  // sin(k pi w_i) at the five first-level start points (table nodes 4 i), padded
+    double w5[2][6];        // those start points
     WTable<KMAX> wt[2];
     double etab[kExpTab];
     double tn[5];          // decision-time nodes of the first outer level, ascending: lb, d, c, e, ub
     double rho[5];         // exp(pi^2 (tn[j] - tn[0]) / (2 a^2))
-    double sw2[2][5];      // (a sv w_i)^2 at start points i (table nodes 4 i), per boundary
-    double aw2[2][5];      // 2 a w_i
+    // sv-marginal exponent numerator c(w) = (a sv w)^2 - 2 a v w at the start points, as a function of
+    // the drift: c_0 = sw0 - aw0 v, c_1 - c_0 = dsw - daw v, second difference d2c (free of v)
+    double sw0[2], aw0[2], dsw[2], daw[2], d2c[2];
     unsigned long long xwin[kThrWin];  // bit patterns of xthr inside the window, padded with +inf
     int code[kMaxRegions];
     int region0;           // thresholds below the window (always passed)
     int ok;                // 0: the grid evaluator cannot be used for this set
+    int support;           // the set-level part of the support test of src/pdf.pxi:111-113 passed
+    double t_onset;        // t - st/2 with the raw st (the per-trial part of that test)
     double xt_lo, xt_hi;   // comfortable decision-time range [a^2/512, 128 a^2]
     double a, sv, t, st, sz;  // st, sz after the 1e-3 snap of src/pdf.pxi:122-125
     double a_sq, inv_a_sq, sv_sq, qk;  // qk = -pi^2 / (2 a^2)
@@ -152,16 +157,33 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
             else if (tab.thr[i] <= tt_hi) nwin++;
         }
         G.region0 = r0;
+        {
+            const double z = par[3], szr = par[4], t = par[5], str = par[6];
+            G.support = !((z < 0) || (z > 1) || (a < 0) || (t < 0) || (str < 0) || (sv < 0) || (szr < 0) ||
+                          (szr > 1) || (z + szr / 2. > 1) || (z - szr / 2. < 0) || (t - str / 2. < 0));
+            G.t_onset = t - str / 2.;
+        }
         // a in a sane range keeps every product below normal and finite
-        G.ok = (nwin <= kThrWin) && (a_sq >= 1e-100) && (a_sq <= 1e100) && (tab.n_thr >= 0) ? 1 : 0;
+        G.ok = (nwin <= kThrWin - 1) && (a_sq >= 1e-100) && (a_sq <= 1e100) && (tab.n_thr >= 0) ? 1 : 0;
     }
     if (tid >= 96 && tid < 96 + kMaxRegions) G.code[tid - 96] = tid - 96 <= tab.n_thr ? tab.code[tid - 96] : 0;
-    if (tid >= 128 && tid < 128 + 10) {
-        const int b = (tid - 128) / 5, i = (tid - 128) % 5;
-        const double w = G.wt[b].w[4 * i];
-        const double asw = (a * sv) * w;
-        G.sw2[b][i] = asw * asw;
-        G.aw2[b][i] = (2.0 * a) * w;
+    if (tid >= 128 && tid < 130) {
+        const int b = tid - 128;
+        double sw[3], aw[3];
+        for (int i = 0; i < 3; ++i) {
+            const double w = G.wt[b].w[4 * i];
+            const double asw = (a * sv) * w;
+            sw[i] = asw * asw;
+            aw[i] = (2.0 * a) * w;
+        }
+        G.sw0[b] = sw[0]; G.aw0[b] = aw[0];
+        G.dsw[b] = sw[1] - sw[0]; G.daw[b] = aw[1] - aw[0];
+        G.d2c[b] = (sw[2] - sw[1]) - (sw[1] - sw[0]);
+        for (int i = 0; i < 6; ++i) G.w5[b][i] = i < 5 ? G.wt[b].w[4 * i] : 0.0;
+    }
+    if (tid >= 160 && tid < 160 + 2 * KMAX * 6) {
+        const int r = tid - 160, b = r / (KMAX * 6), k = (r / 6) % KMAX, i = r % 6;
+        G.s5[b][k][i] = i < 5 ? G.wt[b].s[k][4 * i] : 0.0;
     }
     __syncthreads();
     if (tid < 5) G.rho[tid] = exp(-G.qk * (G.tn[tid] - G.tn[0]));
@@ -174,22 +196,31 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
     __syncthreads();
 }
 
-// (branch, K) code for a positive decision time inside the comfortable range.
+// (branch, K) code for a positive decision time inside the comfortable range: three-step binary
+// search for #{k : xt >= xwin[k]} over the 7 usable window entries (xwin[7] is always +inf).
 template <int KMAX>
 __device__ __forceinline__ int grid_code(const GridSet<KMAX>& G, double xt)
 {
     const unsigned long long bits = (unsigned long long)__double_as_longlong(xt);
-    int r = G.region0;
-#pragma unroll
-    for (int k = 0; k < kThrWin; ++k) r += bits >= G.xwin[k] ? 1 : 0;
-    return G.code[r];
+    int r = bits >= G.xwin[3] ? 4 : 0;
+    r += bits >= G.xwin[r + 1] ? 2 : 0;
+    r += bits >= G.xwin[r] ? 1 : 0;
+    return G.code[G.region0 + r];
 }
 
 // Per-trial constants of the grid evaluator (after the boundary flip).
 struct GridTrial {
     double v, v_sq;
+    double c0, dc0;  // c(w_0) and c(w_1) - c(w_0) for this trial's drift
     int b;
 };
+
+__device__ __forceinline__ void load5(const double* __restrict__ p, double v[5])
+{
+    const double2 a = *reinterpret_cast<const double2*>(p);
+    const double2 b = *reinterpret_cast<const double2*>(p + 2);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = p[4];
+}
 
 // pdf_sv(xt, v, sv, a, w_i) / ZT at the NW first-level start points (NW = 5: table nodes 0,4,..,16;
 // NW = 1: the set's own start point) of one decision time xt inside the comfortable range.
@@ -198,12 +229,18 @@ template <int KMAX, int NW>
 __device__ __forceinline__ void grid_node(const GridSet<KMAX>& G, const GridTrial& c, double xt, int code,
                                           double q, double f[NW])
 {
-    const WTable<KMAX>& T = G.wt[c.b];
     double p[NW];
-#pragma unroll
-    for (int i = 0; i < NW; ++i) p[i] = 0.0;
     double post;
+    auto sines = [&](int k, double sv[NW]) {  // sin(k pi w_i), k = 1..KMAX
+        if (NW == 5) load5(G.s5[c.b][k - 1], sv);
+        else sv[0] = G.s5[c.b][k - 1][2];
+    };
     if (code > 0) {  // small-time, src/pdf.pxi:51-57
+        double w[NW];
+        if (NW == 5) load5(G.w5[c.b], w);
+        else w[0] = G.w5[c.b][2];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) p[i] = 0.0;
         const double inv_tt = G.a_sq * rcp_fast(xt);
         const double arg = 0.5 * inv_tt;
         const int K = code;
@@ -211,31 +248,54 @@ __device__ __forceinline__ void grid_node(const GridSet<KMAX>& G, const GridTria
             const double two_k = (double)(2 * k);
 #pragma unroll
             for (int i = 0; i < NW; ++i) {
-                const double u = T.w[NW == 5 ? 4 * i : 8] + two_k;
+                const double u = w[i] + two_k;
                 p[i] = fma(u, exp_tab<true>(-(u * u) * arg, G.etab), p[i]);
             }
         }
         // 1/sqrt(2 pi tt^3) = inv_tt * sqrt(inv_tt / (2 pi))
         post = inv_tt * (inv_tt * rsqrt_fast((2.0 * kPi) * inv_tt));
-    } else {  // large-time, :59-63: terms k q^(k^2) sin(k pi w)
+    } else {  // large-time, :59-63: terms k q^(k^2) sin(k pi w), ascending k
         const int K = -code;
-        const double q2 = q * q;
-        double odd = q, pw = q;
+        double sv[NW];
+        sines(1, sv);
 #pragma unroll
-        for (int k = 1; k <= KMAX; ++k) {
-            if (k <= K) {
-                if (k > 1) {
-                    odd *= q2;
-                    pw *= odd;
+        for (int i = 0; i < NW; ++i) p[i] = q * sv[i];
+        if (K >= 2) {
+            const double q2 = q * q;
+            double odd = q * q2, pw = q * odd;  // q^3, q^4
+            double e = 2.0 * pw;
+            sines(2, sv);
+#pragma unroll
+            for (int i = 0; i < NW; ++i) p[i] = fma(e, sv[i], p[i]);
+            if (K >= 3) {
+                odd *= q2; pw *= odd;  // q^5, q^9
+                e = 3.0 * pw;
+                sines(3, sv);
+#pragma unroll
+                for (int i = 0; i < NW; ++i) p[i] = fma(e, sv[i], p[i]);
+                if (K >= 4) {
+                    odd *= q2; pw *= odd;  // q^7, q^16
+                    e = 4.0 * pw;
+                    sines(4, sv);
+#pragma unroll
+                    for (int i = 0; i < NW; ++i) p[i] = fma(e, sv[i], p[i]);
+                    if (KMAX > 4) {
+                        for (int k = 5; k <= K; ++k) {  // K <= KMAX: the launch picked KMAX >= max K
+                            odd *= q2; pw *= odd;
+                            e = (double)k * pw;
+                            sines(k, sv);
+#pragma unroll
+                            for (int i = 0; i < NW; ++i) p[i] = fma(e, sv[i], p[i]);
+                        }
+                    }
                 }
-                const double e = (double)k * pw;
-#pragma unroll
-                for (int i = 0; i < NW; ++i) p[i] = fma(e, T.s[k - 1][NW == 5 ? 4 * i : 8], p[i]);
             }
         }
         post = kPi;
     }
-    // sv marginal, src/pdf.pxi:85,102
+    // sv marginal, src/pdf.pxi:85,102: exp(((a sv w)^2 - 2 a v w - v^2 x) / (2 sv^2 x + 2)) / sqrt(sv^2 x + 1) / a^2.
+    // The numerator is quadratic in the start-point index (equally spaced w_i), so the five exponentials are
+    // E_0, E_0 g, E_0 g (g r2), ...: three exps and eight multiplications instead of five exps.
     double r = 1.0, d = 0.5;
     const bool sv_zero = G.sv == 0.0;
     if (!sv_zero) {
@@ -243,14 +303,27 @@ __device__ __forceinline__ void grid_node(const GridSet<KMAX>& G, const GridTria
         d = 0.5 * (r * r);
     }
     const double scale = (post * r) * (G.inv_a_sq * G.inv_zt);
-    const double vx = c.v_sq * xt;
+    double E = exp_tab<false>(fma(-c.v_sq, xt, c.c0) * d, G.etab);
+    f[0] = (p[0] * scale) * E;
+    if (NW == 5) {
+        double g = exp_tab<false>(c.dc0 * d, G.etab);
+        const double r2 = exp_tab<false>(G.d2c[c.b] * d, G.etab);
 #pragma unroll
-    for (int i = 0; i < NW; ++i) {
-        const int m = NW == 5 ? i : 2;
-        const double ci = fma(-G.aw2[c.b][m], c.v, G.sw2[c.b][m]);
-        double val = (p[i] * scale) * exp_tab<false>((ci - vx) * d, G.etab);
-        if (!sv_zero && p[i] < 0.0) val = __longlong_as_double(0x7ff8000000000000LL);  // log(p < 0)
-        f[i] = val;
+        for (int i = 1; i < NW; ++i) {
+            E *= g;
+            if (i < NW - 1) g *= r2;
+            f[i] = (p[i] * scale) * E;
+        }
+    }
+    if (!sv_zero) {  // exp(log(p) + ...) with p < 0 is NaN (src/pdf.pxi:102); never seen for err <= 1e-3
+        int neg = __double2hiint(p[0]);
+#pragma unroll
+        for (int i = 1; i < NW; ++i) neg |= __double2hiint(p[i]);
+        if (neg < 0) {
+#pragma unroll
+            for (int i = 0; i < NW; ++i)
+                if (p[i] < 0.0) f[i] = __longlong_as_double(0x7ff8000000000000LL);
+        }
     }
 }
 
@@ -309,15 +382,14 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const double
                                                 const Numerics& nm, const SeriesTable* tab,
                                                 unsigned long long& evals)
 {
-    const double sv = par[1], a = par[2], z = par[3], sz = par[4], t = par[5], st = par[6];
     const double ax = fabs(x);
-    if ((z < 0) || (z > 1) || (a < 0) || (t < 0) || (st < 0) || (sv < 0) || (sz < 0) || (sz > 1) ||
-        ((ax - (t - st / 2.)) < 0) || (z + sz / 2. > 1) || (z - sz / 2. < 0) || (t - st / 2. < 0))
-        return 0.0;
+    if (!G.support || (ax - G.t_onset) < 0) return 0.0;  // src/pdf.pxi:111-113
     GridTrial c;
     c.b = x > 0 ? 1 : 0;
     c.v = c.b ? -v : v;
     c.v_sq = c.v * c.v;
+    c.c0 = fma(-G.aw0[c.b], c.v, G.sw0[c.b]);
+    c.dc0 = fma(-G.daw[c.b], c.v, G.dsw[c.b]);
 
     const double xt_max = ax - G.tn[0];
     // exponent of the sv marginal lies in [-(2 a |v| + v^2 x_t) / 2, w^2 / (2 tt) + a |v|]
@@ -405,7 +477,7 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const double
         }
     }
     if (!ok)  // outside the comfortable range: the v2 evaluator handles every corner
-        return full_pdf_fast<KMAX>(x, v, sv, a, z, sz, t, st, nm, tab, G.wt, evals);
+        return full_pdf_fast<KMAX>(x, v, par[1], par[2], par[3], par[4], par[5], par[6], nm, tab, G.wt, evals);
     evals += n_eval + extra;
     return out;
 }
