@@ -327,51 +327,133 @@ __device__ __forceinline__ void grid_node(const GridSet<KMAX>& G, const GridTria
     }
 }
 
-// Rare: the inner z-integration at decision time xt did not converge on its first level; continue
-// with the v2 walk from the five values already known.
+// The inner z-integration at decision time xt did not converge on its first level
+// (src/integrate.pxi:99-112): walk deeper from the five values already known.  New start points are
+// table nodes m/16 for the next two levels (sines from shared memory), arbitrary below that.
 template <int KMAX>
-__device__ __noinline__ double grid_refine_z(const GridSet<KMAX>& G, const GridTrial& c, double xt,
-                                             const SeriesTable* tab, const double f[5], double coarse,
-                                             double tol, int levels, unsigned long long& evals)
+__device__ __noinline__ double grid_refine_z(const GridSet<KMAX>& G, const GridTrial& c, double xt, int code,
+                                             double q, const double f[5], double coarse, double tol,
+                                             int levels, unsigned long long& evals)
 {
-    TrialCtx tc;
-    tc.a_sq = G.a_sq; tc.inv_a_sq = 1.0 / G.a_sq; tc.sv_sq = G.sv_sq; tc.v_sq = c.v_sq;
-    tc.asv = G.a * G.sv; tc.av2 = (2.0 * G.a) * c.v; tc.tab = tab; tc.sv_zero = G.sv == 0.0;
-    tc.inv_zt = 1.0 / G.zw;
-    const TimeNode n = make_time_node(tc, xt);
-    return refine_z<KMAX>(tc, G.wt[c.b], n, f, coarse, tol, levels, evals);
+    double post, qa;
+    if (code > 0) {
+        const double inv_tt = G.a_sq * rcp_fast(xt);
+        qa = 0.5 * inv_tt;
+        post = inv_tt * (inv_tt * rsqrt_fast((2.0 * kPi) * inv_tt));
+    } else {
+        qa = q;
+        post = kPi;
+    }
+    double r = 1.0, d = 0.5;
+    const bool sv_zero = G.sv == 0.0;
+    if (!sv_zero) {
+        r = rsqrt_fast(fma(G.sv_sq, xt, 1.0));
+        d = 0.5 * (r * r);
+    }
+    const double scale = (post * r) * (G.inv_a_sq * G.inv_zt);
+    const double vx = c.v_sq * xt;
+    const double asv = G.a * G.sv, av2 = (2.0 * G.a) * c.v;
+    const WTable<KMAX>& T = G.wt[c.b];
+    unsigned long long extra = 0;
+    auto g = [&](double w, int pos) {
+        extra++;
+        const int m = (pos & ((1 << kPosShift) - 1)) == 0 ? (pos >> kPosShift) : -1;
+        double p = 0.0;
+        if (code > 0) {
+            const int K = code;
+            for (int k = -((K - 1) / 2); k <= K / 2; ++k) {
+                const double u = w + (double)(2 * k);
+                p = fma(u, exp_tab<true>(-(u * u) * qa, G.etab), p);
+            }
+        } else {
+            const int K = -code;
+            const double q2 = qa * qa;
+            double odd = qa, pw = qa;
+            for (int k = 1; k <= K; ++k) {
+                if (k > 1) {
+                    odd *= q2;
+                    pw *= odd;
+                }
+                const double kd = (double)k;
+                const double sn = (m >= 0 && k <= KMAX) ? T.s[k - 1][m] : sin((kd * kPi) * w);
+                p = fma(kd * pw, sn, p);
+            }
+        }
+        const double t1 = asv * w;
+        double val = (p * scale) * exp_tab<false>((fma(t1, t1, -av2 * w) - vx) * d, G.etab);
+        if (!sv_zero && p < 0.0) val = __longlong_as_double(0x7ff8000000000000LL);
+        return val;
+    };
+    Span stack[kMaxDepth];
+    Span top;
+    top.lo = T.w[0]; top.hi = T.w[16]; top.coarse = coarse;
+    top.f_lo = f[0]; top.f_hi = f[4]; top.f_mid = f[2];
+    top.tol = tol; top.levels = levels; top.ilo = 0; top.ihi = kPosWidth;
+    const double res = simpson_walk(g, top, true, f[1], f[3], stack);
+    evals += extra;
+    return res;
 }
 
-// Rare: the outer t-integration did not converge on its first level; continue with the v2 walk.
+// Trials outside the comfortable range: the v2 evaluator handles every corner (one out-of-line copy).
+template <int KMAX>
+__device__ __noinline__ double grid_fallback(double x, double v, const double par[7], const GridSet<KMAX>& G,
+                                             const Numerics& nm, const SeriesTable* tab,
+                                             unsigned long long& evals)
+{
+    return full_pdf_fast<KMAX>(x, v, par[1], par[2], par[3], par[4], par[5], par[6], nm, tab, G.wt, evals);
+}
+
+// adaptiveSimpsons_1D over z at decision time xt (src/integrate.pxi:114-141), already / ZT -- or pdf_sv at
+// the set's own start point when sz == 0.  xt is positive and inside the comfortable range.
+template <int KMAX>
+__device__ __forceinline__ double grid_inner(const GridSet<KMAX>& G, const GridTrial& c, double xt, int code,
+                                             double q, const Numerics& nm, const SeriesTable* tab,
+                                             unsigned long long& extra)
+{
+    if (G.sz != 0) {
+        double f[5];
+        grid_node<KMAX, 5>(G, c, xt, code, q, f);
+        const double coarse = G.zw6 * ((f[0] + 4.0 * f[2]) + f[4]);
+        const double left = G.zw12 * ((f[0] + 4.0 * f[1]) + f[2]);
+        const double right = G.zw12 * ((f[2] + 4.0 * f[3]) + f[4]);
+        const double fine = left + right;
+        if (nm.n_sz <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err) return fma(fine - coarse, 1.0 / 15.0, fine);
+        return grid_refine_z<KMAX>(G, c, xt, code, q, f, coarse, nm.simps_err, nm.n_sz, extra);
+    }
+    double f[1];
+    grid_node<KMAX, 1>(G, c, xt, code, q, f);
+    return f[0];
+}
+
+// The outer t-integration did not converge on its first level (src/integrate.pxi:170-178): walk deeper
+// with the same node evaluator.  *bad is set when a node leaves the comfortable range.
 template <int KMAX>
 __device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridTrial& c, double ax,
                                              const Numerics& nm, const SeriesTable* tab, const double F[5],
-                                             double coarse, unsigned long long& evals)
+                                             double coarse, unsigned long long& evals, bool* bad)
 {
-    TrialCtx tc;
-    tc.a_sq = G.a_sq; tc.inv_a_sq = 1.0 / G.a_sq; tc.sv_sq = G.sv_sq; tc.v_sq = c.v_sq;
-    tc.asv = G.a * G.sv; tc.av2 = (2.0 * G.a) * c.v; tc.tab = tab; tc.sv_zero = G.sv == 0.0;
-    const WTable<KMAX>& T = G.wt[c.b];
-    const bool over_z = G.sz != 0;
-    tc.inv_zt = over_z ? 1.0 / G.zw : 1.0;
-    if (over_z) {
-#pragma unroll
-        for (int i = 0; i < 5; ++i) {
-            const double w = T.w[4 * i], t1 = tc.asv * w;
-            tc.c5[i] = t1 * t1 - tc.av2 * w;
-        }
-    }
-    const double width = G.tw;
+    const unsigned int per_node = G.sz != 0 ? 5 : 1;
+    bool out_of_range = false;
     auto g = [&](double tn, int) {
-        return (over_z ? inner_z<KMAX>(tc, T, ax - tn, nm.simps_err, nm.n_sz, evals)
-                       : single_z<KMAX>(tc, T, ax - tn, evals)) / width;
+        const double xt = ax - tn;
+        evals += per_node;
+        if (!(xt > 0.0)) return 0.0;  // src/pdf.pxi:92-93
+        if (xt < G.xt_lo) {
+            out_of_range = true;
+            return 0.0;
+        }
+        const int code = grid_code(G, xt);
+        const double q = code < 0 ? exp_tab<false>(G.qk * xt, G.etab) : 0.0;
+        return grid_inner<KMAX>(G, c, xt, code, q, nm, tab, evals) * G.inv_st;
     };
     Span top;
     top.lo = G.tn[0]; top.hi = G.tn[4]; top.coarse = coarse;
     top.f_lo = F[0]; top.f_hi = F[4]; top.f_mid = F[2];
     top.tol = nm.simps_err; top.levels = nm.n_st; top.ilo = 0; top.ihi = kPosWidth;
     Span stack[kMaxDepth];
-    return simpson_walk(g, top, true, F[1], F[3], stack);
+    const double r = simpson_walk(g, top, true, F[1], F[3], stack);
+    *bad = out_of_range;
+    return r;
 }
 
 // full_pdf (src/pdf.pxi:104-146) for one trial of the CTA's set.  par = raw v, sv, a, z, sz, t, st of
@@ -409,24 +491,8 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const double
                 ok = false;
             } else {
                 const int code = grid_code(G, xt);
-                if (over_z) {
-                    double f[5];
-                    grid_node<KMAX, 5>(G, c, xt, code, q0, f);
-                    n_eval = 5;
-                    const double coarse = G.zw6 * ((f[0] + 4.0 * f[2]) + f[4]);
-                    const double left = G.zw12 * ((f[0] + 4.0 * f[1]) + f[2]);
-                    const double right = G.zw12 * ((f[2] + 4.0 * f[3]) + f[4]);
-                    const double fine = left + right;
-                    if (nm.n_sz <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err)
-                        out = fma(fine - coarse, 1.0 / 15.0, fine);
-                    else
-                        out = grid_refine_z<KMAX>(G, c, xt, tab, f, coarse, nm.simps_err, nm.n_sz, extra);
-                } else {
-                    double f[1];
-                    grid_node<KMAX, 1>(G, c, xt, code, q0, f);
-                    n_eval = 1;
-                    out = f[0];
-                }
+                n_eval = over_z ? 5 : 1;
+                out = grid_inner<KMAX>(G, c, xt, code, q0, nm, tab, extra);
             }
         } else {  // :131-134, :143-146: five decision times, then the outer Simpson level
             double F[5];
@@ -445,22 +511,7 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const double
                     if (xt < G.xt_lo) ok = false;
                     const int code = uniform ? code_hi : grid_code(G, xt);
                     const double q = q0 * G.rho[j];
-                    if (over_z) {
-                        double f[5];
-                        grid_node<KMAX, 5>(G, c, xt, code, q, f);
-                        const double coarse = G.zw6 * ((f[0] + 4.0 * f[2]) + f[4]);
-                        const double left = G.zw12 * ((f[0] + 4.0 * f[1]) + f[2]);
-                        const double right = G.zw12 * ((f[2] + 4.0 * f[3]) + f[4]);
-                        const double fine = left + right;
-                        if (nm.n_sz <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err)
-                            val = fma(fine - coarse, 1.0 / 15.0, fine);
-                        else if (ok)
-                            val = grid_refine_z<KMAX>(G, c, xt, tab, f, coarse, nm.simps_err, nm.n_sz, extra);
-                    } else {
-                        double f[1];
-                        grid_node<KMAX, 1>(G, c, xt, code, q, f);
-                        val = f[0];
-                    }
+                    if (ok) val = grid_inner<KMAX>(G, c, xt, code, q, nm, tab, extra);
                 }
                 F[j] = val * G.inv_st;
             }
@@ -471,13 +522,15 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const double
                 const double fine = left + right;
                 if (nm.n_st <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err)
                     out = fma(fine - coarse, 1.0 / 15.0, fine);
-                else
-                    out = grid_refine_t<KMAX>(G, c, ax, nm, tab, F, coarse, extra);
+                else {
+                    bool bad = false;
+                    out = grid_refine_t<KMAX>(G, c, ax, nm, tab, F, coarse, extra, &bad);
+                    ok = !bad;
+                }
             }
         }
     }
-    if (!ok)  // outside the comfortable range: the v2 evaluator handles every corner
-        return full_pdf_fast<KMAX>(x, v, par[1], par[2], par[3], par[4], par[5], par[6], nm, tab, G.wt, evals);
+    if (!ok) return grid_fallback<KMAX>(x, v, par, G, nm, tab, evals);
     evals += n_eval + extra;
     return out;
 }
