@@ -113,6 +113,7 @@ struct alignas(16) GridSet {
     double inv_zt, inv_st; // 1/(ub_z - lb_z) (1 when sz == 0), 1/(ub_t - lb_t)
     double zw, zw6, zw12;  // ub_z - lb_z, and that / 6, / 12 (src/integrate.pxi:99-100,137)
     double tw, tw6, tw12;  // ub_t - lb_t, / 6, / 12
+    double raw[7];         // the set's v, sv, a, z, sz, t, st as given (for the out-of-range fallback)
 };
 
 // Smallest double X with fl(X / a_sq) >= thr (thr and thr * a_sq normal and positive).
@@ -136,6 +137,7 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
     const double sz = par[4] < 1e-3 ? 0.0 : par[4];
     const double tt_lo = 1.0 / 512.0, tt_hi = 128.0;
     if (tid < kExpTab) G.etab[tid] = g_exp2_tab[tid];
+    if (tid >= 72 && tid < 79) G.raw[tid - 72] = par[tid - 72];
     if (tid == 64) {
         const double lo = par[5] - st / 2., hi = par[5] + st / 2.;
         const double c = (lo + hi) / 2.;
@@ -396,11 +398,11 @@ __device__ __noinline__ double grid_refine_z(const GridSet<KMAX>& G, const GridT
 
 // Trials outside the comfortable range: the v2 evaluator handles every corner (one out-of-line copy).
 template <int KMAX>
-__device__ __noinline__ double grid_fallback(double x, double v, const double par[7], const GridSet<KMAX>& G,
-                                             const Numerics& nm, const SeriesTable* tab,
-                                             unsigned long long& evals)
+__device__ __noinline__ double grid_fallback(double x, double v, const GridSet<KMAX>& G, const Numerics& nm,
+                                             const SeriesTable* tab, unsigned long long& evals)
 {
-    return full_pdf_fast<KMAX>(x, v, par[1], par[2], par[3], par[4], par[5], par[6], nm, tab, G.wt, evals);
+    return full_pdf_fast<KMAX>(x, v, G.raw[1], G.raw[2], G.raw[3], G.raw[4], G.raw[5], G.raw[6], nm, tab, G.wt,
+                               evals);
 }
 
 // adaptiveSimpsons_1D over z at decision time xt (src/integrate.pxi:114-141), already / ZT -- or pdf_sv at
@@ -456,11 +458,10 @@ __device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridT
     return r;
 }
 
-// full_pdf (src/pdf.pxi:104-146) for one trial of the CTA's set.  par = raw v, sv, a, z, sz, t, st of
-// the set; v may differ per trial.  Returns through the v2 evaluator when the trial is outside the
+// full_pdf (src/pdf.pxi:104-146) for one trial of the CTA's set (v may differ per trial).  Returns through the v2 evaluator when the trial is outside the
 // comfortable range (normalised time outside [2^-9, 128], extreme drift, NaN).
 template <int KMAX>
-__device__ __forceinline__ double full_pdf_grid(double x, double v, const double par[7], const GridSet<KMAX>& G,
+__device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSet<KMAX>& G,
                                                 const Numerics& nm, const SeriesTable* tab,
                                                 unsigned long long& evals)
 {
@@ -530,7 +531,7 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const double
             }
         }
     }
-    if (!ok) return grid_fallback<KMAX>(x, v, par, G, nm, tab, evals);
+    if (!ok) return grid_fallback<KMAX>(x, v, G, nm, tab, evals);
     evals += n_eval + extra;
     return out;
 }

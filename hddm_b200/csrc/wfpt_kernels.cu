@@ -78,21 +78,34 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         build_wtables<KT>(wt, par[3], par[4]);
 
     auto density = [&](double x, unsigned long long& ev) {
-        if (GRID) return full_pdf_grid<KT>(x, par[0], par, gs, a.nm, &a.tab, ev);
+        if (GRID) return full_pdf_grid<KT>(x, par[0], gs, a.nm, &a.tab, ev);
         if (KMAX > 0)
             return full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(x, par[0], par[1], par[2], par[3], par[4], par[5],
                                                         par[6], a.nm, &a.tab, wt, ev);
         return full_pdf(x, par[0], par[1], par[2], par[3], par[4], par[5], par[6], a.nm, &a.tab, ev);
     };
 
-    double acc = 0.0;
+    // sum of log(d) = log(prod of mantissas) + ln2 * (sum of exponents) for normal positive d: one log
+    // per thread instead of one per trial; anything else (0, negative, NaN, inf, subnormal) takes log().
+    double acc = 0.0, mant = 1.0;
+    int expo = 0;
+    auto add_log = [&](double d) {
+        const int hi = __double2hiint(d);
+        if ((unsigned)(hi - 0x00100000) < 0x7fe00000u) {
+            expo += (hi >> 20) - 1023;
+            mant *= __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(d));
+        } else {
+            acc += log(d);
+        }
+    };
+    static_assert(kTrialsPerBlock / kLikeThreads <= 512, "mantissa product must stay finite");
     unsigned long long evals = 0;
     bool hit_zero = false;
     for (int64_t i = begin + threadIdx.x; i < end; i += kLikeThreads) {
         const double x = __ldg(a.x + i);
         if (per_trial) {
 #pragma unroll
-            for (int k = 0; k < 7; ++k)
+            for (int k = 0; k < (GRID ? 1 : 7); ++k)  // GRID: only the drift can vary per trial
                 if (a.trial_stride[k] != 0) par[k] = load_par(a, k, p, i);
         }
         double d;
@@ -101,19 +114,20 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
                 d = density(x, evals);
                 d = d * (1 - p_out) + w_out * p_out;
             } else if (x == 999.) {  // :267-268
-                d = prob_ub(par[0], par[2], par[3]);
+                d = prob_ub(par[0], GRID ? gs.raw[2] : par[2], GRID ? gs.raw[3] : par[3]);
             } else {  // :269-270
-                d = 1 - prob_ub(par[0], par[2], par[3]);
+                d = 1 - prob_ub(par[0], GRID ? gs.raw[2] : par[2], GRID ? gs.raw[3] : par[3]);
             }
-            acc += log(d);
+            add_log(d);
         } else {
             if (a.mode == kModeContaminant && a.cont[i] != 0) continue;  // src/wfpt.pyx:374
             d = density(x, evals);
             d = d * (1 - p_out) + w_out * p_out;  // src/wfpt.pyx:70 (contaminant: p_out = 0)
             hit_zero |= (d == 0);                 // :71-72, :377-379
-            acc += log(d);
+            add_log(d);
         }
     }
+    acc += fma((double)expo, 0.693147180559945309417, log(mant));
 
     __shared__ double warp_part[kLikeThreads / 32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -198,7 +212,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
         double d;
         if (GRID)
-            d = full_pdf_grid<KT>(__ldg(a.x + i), a.par[0], a.par, gs, a.nm, &a.tab, evals);
+            d = full_pdf_grid<KT>(__ldg(a.x + i), a.par[0], gs, a.nm, &a.tab, evals);
         else if (KMAX > 0)
             d = full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(__ldg(a.x + i), a.par[0], a.par[1], a.par[2], a.par[3],
                                                      a.par[4], a.par[5], a.par[6], a.nm, &a.tab, wt, evals);
