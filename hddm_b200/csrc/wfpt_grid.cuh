@@ -47,8 +47,8 @@ __device__ const double g_exp2_tab[kExpTab] = {
     0x1.d5818dcfba487p+0, 0x1.da9e603db3285p+0, 0x1.dfc97337b9b5fp+0, 0x1.e502ee78b3ff6p+0,
     0x1.ea4afa2a490dap+0, 0x1.efa1bee615a27p+0, 0x1.f50765b6e4540p+0, 0x1.fa7c1819e90d8p+0};
 
-// exp(x) for -700 <= x <= 700 (CLAMP: any x <= 700; results below 2^-1000 come out as ~2^-1000 * m,
-// used only where such a term is added to one that is larger by hundreds of orders of magnitude).
+// exp(x) for -700 <= x <= 700 (CLAMP: -2e7 <= x <= 700; results below 2^-1021 come out as exactly 0,
+// used only where such a term is added to one that is larger by tens of orders of magnitude).
 // x = (64 n' + i) ln2/64 + r, |r| <= ln2/128: exp(x) = 2^n' * T[i] * (1 + r + r^2/2 + ... + r^5/120).
 template <bool CLAMP>
 __device__ __forceinline__ double exp_tab(double x, const double* __restrict__ T)
@@ -66,9 +66,10 @@ __device__ __forceinline__ double exp_tab(double x, const double* __restrict__ T
     const double p = fma(r2, c, r);
     const double tv = T[n & (kExpTab - 1)];
     const double m = fma(tv, p, tv);
-    int e = n >> 6;
-    if (CLAMP) e = max(e, -1000);
-    return __hiloint2double(__double2hiint(m) + (e << 20), __double2loint(m));
+    const int e = n >> 6;
+    int hi = __double2hiint(m) + (e << 20), lo = __double2loint(m);
+    if (CLAMP && e < -1021) hi = lo = 0;  // below the normal range: exactly 0
+    return __hiloint2double(hi, lo);
 }
 
 // 1/sqrt(y), y normal and positive: MUFU seed (~2^-20) + one cubic step (error ~ 5/16 e^3 < 1e-17).
@@ -101,13 +102,17 @@ struct alignas(16) GridSet {
     // sv-marginal exponent numerator c(w) = (a sv w)^2 - 2 a v w at the start points, as a function of
     // the drift: c_0 = sw0 - aw0 v, c_1 - c_0 = dsw - daw v, second difference d2c (free of v)
     double sw0[2], aw0[2], dsw[2], daw[2], d2c[2];
+    // small-time chain (see grid_node): w_0^2, w_1^2 - w_0^2, second difference of w_i^2, w_0 + 1,
+    // 1 - w_4 per boundary; hw = w_1 - w_0; chain_ok: start points well inside (0, 1)
+    double w0sq[2], dw1[2], d2w[2], w0p1[2], omw4[2], hw;
+    int chain_ok[2];
     unsigned long long xwin[kThrWin];  // bit patterns of xthr inside the window, padded with +inf
     int code[kMaxRegions];
     int region0;           // thresholds below the window (always passed)
     int ok;                // 0: the grid evaluator cannot be used for this set
     int support;           // the set-level part of the support test of src/pdf.pxi:111-113 passed
     double t_onset;        // t - st/2 with the raw st (the per-trial part of that test)
-    double xt_lo, xt_hi;   // comfortable decision-time range [a^2/512, 128 a^2]
+    double xt_lo[2], xt_hi;  // comfortable decision-time range per boundary, see build_gridset
     double a, sv, t, st, sz;  // st, sz after the 1e-3 snap of src/pdf.pxi:122-125
     double a_sq, inv_a_sq, sv_sq, qk;  // qk = -pi^2 / (2 a^2)
     double inv_zt, inv_st; // 1/(ub_z - lb_z) (1 when sz == 0), 1/(ub_t - lb_t)
@@ -135,7 +140,7 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
     const double a_sq = a * a;
     const double st = par[6] < 1e-3 ? 0.0 : par[6];
     const double sz = par[4] < 1e-3 ? 0.0 : par[4];
-    const double tt_lo = 1.0 / 512.0, tt_hi = 128.0;
+    const double tt_lo = 1.0 / 1048576.0, tt_hi = 128.0;
     if (tid < kExpTab) G.etab[tid] = g_exp2_tab[tid];
     if (tid >= 72 && tid < 79) G.raw[tid - 72] = par[tid - 72];
     if (tid == 64) {
@@ -150,7 +155,14 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
         G.tw = hi - lo; G.tw6 = G.tw / 6.0; G.tw12 = G.tw / 12.0;
         G.inv_zt = sz == 0 ? 1.0 : 1.0 / G.zw;
         G.inv_st = st == 0 ? 1.0 : 1.0 / (hi - lo);
-        G.xt_lo = tt_lo * a_sq;  // exact (power of two) unless it leaves the normal range
+        // Comfortable range of normalised time: [max(2^-20, w_0^2 / 1300), 128].  Lower end: the largest
+        // small-time term exp(-w_0^2 / (2 tt)) stays above e^-650 (every term that underflows is then < 1e-25 of
+        // it) and exp arguments stay above -2e7; upper end: q = exp(-pi^2 tt / 2) stays normal.
+        for (int b = 0; b < 2; ++b) {
+            const double w0 = G.wt[b].w[0];
+            const double lo_b = (w0 * w0) / 1300.0;
+            G.xt_lo[b] = (lo_b > tt_lo ? lo_b : tt_lo) * a_sq;
+        }
         G.xt_hi = tt_hi * a_sq;
         // window of thresholds inside (tt_lo, tt_hi]
         int r0 = 0, nwin = 0;
@@ -166,7 +178,11 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
             G.t_onset = t - str / 2.;
         }
         // a in a sane range keeps every product below normal and finite
-        G.ok = (nwin <= kThrWin - 1) && (a_sq >= 1e-100) && (a_sq <= 1e100) && (tab.n_thr >= 0) ? 1 : 0;
+        // and the positive part of the sv-marginal exponent, (a sv w)^2 / (2 sv^2 x + 2) <= (a sv w_4)^2 / 2, stays small
+        const double wmax = G.wt[0].w[16] > G.wt[1].w[16] ? G.wt[0].w[16] : G.wt[1].w[16];
+        const double asw = (a * sv) * wmax;
+        G.ok = (nwin <= kThrWin - 1) && (a_sq >= 1e-100) && (a_sq <= 1e100) && (tab.n_thr >= 0) &&
+               (asw * asw <= 600.0) ? 1 : 0;
     }
     if (tid >= 96 && tid < 96 + kMaxRegions) G.code[tid - 96] = tid - 96 <= tab.n_thr ? tab.code[tid - 96] : 0;
     if (tid >= 128 && tid < 130) {
@@ -182,6 +198,16 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
         G.dsw[b] = sw[1] - sw[0]; G.daw[b] = aw[1] - aw[0];
         G.d2c[b] = (sw[2] - sw[1]) - (sw[1] - sw[0]);
         for (int i = 0; i < 6; ++i) G.w5[b][i] = i < 5 ? G.wt[b].w[4 * i] : 0.0;
+        {
+            const double w0 = G.wt[b].w[0], w1 = G.wt[b].w[4], w2 = G.wt[b].w[8], w4 = G.wt[b].w[16];
+            G.w0sq[b] = w0 * w0;
+            G.dw1[b] = (w1 - w0) * (w1 + w0);
+            G.d2w[b] = (w2 - w1) * (w2 + w1) - (w1 - w0) * (w1 + w0);
+            G.w0p1[b] = w0 + 1.0;
+            G.omw4[b] = 1.0 - w4;
+            if (b == 0) G.hw = w1 - w0;
+            G.chain_ok[b] = (w0 >= 0.01) && (w4 <= 0.99) ? 1 : 0;
+        }
     }
     if (tid >= 160 && tid < 160 + 2 * KMAX * 6) {
         const int r = tid - 160, b = r / (KMAX * 6), k = (r / 6) % KMAX, i = r % 6;
@@ -246,12 +272,65 @@ __device__ __forceinline__ void grid_node(const GridSet<KMAX>& G, const GridTria
         const double inv_tt = G.a_sq * rcp_fast(xt);
         const double arg = 0.5 * inv_tt;
         const int K = code;
-        for (int k = -((K - 1) / 2); k <= K / 2; ++k) {
-            const double two_k = (double)(2 * k);
+        if (NW == 5 && K <= 5 && G.chain_ok[c.b]) {
+            // exp(-g (w_i + 2k)^2) = A_i R_{k,i} with A_i = exp(-g w_i^2) and R_{k,i} = exp(-4 g k (w_i + k)) <= 1.
+            // The w_i are equally spaced, so A_i is a quadratic chain (3 exps), R_{1,i} and R_{-1,i} are geometric
+            // in i with ratio eta = exp(-4 g h) (3 exps), R_{+-2,i} = R_{+-1,i}^2 exp(-8 g) (1 exp): 7 exps instead
+            // of 5 K.  A side whose largest ratio is below e^-60 cannot change the sum (it is < 1e-23 of the
+            // k = 0 term) and is skipped.
+            const int b = c.b;
+            double A = exp_tab<false>(-arg * G.w0sq[b], G.etab);
+            double ga = exp_tab<true>(-arg * G.dw1[b], G.etab);
+            const double de = exp_tab<true>(-arg * G.d2w[b], G.etab);
+            const double g4 = 4.0 * arg;
+            const bool pos = g4 * G.w0p1[b] <= 60.0;            // k = 1 (and 2)
+            const bool neg = K >= 3 && g4 * G.omw4[b] <= 60.0;  // k = -1 (and -2)
+            double t[5];
 #pragma unroll
-            for (int i = 0; i < NW; ++i) {
-                const double u = w[i] + two_k;
-                p[i] = fma(u, exp_tab<true>(-(u * u) * arg, G.etab), p[i]);
+            for (int i = 0; i < 5; ++i) t[i] = w[i];
+            if (pos || neg) {
+                const double eta = exp_tab<true>(-g4 * G.hw, G.etab);
+                double C2 = 0.0;
+                if (K >= 4) {
+                    const double C = exp_tab<true>(-g4, G.etab);
+                    C2 = C * C;
+                }
+                if (neg) {  // the reference adds k ascending; negative k first
+                    double R = exp_tab<true>(-g4 * G.omw4[b], G.etab);
+#pragma unroll
+                    for (int i = 4; i >= 0; --i) {
+                        double u = (w[i] - 2.0) * R;
+                        if (K >= 5) u = fma(w[i] - 4.0, (R * R) * C2, u);
+                        t[i] = u + t[i];
+                        if (i > 0) R *= eta;
+                    }
+                }
+                if (pos) {
+                    double R = exp_tab<true>(-g4 * G.w0p1[b], G.etab);
+#pragma unroll
+                    for (int i = 0; i < 5; ++i) {
+                        t[i] = fma(w[i] + 2.0, R, t[i]);
+                        if (K >= 4) t[i] = fma(w[i] + 4.0, (R * R) * C2, t[i]);
+                        if (i < 4) R *= eta;
+                    }
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 5; ++i) {
+                p[i] = A * t[i];
+                if (i < 4) {
+                    A *= ga;
+                    ga *= de;
+                }
+            }
+        } else {
+            for (int k = -((K - 1) / 2); k <= K / 2; ++k) {
+                const double two_k = (double)(2 * k);
+#pragma unroll
+                for (int i = 0; i < NW; ++i) {
+                    const double u = w[i] + two_k;
+                    p[i] = fma(u, exp_tab<true>(-(u * u) * arg, G.etab), p[i]);
+                }
             }
         }
         // 1/sqrt(2 pi tt^3) = inv_tt * sqrt(inv_tt / (2 pi))
@@ -440,7 +519,7 @@ __device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridT
         const double xt = ax - tn;
         evals += per_node;
         if (!(xt > 0.0)) return 0.0;  // src/pdf.pxi:92-93
-        if (xt < G.xt_lo) {
+        if (xt < G.xt_lo[c.b]) {
             out_of_range = true;
             return 0.0;
         }
@@ -475,8 +554,8 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
     c.dc0 = fma(-G.daw[c.b], c.v, G.dsw[c.b]);
 
     const double xt_max = ax - G.tn[0];
-    // exponent of the sv marginal lies in [-(2 a |v| + v^2 x_t) / 2, w^2 / (2 tt) + a |v|]
-    bool ok = G.ok && (xt_max <= G.xt_hi) && (fma(c.v_sq, xt_max, (2.0 * G.a) * fabs(c.v)) <= 800.0) &&
+    // exponent of the sv marginal lies in [-(2 a |v| + v^2 x_t) / 2, (a sv w_4)^2 / 2 + a |v|]
+    bool ok = G.ok && (xt_max <= G.xt_hi) && (fma(c.v_sq, xt_max, (2.0 * G.a) * fabs(c.v)) <= 600.0) &&
               (nm.simps_err >= 0.0);
     unsigned int n_eval = 0;
     unsigned long long extra = 0;
@@ -488,7 +567,7 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
             const double xt = ax - G.t;
             if (xt <= 0.0) {
                 n_eval = over_z ? 5 : 1;  // src/pdf.pxi:92-93
-            } else if (xt < G.xt_lo) {
+            } else if (xt < G.xt_lo[c.b]) {
                 ok = false;
             } else {
                 const int code = grid_code(G, xt);
@@ -509,7 +588,7 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
                 n_eval += over_z ? 5 : 1;
                 double val = 0.0;
                 if (xt > 0.0) {
-                    if (xt < G.xt_lo) ok = false;
+                    if (xt < G.xt_lo[c.b]) ok = false;
                     const int code = uniform ? code_hi : grid_code(G, xt);
                     const double q = q0 * G.rho[j];
                     if (ok) val = grid_inner<KMAX>(G, c, xt, code, q, nm, tab, extra);
