@@ -506,6 +506,15 @@ __device__ __forceinline__ double grid_inner(const GridSet<KMAX>& G, const GridT
     return f[0];
 }
 
+// Out-of-line copy for the paths outside the five-node loop (keeps the instruction footprint small).
+template <int KMAX>
+__device__ __noinline__ double grid_inner_ool(const GridSet<KMAX>& G, const GridTrial& c, double xt, int code,
+                                              double q, const Numerics& nm, const SeriesTable* tab,
+                                              unsigned long long& extra)
+{
+    return grid_inner<KMAX>(G, c, xt, code, q, nm, tab, extra);
+}
+
 // The outer t-integration did not converge on its first level (src/integrate.pxi:170-178): walk deeper
 // with the same node evaluator.  *bad is set when a node leaves the comfortable range.
 template <int KMAX>
@@ -525,7 +534,7 @@ __device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridT
         }
         const int code = grid_code(G, xt);
         const double q = code < 0 ? exp_tab<false>(G.qk * xt, G.etab) : 0.0;
-        return grid_inner<KMAX>(G, c, xt, code, q, nm, tab, evals) * G.inv_st;
+        return grid_inner_ool<KMAX>(G, c, xt, code, q, nm, tab, evals) * G.inv_st;
     };
     Span top;
     top.lo = G.tn[0]; top.hi = G.tn[4]; top.coarse = coarse;
@@ -572,7 +581,7 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
             } else {
                 const int code = grid_code(G, xt);
                 n_eval = over_z ? 5 : 1;
-                out = grid_inner<KMAX>(G, c, xt, code, q0, nm, tab, extra);
+                out = grid_inner_ool<KMAX>(G, c, xt, code, q0, nm, tab, extra);
             }
         } else {  // :131-134, :143-146: five decision times, then the outer Simpson level
             double F[5];
