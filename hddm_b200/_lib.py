@@ -50,6 +50,8 @@ SIGNATURES = {
     "hddm_trials_free": (_i, [_v]),
     "hddm_trials_wiener_like": (_i, [_v] + [_d] * 7 + _NUM + [_d, _d, c_dp]),
     "hddm_trials_wiener_like_batch": (_i, [_v, c_lp, c_dp, _l] + _NUM + [c_dp, c_up]),
+    "hddm_wiener_like_nodes": (_i, [c_dp, _l, c_lp, _l, c_lp, c_dp, _l] + _NUM + [c_dp, c_up]),
+    "hddm_trials_wiener_like_nodes": (_i, [_v, c_lp, _l, c_lp, c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_wiener_like_batch_scratch": (_l, [_l, _l]),
     "hddm_wiener_like_batch_dev": (_i, [_v, _l, _v, _l, _v, _l] + _NUM + [_v, _v, _v, _v]),
     "hddm_pdf_array_dev": (_i, [_v, _l] + [_d] * 7 + [_d, _i, _i, _i, _i, _d, _d, _d, _v, _v, _v]),

@@ -141,8 +141,8 @@ struct ParSpec {
 
 // Core of every "sum of log densities" entry point.  x is either a host buffer (h_x) staged
 // into the arena or already device-resident (d_x).
-int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_seg,
-              const int32_t* h_cont, const Upload* uploads, int n_uploads, const ParSpec spec[kNumPar],
+int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_seg, int64_t n_seg,
+              const int64_t* h_node, const int32_t* h_cont, const Upload* uploads, int n_uploads, const ParSpec spec[kNumPar],
               int64_t P, int mode, const Numerics& nm, double* logp, unsigned long long* evals)
 {
     if (n < 0 || P < 0 || (n > 0 && !h_x && !d_x) || (P > 0 && !logp))
@@ -154,12 +154,18 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     int64_t max_len = n;
     if (h_seg) {
         max_len = 0;
-        for (int64_t p = 0; p < P; ++p) {
+        for (int64_t p = 0; p < n_seg; ++p) {
             const int64_t len = h_seg[p + 1] - h_seg[p];
             if (len < 0 || h_seg[p] < 0 || h_seg[p + 1] > n)
                 return fail(HDDM_ERR_ARG, "batch: segment offsets must be ascending within [0, n]");
             if (len > max_len) max_len = len;
         }
+        if (h_node)
+            for (int64_t p = 0; p < P; ++p)
+                if (h_node[p] < 0 || h_node[p] >= n_seg)
+                    return fail(HDDM_ERR_ARG, "batch: set_node entries must index a segment");
+    } else if (h_node) {
+        return fail(HDDM_ERR_ARG, "batch: set_node needs segment offsets");
     }
     const int64_t chunks = chunks_for(max_len);
     if (chunks > 65535) return fail(HDDM_ERR_ARG, "more than 65535*2048 trials per parameter set");
@@ -168,14 +174,15 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     // Shared-parameter sums are order-independent: lay the trials out by |rt| (sort_kernels.cu).
     bool sortable = g_sort_trials && h_x && mode == kModeWienerLike && !h_cont && n >= kSortMin;
     for (int k = 0; k < 7; ++k) sortable = sortable && spec[k].trial_stride == 0;
-    const size_t sort_bytes = sortable ? sort_trials_scratch_bytes(n, h_seg ? P : 0) : 0;
+    const size_t sort_bytes = sortable ? sort_trials_scratch_bytes(n, h_seg ? n_seg : 0) : 0;
 
     Layout L;
     const size_t off_x = h_x ? L.reserve((size_t)n * sizeof(double)) : 0;
     const size_t off_xs = sortable ? L.reserve((size_t)n * sizeof(double)) : 0;
     const size_t off_sort = sortable ? L.reserve(sort_bytes) : 0;
     const size_t off_cont = h_cont ? L.reserve((size_t)n * sizeof(int32_t)) : 0;
-    const size_t off_seg = h_seg ? L.reserve((size_t)(P + 1) * sizeof(int64_t)) : 0;
+    const size_t off_seg = h_seg ? L.reserve((size_t)(n_seg + 1) * sizeof(int64_t)) : 0;
+    const size_t off_node = h_node ? L.reserve((size_t)P * sizeof(int64_t)) : 0;
     size_t off_up[8];
     for (int u = 0; u < n_uploads; ++u) off_up[u] = L.reserve(uploads[u].bytes);
     const size_t off_partial = L.reserve((size_t)P * chunks * sizeof(double));
@@ -189,7 +196,9 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     if (h_cont && n > 0)
         CUDA_TRY(cudaMemcpyAsync(L.at<int32_t>(off_cont), h_cont, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
     if (h_seg)
-        CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_seg), h_seg, (size_t)(P + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+        CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_seg), h_seg, (size_t)(n_seg + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    if (h_node)
+        CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_node), h_node, (size_t)P * sizeof(int64_t), cudaMemcpyHostToDevice, s));
     for (int u = 0; u < n_uploads; ++u)
         if (uploads[u].bytes)
             CUDA_TRY(cudaMemcpyAsync(L.at<char>(off_up[u]), uploads[u].host, uploads[u].bytes, cudaMemcpyHostToDevice, s));
@@ -199,8 +208,9 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     memset(&a, 0, sizeof(a));
     a.x = h_x ? L.at<double>(off_x) : d_x;
     a.seg = h_seg ? L.at<int64_t>(off_seg) : nullptr;
+    a.set_node = h_node ? L.at<int64_t>(off_node) : nullptr;
     if (sortable) {
-        CUDA_TRY(sort_trials(L.at<double>(off_x), L.at<double>(off_xs), n, a.seg, h_seg ? P : 0,
+        CUDA_TRY(sort_trials(L.at<double>(off_x), L.at<double>(off_xs), n, a.seg, h_seg ? n_seg : 0,
                              L.at<char>(off_sort), sort_bytes, s));
         a.x = L.at<double>(off_xs);
     }
@@ -231,17 +241,18 @@ int scalar_like(const double* h_x, const double* d_x, int64_t n, const double pa
     const Upload up[1] = {{par, kNumPar * sizeof(double)}};
     ParSpec spec[kNumPar];
     for (int k = 0; k < kNumPar; ++k) spec[k] = {0, k, 0, 0};
-    return like_impl(h_x, d_x, n, nullptr, h_cont, up, 1, spec, 1, mode, nm, logp, nullptr);
+    return like_impl(h_x, d_x, n, nullptr, 0, nullptr, h_cont, up, 1, spec, 1, mode, nm, logp, nullptr);
 }
 
-int batch_like(const double* h_x, const double* d_x, int64_t n, const int64_t* seg, const double* params,
-               int64_t P, const Numerics& nm, double* logp, unsigned long long* evals)
+int batch_like(const double* h_x, const double* d_x, int64_t n, const int64_t* seg, int64_t n_seg,
+               const int64_t* set_node, const double* params, int64_t P, const Numerics& nm, double* logp,
+               unsigned long long* evals)
 {
     if (P > 0 && !params) return fail(HDDM_ERR_ARG, "batch: null params");
     const Upload up[1] = {{params, (size_t)P * kNumPar * sizeof(double)}};
     ParSpec spec[kNumPar];
     for (int k = 0; k < kNumPar; ++k) spec[k] = {0, k * P, 1, 0};
-    return like_impl(h_x, d_x, n, seg, nullptr, up, 1, spec, P, kModeWienerLike, nm, logp, evals);
+    return like_impl(h_x, d_x, n, seg, n_seg, set_node, nullptr, up, 1, spec, P, kModeWienerLike, nm, logp, evals);
 }
 
 int pdf_array_impl(const double* x, int64_t n, const double par[kNumPar], const Numerics& nm, int logp,
@@ -401,7 +412,7 @@ int hddm_wiener_like_multi(const double* x, int64_t n, const double* const par[7
     spec[7] = {0, 7, 0, 0};
     spec[8] = {0, 8, 0, 0};
     up[0] = {scalars, sizeof(scalars)};
-    return like_impl(x, nullptr, n, nullptr, nullptr, up, n_up, spec, 1, kModeMulti,
+    return like_impl(x, nullptr, n, nullptr, 0, nullptr, nullptr, up, n_up, spec, 1, kModeMulti,
                      make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, nullptr);
 }
 
@@ -546,7 +557,7 @@ int hddm_wiener_like_batch(const double* x, int64_t n, const int64_t* seg, const
                            unsigned long long* evals)
 {
     std::lock_guard<std::mutex> lock(g_rt.mu);
-    return batch_like(x, nullptr, n, seg, params, P, make_numerics(err, n_st, n_sz, use_adaptive, simps_err),
+    return batch_like(x, nullptr, n, seg, P, nullptr, params, P, make_numerics(err, n_st, n_sz, use_adaptive, simps_err),
                       logp, evals);
 }
 
@@ -561,7 +572,7 @@ int hddm_wiener_like_multi_batch(const double* x, int64_t n, const double* v_tri
     ParSpec spec[kNumPar];
     for (int k = 0; k < kNumPar; ++k) spec[k] = {0, k * P, 1, 0};
     spec[0] = {1, 0, n, 1};
-    return like_impl(x, nullptr, n, nullptr, nullptr, up, 2, spec, P, kModeMulti,
+    return like_impl(x, nullptr, n, nullptr, 0, nullptr, nullptr, up, 2, spec, P, kModeMulti,
                      make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, evals);
 }
 
@@ -661,7 +672,33 @@ int hddm_trials_wiener_like_batch(const hddm_trials* h, const int64_t* seg, cons
     const double* dx = nullptr;
     TRY(ensure_ready());
     TRY(sorted_view(const_cast<hddm_trials*>(h), seg, P, &dx));
-    return batch_like(nullptr, dx, h->n, seg, params, P,
+    return batch_like(nullptr, dx, h->n, seg, P, nullptr, params, P,
+                      make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, evals);
+}
+
+int hddm_wiener_like_nodes(const double* x, int64_t n, const int64_t* node_off, int64_t n_nodes,
+                           const int64_t* set_node, const double* params, int64_t P, double err, int n_st,
+                           int n_sz, int use_adaptive, double simps_err, double* logp, unsigned long long* evals)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!node_off || n_nodes < 0 || (P > 0 && !set_node)) return fail(HDDM_ERR_ARG, "nodes: null node table");
+    return batch_like(x, nullptr, n, node_off, n_nodes, set_node, params, P,
+                      make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, evals);
+}
+
+int hddm_trials_wiener_like_nodes(const hddm_trials* h, const int64_t* node_off, int64_t n_nodes,
+                                  const int64_t* set_node, const double* params, int64_t P, double err,
+                                  int n_st, int n_sz, int use_adaptive, double simps_err, double* logp,
+                                  unsigned long long* evals)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!h) return fail(HDDM_ERR_ARG, "null trials handle");
+    if (!node_off || n_nodes < 0 || P < 0 || (P > 0 && !set_node))
+        return fail(HDDM_ERR_ARG, "nodes: null node table");
+    const double* dx = nullptr;
+    TRY(ensure_ready());
+    TRY(sorted_view(const_cast<hddm_trials*>(h), node_off, n_nodes, &dx));
+    return batch_like(nullptr, dx, h->n, node_off, n_nodes, set_node, params, P,
                       make_numerics(err, n_st, n_sz, use_adaptive, simps_err), logp, evals);
 }
 

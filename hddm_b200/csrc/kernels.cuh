@@ -51,10 +51,12 @@ enum LikeMode : int {
 //   scalar set                -> both strides 0
 //   batch of sets (SoA [9][P]) -> set_stride 1, trial_stride 0
 //   regression (per trial)    -> trial_stride 1 (set_stride = n for a batch of regressions)
-// Set p sees trials [seg[p], seg[p+1]) of x, or all n trials when seg == nullptr.
+// Set p sees trials [seg[s], seg[s+1]) of x with s = set_node ? set_node[p] : p, or all n trials when
+// seg == nullptr.
 struct LikeArgs {
     const double* x;
     const int64_t* seg;
+    const int64_t* set_node;  // optional [n_sets]: set p sees segment set_node[p] (many sets per segment)
     const int32_t* cont;  // contaminant flags (mode 2) or nullptr
     const double* par[kNumPar];
     int64_t set_stride[kNumPar];

@@ -51,8 +51,9 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     WTable<KT>* wt = gs.wt;
     const int64_t p = blockIdx.x;
     const int chunk = blockIdx.y;
-    const int64_t lo = a.seg ? a.seg[p] : 0;
-    const int64_t hi = a.seg ? a.seg[p + 1] : a.n;
+    const int64_t node = a.set_node ? a.set_node[p] : p;
+    const int64_t lo = a.seg ? a.seg[node] : 0;
+    const int64_t hi = a.seg ? a.seg[node + 1] : a.n;
     const int64_t begin = lo + (int64_t)chunk * kTrialsPerBlock;
     const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
     // src/wfpt.pyx:50-51,63-64: p_outlier outside [0,1] -> -inf before any trial is looked at

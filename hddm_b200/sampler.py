@@ -1,0 +1,199 @@
+"""Batched slice-within-Gibbs sampler for the hierarchical HDDM of BASELINE.json configs[1]
+(subjects x trials, include=('sv','sz','st')): the caller that turns the batched likelihood into
+MCMC iterations per second.
+
+The reference samples this model with PyMC 2.3 + kabuki (hddm/models/hddm_info.py:121-175): one
+observed `wfpt` node per subject, slice steps of fixed width per stochastic
+(`slice_widths`, hddm/models/hddm_info.py:103-105; `SliceStep(width, left, maxiter=5000)`, :163-175), each
+proposal re-evaluating the children's logp one node at a time.  Neither package can be installed
+here, so this module restates the model (priors of `_create_stochastic_knodes_info`,
+hddm/models/hddm_info.py:121-141, families of hddm/models/base.py:578-681) with the update order
+re-designed for a batched likelihood:
+
+  * subject-level parameters (v_subj, a_subj, t_subj) of ALL subjects and ALL chains take their slice
+    steps in lock-step: every stepping-out / shrinkage round is ONE launch of chains x subjects sets;
+  * group-only parameters (sv, sz, st) touch every observed node: one launch of chains x subjects sets
+    per proposal (all children of the node at once);
+  * group means / spreads only see the subject-level priors: plain numpy, no likelihood.
+
+The likelihood is a callable `loglik(set_node[P], params[9, P]) -> float64[P]`: on the product path it
+is `hddm_b200.likelihoods.BatchedNodes.logp` (CUDA); the benchmark passes the CPU reference through the
+same interface to time "the same sampler, reference likelihood".  This module never imports `oracle`.
+"""
+import math
+import time
+
+import numpy as np
+
+SLICE_WIDTHS = {'a': 1, 't': 0.01, 'a_std': 1, 't_std': 0.15, 'sz': 1.1, 'v': 1.5, 'st': 0.1, 'sv': 3,
+                'v_std': 1}  # hddm/models/hddm_info.py:103-105
+SUBJ_WIDTHS = {'v': 1.5, 'a': 1, 't': 0.01}
+MAXITER = 5000  # hddm/models/hddm_info.py:174
+
+
+# ---- log-densities of the prior families (pymc 2.3 parameterisations) -----------------------------
+
+def _norm_logpdf(x, mu, sd):
+    return -0.5 * ((x - mu) / sd) ** 2 - np.log(sd) - 0.9189385332046727
+
+
+def _halfnorm_logpdf(x, sd):
+    return np.where(x > 0, -0.5 * (x / sd) ** 2 - np.log(sd) - 0.2257913526447274, -np.inf)
+
+
+def _gamma_logpdf(x, shape, rate):
+    with np.errstate(divide='ignore', invalid='ignore'):
+        out = shape * np.log(rate) - _lgamma(shape) + (shape - 1) * np.log(x) - rate * x
+    return np.where((x > 0) & (shape > 0) & (rate > 0), out, -np.inf)
+
+
+def _beta_logpdf(x, a, b):
+    with np.errstate(divide='ignore', invalid='ignore'):
+        out = (a - 1) * np.log(x) + (b - 1) * np.log1p(-x) - (_lgamma(a) + _lgamma(b) - _lgamma(a + b))
+    return np.where((x > 0) & (x < 1), out, -np.inf)
+
+
+_lgamma = np.vectorize(math.lgamma, otypes=[np.float64])
+
+
+def _gamma_from_mean_std(x, mean, std):
+    """pm.Gamma(alpha=mean^2/std^2, beta=mean/std^2), hddm/models/base.py:649-668."""
+    with np.errstate(divide='ignore', invalid='ignore'):
+        return _gamma_logpdf(x, mean ** 2 / std ** 2, mean / std ** 2)
+
+
+# ---- vectorised slice step (Neal 2003: stepping out + shrinkage), all units in lock-step -----------
+
+def slice_step(x0, logp, width, rng, left=None, maxiter=MAXITER):
+    """One slice update of every element of x0 (independent targets).  `logp(x) -> array like x` evaluates
+    all targets at once (one batched launch).  Returns (x1, logp(x1), n_logp_calls)."""
+    x0 = np.asarray(x0, dtype=np.float64)
+    shape = x0.shape
+    x0 = x0.ravel()
+    n = x0.size
+    calls = 1
+    lp0 = np.asarray(logp(x0.reshape(shape)), dtype=np.float64).ravel()
+    y = lp0 + np.log(rng.random(n))
+    L = x0 - width * rng.random(n)
+    R = L + width
+    if left is not None:
+        L = np.maximum(L, left)
+    # stepping out, both ends per round
+    grow_l = np.ones(n, dtype=bool) if left is None else (L > left)
+    grow_r = np.ones(n, dtype=bool)
+    it = 0
+    while (grow_l.any() or grow_r.any()) and it < maxiter:
+        lpl = np.asarray(logp(np.where(grow_l, L, x0).reshape(shape)), dtype=np.float64).ravel()
+        lpr = np.asarray(logp(np.where(grow_r, R, x0).reshape(shape)), dtype=np.float64).ravel()
+        calls += 2
+        grow_l &= lpl > y
+        grow_r &= lpr > y
+        L = np.where(grow_l, L - width, L)
+        if left is not None:
+            hit = L <= left
+            L = np.where(hit, left, L)
+            grow_l &= ~hit
+        R = np.where(grow_r, R + width, R)
+        it += 1
+    # shrinkage
+    x1 = x0.copy()
+    lp1 = lp0.copy()
+    todo = np.ones(n, dtype=bool)
+    it = 0
+    while todo.any() and it < maxiter:
+        cand = np.where(todo, L + (R - L) * rng.random(n), x1)
+        lpc = np.asarray(logp(cand.reshape(shape)), dtype=np.float64).ravel()
+        calls += 1
+        ok = todo & (lpc > y)
+        x1 = np.where(ok, cand, x1)
+        lp1 = np.where(ok, lpc, lp1)
+        rej = todo & ~ok
+        L = np.where(rej & (cand < x0), cand, L)
+        R = np.where(rej & (cand >= x0), cand, R)
+        todo = rej
+        it += 1
+    return x1.reshape(shape), lp1.reshape(shape), calls
+
+
+class HierarchicalDDM(object):
+    """State + one-sweep update of the hierarchical full DDM, `chains` independent chains at once.
+
+    loglik(set_node, params) evaluates P = chains * subjects sets in one call."""
+
+    def __init__(self, n_subjects, loglik, chains=1, z=0.5, p_outlier=0.05, w_outlier=0.1, seed=0):
+        self.S, self.C = int(n_subjects), int(chains)
+        self.loglik = loglik
+        self.z, self.p_outlier, self.w_outlier = z, p_outlier, w_outlier
+        self.rng = np.random.default_rng(seed)
+        C, S = self.C, self.S
+        # starting values of hddm/models/hddm_info.py:124-141
+        self.g = {'v': np.full(C, 2.0), 'v_std': np.full(C, 0.1), 'a': np.full(C, 1.5), 'a_std': np.full(C, 0.1),
+                  't': np.full(C, 0.4), 't_std': np.full(C, 0.2), 'sv': np.full(C, 1.0), 'sz': np.full(C, 0.01),
+                  'st': np.full(C, 0.001)}
+        self.subj = {'v': np.full((C, S), 2.0), 'a': np.full((C, S), 1.0), 't': np.full((C, S), 0.001)}
+        self.set_node = np.tile(np.arange(S, dtype=np.int64), C)
+        self.loglik_calls = 0
+        self.sets_evaluated = 0
+
+    # -- likelihood of every (chain, subject) node for the current state with overrides
+    def _node_loglik(self, **over):
+        C, S = self.C, self.S
+        get = lambda name: over[name] if name in over else (self.subj[name] if name in self.subj else self.g[name])
+        bc = lambda a: np.broadcast_to(np.asarray(a, dtype=np.float64).reshape(C, -1), (C, S)).ravel()
+        params = np.empty((9, C * S))
+        params[0] = bc(get('v')); params[1] = bc(get('sv')); params[2] = bc(get('a')); params[3] = self.z
+        params[4] = bc(get('sz')); params[5] = bc(get('t')); params[6] = bc(get('st'))
+        params[7] = self.p_outlier; params[8] = self.w_outlier
+        self.loglik_calls += 1
+        self.sets_evaluated += C * S
+        return np.asarray(self.loglik(self.set_node, params), dtype=np.float64).reshape(C, S)
+
+    def _subj_prior(self, name, x, g=None, std=None):
+        g = self.g[name][:, None] if g is None else g
+        std = self.g[name + '_std'][:, None] if std is None else std
+        if name == 'v':
+            return _norm_logpdf(x, g, std)
+        return _gamma_from_mean_std(x, g, std)
+
+    def sweep(self):
+        """One MCMC iteration: every stochastic of the model is updated once."""
+        rng = self.rng
+        # subject-level parameters: chains x subjects targets in lock-step
+        for name in ('v', 'a', 't'):
+            target = lambda x, name=name: self._node_loglik(**{name: x}) + self._subj_prior(name, x)
+            self.subj[name], _, _ = slice_step(self.subj[name], target, SUBJ_WIDTHS[name], rng)
+        # group-only parameters: every observed node is a child
+        priors = {'sv': lambda x: _halfnorm_logpdf(x, 2.0), 'sz': lambda x: _beta_logpdf(x, 1.0, 3.0),
+                  'st': lambda x: _halfnorm_logpdf(x, 0.3)}
+        for name in ('sv', 'sz', 'st'):
+            target = lambda x, name=name: self._node_loglik(**{name: x[:, None]}).sum(axis=1) + priors[name](x)
+            self.g[name], _, _ = slice_step(self.g[name], target, SLICE_WIDTHS[name], rng, left=0.0)
+        # group means and spreads: children are the subject-level priors only
+        hyper = {'v': lambda x: _norm_logpdf(x, 2.0, 3.0), 'a': lambda x: _gamma_from_mean_std(x, 1.5, 0.75),
+                 't': lambda x: _gamma_from_mean_std(x, 0.4, 0.2)}
+        std_sd = {'v': 2.0, 'a': 2.0, 't': 1.0}
+        for name in ('v', 'a', 't'):
+            xs = self.subj[name]
+            tg = lambda g, name=name, xs=xs: self._subj_prior(name, xs, g=g[:, None]).sum(axis=1) + hyper[name](g)
+            self.g[name], _, _ = slice_step(self.g[name], tg, SLICE_WIDTHS[name], rng)
+            ts = lambda s, name=name, xs=xs: (self._subj_prior(name, xs, std=s[:, None]).sum(axis=1) +
+                                              _halfnorm_logpdf(s, std_sd[name]))
+            self.g[name + '_std'], _, _ = slice_step(self.g[name + '_std'], ts, SLICE_WIDTHS[name + '_std'], rng,
+                                                     left=0.0)
+
+    def sample(self, n_iter, trace=True):
+        """Run n_iter sweeps; returns (trace dict name -> [n_iter, chains(, subjects)], seconds)."""
+        names = list(self.g) + [k + '_subj' for k in self.subj]
+        tr = {k: [] for k in names} if trace else None
+        t0 = time.perf_counter()
+        for _ in range(n_iter):
+            self.sweep()
+            if trace:
+                for k in self.g:
+                    tr[k].append(self.g[k].copy())
+                for k in self.subj:
+                    tr[k + '_subj'].append(self.subj[k].copy())
+        dt = time.perf_counter() - t0
+        if trace:
+            tr = {k: np.stack(v) for k, v in tr.items()}
+        return tr, dt

@@ -15,7 +15,7 @@ from ._lib import as_rt_buffer, check, dptr, lib
 
 __all__ = ["full_pdf", "pdf_array", "wiener_like", "wiener_like_multi", "wiener_like_contaminant",
            "gen_cdf_using_pdf", "gen_rts_from_cdf", "split_cdf", "wiener_like_batch",
-           "wiener_like_multi_batch", "Trials"]
+           "wiener_like_multi_batch", "wiener_like_nodes", "Trials"]
 
 _PARAM_NAMES = ("v", "sv", "a", "z", "sz", "t", "st")
 
@@ -192,6 +192,34 @@ def wiener_like_multi_batch(x, v_trial, params, err=1e-4, n_st=10, n_sz=10, use_
     return (out, evals.value) if return_evals else out
 
 
+def _node_tables(node_off, set_node, P):
+    node_off = np.ascontiguousarray(node_off, dtype=np.int64)
+    set_node = np.ascontiguousarray(set_node, dtype=np.int64)
+    if node_off.ndim != 1 or node_off.shape[0] < 1:
+        raise ValueError("node_off must hold n_nodes + 1 offsets")
+    if set_node.shape != (P,):
+        raise ValueError("set_node must have one entry per parameter set")
+    return node_off, set_node
+
+
+def wiener_like_nodes(x, node_off, set_node, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1,
+                      simps_err=1e-3, return_evals=False):
+    """Hierarchical layout: observed node s holds trials x[node_off[s]:node_off[s+1]]; parameter set p
+    (column p of params [9, P]) is evaluated against node set_node[p].  One launch for all proposals /
+    chains of all nodes; returns float64[P] of wiener_like values (src/wfpt.pyx:54-76 per set)."""
+    x = as_rt_buffer(x)
+    params = _pack_params(params)
+    P = params.shape[1]
+    node_off, set_node = _node_tables(node_off, set_node, P)
+    out = np.empty(P, dtype=np.double)
+    evals = C.c_ulonglong(0)
+    check(lib().hddm_wiener_like_nodes(dptr(x), x.shape[0], node_off.ctypes.data_as(_lib.c_lp),
+                                       node_off.shape[0] - 1, set_node.ctypes.data_as(_lib.c_lp), dptr(params),
+                                       P, err, n_st, n_sz, int(bool(use_adaptive)), simps_err, dptr(out),
+                                       C.byref(evals)))
+    return (out, evals.value) if return_evals else out
+
+
 class Trials(object):
     """Device-resident signed RTs of one observed node: uploaded once, reused by every logp call of
     the MCMC loop (the reference re-reads `x['rt'].values` on every call, hddm/likelihoods.py:54)."""
@@ -223,6 +251,20 @@ class Trials(object):
         check(lib().hddm_trials_wiener_like_batch(self._h, segp, dptr(params), P, err, n_st, n_sz,
                                                   int(bool(use_adaptive)), simps_err, dptr(out),
                                                   C.byref(evals)))
+        return (out, evals.value) if return_evals else out
+
+    def wiener_like_nodes(self, node_off, set_node, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1,
+                          simps_err=1e-3, return_evals=False):
+        """As wfpt.wiener_like_nodes on the resident trials (sorted once per node table)."""
+        params = _pack_params(params)
+        P = params.shape[1]
+        node_off, set_node = _node_tables(node_off, set_node, P)
+        out = np.empty(P, dtype=np.double)
+        evals = C.c_ulonglong(0)
+        check(lib().hddm_trials_wiener_like_nodes(self._h, node_off.ctypes.data_as(_lib.c_lp),
+                                                  node_off.shape[0] - 1, set_node.ctypes.data_as(_lib.c_lp),
+                                                  dptr(params), P, err, n_st, n_sz, int(bool(use_adaptive)),
+                                                  simps_err, dptr(out), C.byref(evals)))
         return (out, evals.value) if return_evals else out
 
     def close(self):

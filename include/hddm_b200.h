@@ -148,6 +148,19 @@ int hddm_trials_wiener_like_batch(const hddm_trials *h, const int64_t *seg, cons
                                   int64_t P, double err, int n_st, int n_sz, int use_adaptive,
                                   double simps_err, double *logp, unsigned long long *evals);
 
+/* Hierarchical layout: the observed nodes (subject x condition) are the segments
+ * [node_off[s], node_off[s+1]) of x, s < n_nodes, and parameter set p is evaluated against node
+ * set_node[p] -- many proposals / chains per node and all children of a group-level parameter in ONE
+ * launch (the per-node logp of hddm/likelihoods.py:52-55, batched).  logp[p] as hddm_wiener_like. */
+int hddm_wiener_like_nodes(const double *x, int64_t n, const int64_t *node_off, int64_t n_nodes,
+                           const int64_t *set_node, const double *params, int64_t P, double err,
+                           int n_st, int n_sz, int use_adaptive, double simps_err, double *logp,
+                           unsigned long long *evals);
+int hddm_trials_wiener_like_nodes(const hddm_trials *h, const int64_t *node_off, int64_t n_nodes,
+                                  const int64_t *set_node, const double *params, int64_t P, double err,
+                                  int n_st, int n_sz, int use_adaptive, double simps_err, double *logp,
+                                  unsigned long long *evals);
+
 /* ---- device-pointer entry points (enqueue only; used under torch.distributed sharding) ----- */
 
 /* One-time layout step for a device-resident trial vector that many launches will reuse: d_sorted =

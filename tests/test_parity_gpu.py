@@ -320,3 +320,84 @@ def test_full_size_properties(W, O):
     for p in (3, 500, 1023):
         want = O.wiener_like(x, *params[:7, p], p_outlier=0.05, w_outlier=0.1, **HDDM)
         assert_parity(a[p], want, RTOL_SUM, what="subsample set %d" % p)
+
+
+def test_nodes_batch_vs_oracle(W, O):
+    """Hierarchical layout: many parameter sets per observed node in one launch (host-buffer entry point
+    and the device-resident handle), against one oracle call per set."""
+    rng = np.random.default_rng(9400)
+    lens = [0, 37, 200, 64, 311]
+    xs = [draw_rts(rng, n, 0.40) for n in lens]
+    x = np.concatenate(xs)
+    node_off = np.concatenate([[0], np.cumsum(lens)])
+    P = 23
+    set_node = rng.integers(0, len(lens), P)
+    par = draw_params(rng, P)
+    params = np.concatenate([par, np.full((1, P), 0.05), np.full((1, P), 0.1)])
+    want = np.array([O.wiener_like(xs[set_node[p]], *par[:, p], p_outlier=0.05, w_outlier=0.1, **HDDM)
+                     for p in range(P)])
+    got = W.wiener_like_nodes(x, node_off, set_node, params, **HDDM)
+    assert_parity(got, want, RTOL_SUM, what="nodes batch")
+    h = W.Trials(x)
+    got2 = h.wiener_like_nodes(node_off, set_node, params, **HDDM)
+    assert np.array_equal(got, got2)
+    assert got[set_node == 0].tolist() == [0.0] * int((set_node == 0).sum())  # empty node: sum over nothing
+    h.close()
+    with pytest.raises(ValueError):
+        W.wiener_like_nodes(x, node_off, np.full(P, 7), params, **HDDM)
+
+
+def test_likelihood_glue_vs_oracle(W, O, gpu):
+    """hddm_b200/likelihoods.py: wfpt_like (incl. the +-999 missing-response branch), pdf / cdf members and
+    the chi-square / quantile methods of the stochastic class against the oracle through the same formulas."""
+    import pandas as pd
+    from scipy import stats
+    from hddm_b200 import likelihoods as L
+    rng = np.random.default_rng(9500)
+    rt = draw_rts(rng, 300, 0.45)
+    par = dict(v=0.8, sv=0.6, a=1.6, z=0.5, sz=0.2, t=0.3, st=0.15)
+    wp = dict(L.DEFAULT_WIENER_PARAMS)
+    num = {k: wp[k] for k in ("err", "n_st", "n_sz", "use_adaptive", "simps_err")}
+    Wfpt = L.generate_wfpt_stochastic_class(wp)
+    node = Wfpt(value=pd.DataFrame({"rt": rt}), p_outlier=0.05, **par)
+    want = O.wiener_like(rt, *[par[k] for k in L._PARENTS], p_outlier=0.05, w_outlier=0.1, **num)
+    assert_parity(node.logp, want, RTOL_SUM, what="wfpt_like")
+    assert node.logp == node.logp  # second call hits the device-resident copy
+    # missing responses
+    rt2 = np.concatenate([rt, [999.0, 999.0, -999.0]])
+    node2 = Wfpt(value=pd.DataFrame({"rt": rt2}), p_outlier=0.05, **par)
+    pu = O.prob_ub(par["v"], par["a"], par["z"]) if hasattr(O, "prob_ub") else L._prob_upper(par["v"], par["a"], par["z"])
+    assert_parity(node2.logp, want + stats.binom.logpmf(2, 3, pu), RTOL_SUM, what="wfpt_like missing")
+    # members
+    node_np = Wfpt(value=rt, p_outlier=0.0, **par)  # the reference's wfpt knode always has a p_outlier parent
+    assert_parity(node_np.pdf(rt[:50].copy()), O.pdf_array(rt[:50].copy(), *[par[k] for k in L._PARENTS], **num),
+                  RTOL_TRIAL, what="pdf member")
+    q = node_np.get_quantiles_stats()
+    assert q["n_samples"] == 300 and q["emp_rt"].shape == (11,) and abs(q["freq_obs"].sum() - 300) < 1e-9
+    cdf_want = O.dmat_cdf_array(np.ascontiguousarray(q["emp_rt"]), *[par[k] for k in L._PARENTS], 0.0, 0.1)
+    theo = np.diff(np.concatenate(([0.], cdf_want, [1.])))
+    theo[theo <= 1e-6] = 1e-6
+    chi_want, _ = stats.chisquare(q["freq_obs"], theo * 300)
+    assert abs(node_np.chisquare() - chi_want) <= 1e-8 * abs(chi_want)
+    assert abs(node_np.gsquare() - 2 * np.sum(q["freq_obs"] * np.log(theo))) <= 1e-8 * abs(node_np.gsquare())
+    ql, qu, pup = node_np.theoretical_quantiles()
+    assert ql.shape == (5,) and qu.shape == (5,) and 0 < pup < 1 and (np.diff(qu) >= 0).all()
+
+
+def test_sampler_gpu_vs_oracle_backend(W, O, gpu):
+    """The batched sampler with the CUDA likelihood and with the oracle likelihood behind the same
+    interface, same seed: the chains coincide (same decisions, values within the likelihood tolerance)."""
+    from hddm_b200 import likelihoods as L, sampler
+    rng = np.random.default_rng(9600)
+    S, C = 4, 2
+    rts = [draw_rts(rng, 60, 0.45) for _ in range(S)]
+    nodes = L.BatchedNodes(rts)
+
+    def oracle_loglik(set_node, params):
+        return np.array([O.wiener_like(rts[set_node[p]], *params[:7, p], p_outlier=params[7, p],
+                                       w_outlier=params[8, p], **HDDM) for p in range(params.shape[1])])
+
+    tr_g, _ = sampler.HierarchicalDDM(S, nodes.logp, chains=C, seed=3).sample(3)
+    tr_o, _ = sampler.HierarchicalDDM(S, oracle_loglik, chains=C, seed=3).sample(3)
+    for k in tr_g:
+        assert np.allclose(tr_g[k], tr_o[k], rtol=1e-9, atol=0), k
