@@ -49,6 +49,8 @@ struct Runtime {
     cudaStream_t stream = nullptr;
     char* arena = nullptr;  // grow-only device scratch, carved per call
     size_t arena_bytes = 0;
+    char* pinned = nullptr;  // grow-only page-locked staging for the small per-call inputs / outputs
+    size_t pinned_bytes = 0;
 };
 Runtime g_rt;
 
@@ -81,6 +83,23 @@ int ensure_arena(size_t bytes)
     g_rt.arena_bytes = want;
     return HDDM_OK;
 }
+
+int ensure_pinned(size_t bytes)
+{
+    if (bytes <= g_rt.pinned_bytes) return HDDM_OK;
+    if (g_rt.pinned) {
+        CUDA_TRY(cudaStreamSynchronize(g_rt.stream));
+        CUDA_TRY(cudaFreeHost(g_rt.pinned));
+        g_rt.pinned = nullptr;
+        g_rt.pinned_bytes = 0;
+    }
+    const size_t want = bytes + bytes / 2 + (64 << 10);
+    CUDA_TRY(cudaMallocHost(&g_rt.pinned, want));
+    g_rt.pinned_bytes = want;
+    return HDDM_OK;
+}
+
+constexpr size_t kPinnedMax = 8u << 20;  // larger inputs are copied straight from the caller's buffer
 
 size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
 
@@ -181,27 +200,43 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     const size_t off_xs = sortable ? L.reserve((size_t)n * sizeof(double)) : 0;
     const size_t off_sort = sortable ? L.reserve(sort_bytes) : 0;
     const size_t off_cont = h_cont ? L.reserve((size_t)n * sizeof(int32_t)) : 0;
+    // small inputs (segment table, node map, parameters) are contiguous: staged through page-locked
+    // memory and uploaded with ONE copy; likewise logp + the eval counter come back with one copy
+    const size_t small_lo = L.total;
     const size_t off_seg = h_seg ? L.reserve((size_t)(n_seg + 1) * sizeof(int64_t)) : 0;
     const size_t off_node = h_node ? L.reserve((size_t)P * sizeof(int64_t)) : 0;
     size_t off_up[8];
     for (int u = 0; u < n_uploads; ++u) off_up[u] = L.reserve(uploads[u].bytes);
+    const size_t small_hi = L.total;
     const size_t off_partial = L.reserve((size_t)P * chunks * sizeof(double));
     const size_t off_logp = L.reserve((size_t)P * sizeof(double));
     const size_t off_evals = L.reserve(sizeof(unsigned long long));
+    const size_t out_bytes = L.total - off_logp;
     TRY(ensure_arena(L.total));
+    const bool staged = (small_hi - small_lo) <= kPinnedMax && out_bytes <= kPinnedMax;
+    if (staged) TRY(ensure_pinned((small_hi - small_lo) > out_bytes ? (small_hi - small_lo) : out_bytes));
 
     cudaStream_t s = g_rt.stream;
     if (h_x && n > 0)
         CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_x), h_x, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
     if (h_cont && n > 0)
         CUDA_TRY(cudaMemcpyAsync(L.at<int32_t>(off_cont), h_cont, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
-    if (h_seg)
-        CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_seg), h_seg, (size_t)(n_seg + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
-    if (h_node)
-        CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_node), h_node, (size_t)P * sizeof(int64_t), cudaMemcpyHostToDevice, s));
-    for (int u = 0; u < n_uploads; ++u)
-        if (uploads[u].bytes)
-            CUDA_TRY(cudaMemcpyAsync(L.at<char>(off_up[u]), uploads[u].host, uploads[u].bytes, cudaMemcpyHostToDevice, s));
+    if (staged) {
+        char* ph = g_rt.pinned - small_lo;
+        if (h_seg) memcpy(ph + off_seg, h_seg, (size_t)(n_seg + 1) * sizeof(int64_t));
+        if (h_node) memcpy(ph + off_node, h_node, (size_t)P * sizeof(int64_t));
+        for (int u = 0; u < n_uploads; ++u)
+            if (uploads[u].bytes) memcpy(ph + off_up[u], uploads[u].host, uploads[u].bytes);
+        CUDA_TRY(cudaMemcpyAsync(L.at<char>(small_lo), g_rt.pinned, small_hi - small_lo, cudaMemcpyHostToDevice, s));
+    } else {
+        if (h_seg)
+            CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_seg), h_seg, (size_t)(n_seg + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+        if (h_node)
+            CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_node), h_node, (size_t)P * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+        for (int u = 0; u < n_uploads; ++u)
+            if (uploads[u].bytes)
+                CUDA_TRY(cudaMemcpyAsync(L.at<char>(off_up[u]), uploads[u].host, uploads[u].bytes, cudaMemcpyHostToDevice, s));
+    }
     CUDA_TRY(cudaMemsetAsync(L.at<char>(off_evals), 0, sizeof(unsigned long long), s));
 
     LikeArgs a;
@@ -229,6 +264,13 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     a.logp = L.at<double>(off_logp);
     a.evals = L.at<unsigned long long>(off_evals);
     CUDA_TRY(launch_like(a, s));
+    if (staged) {  // the upload has been consumed by the kernels queued before this copy: reuse the staging
+        CUDA_TRY(cudaMemcpyAsync(g_rt.pinned, L.at<char>(off_logp), out_bytes, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+        memcpy(logp, g_rt.pinned, (size_t)P * sizeof(double));
+        if (evals) memcpy(evals, g_rt.pinned + (off_evals - off_logp), sizeof(unsigned long long));
+        return HDDM_OK;
+    }
     CUDA_TRY(cudaMemcpyAsync(logp, a.logp, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, s));
     if (evals) CUDA_TRY(cudaMemcpyAsync(evals, a.evals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));

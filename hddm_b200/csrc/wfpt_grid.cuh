@@ -113,6 +113,7 @@ struct alignas(16) GridSet {
     int support;           // the set-level part of the support test of src/pdf.pxi:111-113 passed
     double t_onset;        // t - st/2 with the raw st (the per-trial part of that test)
     double xt_lo[2], xt_hi;  // comfortable decision-time range per boundary, see build_gridset
+    double xt_zero[2];       // below this decision time every start point's density is < 1e-230, see build_gridset
     double a, sv, t, st, sz;  // st, sz after the 1e-3 snap of src/pdf.pxi:122-125
     double a_sq, inv_a_sq, sv_sq, qk;  // qk = -pi^2 / (2 a^2)
     double inv_zt, inv_st; // 1/(ub_z - lb_z) (1 when sz == 0), 1/(ub_t - lb_t)
@@ -164,6 +165,17 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
             G.xt_lo[b] = (lo_b > tt_lo ? lo_b : tt_lo) * a_sq;
         }
         G.xt_hi = tt_hi * a_sq;
+        // Below tt = w_0^2 / 1300 every start point has exp(-w^2 / (2 tt)) <= e^-650; with the sv-marginal
+        // exponent bounded by 100 + 100 (checked per set here and per trial in full_pdf_grid) the node's
+        // density is < 1e-230: when the trial's result is > 1e-150 such a node is exactly as good as 0.
+        {
+            const double wm = G.wt[0].w[16] > G.wt[1].w[16] ? G.wt[0].w[16] : G.wt[1].w[16];
+            const double asw_ = (a * sv) * wm;
+            for (int b = 0; b < 2; ++b) {
+                const double w0 = G.wt[b].w[0];
+                G.xt_zero[b] = (asw_ * asw_ <= 200.0) ? ((w0 * w0) / 1300.0) * a_sq : 0.0;
+            }
+        }
         // window of thresholds inside (tt_lo, tt_hi]
         int r0 = 0, nwin = 0;
         for (int i = 0; i < tab.n_thr; ++i) {
@@ -520,16 +532,18 @@ __device__ __noinline__ double grid_inner_ool(const GridSet<KMAX>& G, const Grid
 template <int KMAX>
 __device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridTrial& c, double ax,
                                              const Numerics& nm, const SeriesTable* tab, const double F[5],
-                                             double coarse, unsigned long long& evals, bool* bad)
+                                             double coarse, unsigned long long& evals, double xz, bool* bad,
+                                             bool* tiny)
 {
     const unsigned int per_node = G.sz != 0 ? 5 : 1;
-    bool out_of_range = false;
+    bool out_of_range = false, saw_tiny = false;
     auto g = [&](double tn, int) {
         const double xt = ax - tn;
         evals += per_node;
         if (!(xt > 0.0)) return 0.0;  // src/pdf.pxi:92-93
         if (xt < G.xt_lo[c.b]) {
-            out_of_range = true;
+            if (xt < xz) saw_tiny = true;
+            else out_of_range = true;
             return 0.0;
         }
         const int code = grid_code(G, xt);
@@ -543,6 +557,7 @@ __device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridT
     Span stack[kMaxDepth];
     const double r = simpson_walk(g, top, true, F[1], F[3], stack);
     *bad = out_of_range;
+    *tiny = saw_tiny;
     return r;
 }
 
@@ -564,8 +579,11 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
 
     const double xt_max = ax - G.tn[0];
     // exponent of the sv marginal lies in [-(2 a |v| + v^2 x_t) / 2, (a sv w_4)^2 / 2 + a |v|]
-    bool ok = G.ok && (xt_max <= G.xt_hi) && (fma(c.v_sq, xt_max, (2.0 * G.a) * fabs(c.v)) <= 600.0) &&
-              (nm.simps_err >= 0.0);
+    const double bnd = fma(c.v_sq, xt_max, (2.0 * G.a) * fabs(c.v));
+    bool ok = G.ok && (xt_max <= G.xt_hi) && (bnd <= 600.0) && (nm.simps_err >= 0.0);
+    // decision times in (0, xz): the node is negligible (see GridSet::xt_zero) and is taken as 0
+    const double xz = (bnd <= 200.0 && nm.simps_err >= 1e-200) ? G.xt_zero[c.b] : 0.0;
+    bool tiny = false;
     unsigned int n_eval = 0;
     unsigned long long extra = 0;
     double out = 0.0;
@@ -577,7 +595,7 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
             if (xt <= 0.0) {
                 n_eval = over_z ? 5 : 1;  // src/pdf.pxi:92-93
             } else if (xt < G.xt_lo[c.b]) {
-                ok = false;
+                ok = false;  // (a single negligible node would make the whole result negligible)
             } else {
                 const int code = grid_code(G, xt);
                 n_eval = over_z ? 5 : 1;
@@ -597,10 +615,14 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
                 n_eval += over_z ? 5 : 1;
                 double val = 0.0;
                 if (xt > 0.0) {
-                    if (xt < G.xt_lo[c.b]) ok = false;
+                    const bool live = !(xt < G.xt_lo[c.b]);
+                    if (!live) {
+                        if (xt < xz) tiny = true;
+                        else ok = false;
+                    }
                     const int code = uniform ? code_hi : grid_code(G, xt);
                     const double q = q0 * G.rho[j];
-                    if (ok) val = grid_inner<KMAX>(G, c, xt, code, q, nm, tab, extra);
+                    if (ok && live) val = grid_inner<KMAX>(G, c, xt, code, q, nm, tab, extra);
                 }
                 F[j] = val * G.inv_st;
             }
@@ -612,10 +634,12 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
                 if (nm.n_st <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err)
                     out = fma(fine - coarse, 1.0 / 15.0, fine);
                 else {
-                    bool bad = false;
-                    out = grid_refine_t<KMAX>(G, c, ax, nm, tab, F, coarse, extra, &bad);
+                    bool bad = false, tiny2 = false;
+                    out = grid_refine_t<KMAX>(G, c, ax, nm, tab, F, coarse, extra, xz, &bad, &tiny2);
                     ok = !bad;
+                    tiny |= tiny2;
                 }
+                if (tiny && !(fabs(out) > 1e-150)) ok = false;
             }
         }
     }
