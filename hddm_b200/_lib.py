@@ -46,6 +46,12 @@ SIGNATURES = {
     "hddm_dmat_cdf_array": (_i, [c_dp, _l] + [_d] * 9 + [c_dp]),
     "hddm_wiener_like_batch": (_i, [c_dp, _l, c_lp, c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_wiener_like_multi_batch": (_i, [c_dp, _l, c_dp, c_dp, _l] + _NUM + [c_dp, c_up]),
+    "hddm_wiener_like_rlddm": (_i, [c_dp, c_lp, c_dp, c_lp, _l] + [_d] * 10 + _NUM + [_d, _d, c_dp]),
+    "hddm_wiener_like_rlddm_batch": (_i, [c_dp, c_lp, c_dp, c_lp, _l, c_dp, _l] + _NUM + [c_dp, c_up]),
+    "hddm_wiener_like_rl": (_i, [c_lp, c_dp, c_lp, _l] + [_d] * 7 + [c_dp]),
+    "hddm_wiener_like_rl_batch": (_i, [c_lp, c_dp, c_lp, _l, c_dp, _l, c_dp]),
+    "hddm_wiener_like_multi_rlddm": (_i, [c_dp, c_lp, c_dp, c_lp, _l, _d, C.POINTER(c_dp), c_lp] + _NUM +
+                                     [_d, _d, c_dp]),
     "hddm_trials_upload": (_i, [c_dp, _l, C.POINTER(_v)]),
     "hddm_trials_free": (_i, [_v]),
     "hddm_trials_wiener_like": (_i, [_v] + [_d] * 7 + _NUM + [_d, _d, c_dp]),

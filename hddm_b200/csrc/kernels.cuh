@@ -43,7 +43,8 @@ constexpr int kLikeThreads = 256;
 enum LikeMode : int {
     kModeWienerLike = 0,  // src/wfpt.pyx:54-76   outlier mix, p==0 -> -inf
     kModeMulti = 1,       // src/wfpt.pyx:244-274 +-999 sentinels, no zero guard
-    kModeContaminant = 2  // src/wfpt.pyx:357-386 skip cont_x != 0, p==0 -> -inf, no mix
+    kModeContaminant = 2, // src/wfpt.pyx:357-386 skip cont_x != 0, p==0 -> -inf, no mix
+    kModeMultiRL = 3      // src/wfpt.pyx:277-320 as kModeMulti but every x is an RT (no +-999 sentinels)
 };
 
 // One launch evaluates `n_sets` parameter sets.  Parameter k of (set p, trial i) is read from
@@ -57,7 +58,8 @@ struct LikeArgs {
     const double* x;
     const int64_t* seg;
     const int64_t* set_node;  // optional [n_sets]: set p sees segment set_node[p] (many sets per segment)
-    const int32_t* cont;  // contaminant flags (mode 2) or nullptr
+    const int32_t* cont;  // trials with cont[i] != 0 are skipped: contaminant flags (mode 2), the unscored
+                          // first trial of each condition (wiener_like_rlddm); or nullptr
     const double* par[kNumPar];
     int64_t set_stride[kNumPar];
     int64_t trial_stride[kNumPar];
@@ -103,6 +105,37 @@ cudaError_t launch_cumsum_normalise(double* table, int64_t m, cudaStream_t strea
 cudaError_t launch_sample_rts(const double* xgrid, const double* table, int64_t m, const double* f,
                               const double* u_delay, int64_t samples, double t, double st,
                               double* rts, cudaStream_t stream);
+
+// Reinforcement-learning likelihoods (rl_kernels.cu; src/wfpt.pyx:79-241,277-320).  The Q-learning
+// recursion depends only on (response, feedback, learning rates), never on the densities: it runs as a
+// sequential scan per (parameter set, run of trials) that writes the per-trial drift, after which the
+// densities of all trials are evaluated in parallel by the ordinary likelihood kernel.
+struct RlScanArgs {
+    const int32_t* response;   // [n] 0 = lower, 1 = upper (in run order)
+    const double* feedback;    // [n]
+    const int64_t* run_off;    // [n_runs + 1]: Q values restart at the head of every run
+    int64_t n, n_runs, n_sets;
+    const double* q;           // per set: set_stride 0 or 1
+    const double* alpha;       // logit learning rate: per set, or per trial (alpha_trial_stride 1)
+    const double* pos_alpha;   // nullptr: single learning rate; 100.0 means "same as alpha" (src/wfpt.pyx:106)
+    const double* v;           // drift scale: per set or per trial
+    int64_t q_stride, alpha_set_stride, alpha_trial_stride, pos_stride, v_set_stride, v_trial_stride;
+    double* drift;             // out [n_sets][n]: v * (Q_upper - Q_lower) BEFORE the trial's update
+};
+cudaError_t launch_rl_scan(const RlScanArgs& a, cudaStream_t stream);
+
+// wiener_like_rl (src/wfpt.pyx:158-241): choice-only likelihood; the same scan, scoring each trial but
+// the first of a run with the closed-form P(response), summed per set in run order.
+struct RlChoiceArgs {
+    RlScanArgs scan;           // drift unused
+    const double* z;           // per set
+    const double* p_outlier;
+    const double* w_outlier;
+    int64_t z_stride, pout_stride, wout_stride;
+    double* partial;           // [n_sets][n_runs]
+    double* logp;              // [n_sets]
+};
+cudaError_t launch_rl_choice(const RlChoiceArgs& a, cudaStream_t stream);
 
 double fp64_peak_probe(int iters, float* ms_out, cudaStream_t stream);
 

@@ -57,7 +57,8 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     const int64_t begin = lo + (int64_t)chunk * kTrialsPerBlock;
     const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
     // src/wfpt.pyx:50-51,63-64: p_outlier outside [0,1] -> -inf before any trial is looked at
-    const bool range_ok = (a.mode == kModeMulti) || ((p_out >= 0) & (p_out <= 1));
+    const bool multi = a.mode == kModeMulti || a.mode == kModeMultiRL;  // no range / zero guards
+    const bool range_ok = multi || ((p_out >= 0) & (p_out <= 1));
     if (begin >= hi || !range_ok) {  // (ragged batch: shorter sets have empty trailing chunks)
         if (threadIdx.x == 0) a.partial[p * a.chunks + chunk] = range_ok ? 0.0 : -INFINITY;
         return;
@@ -110,8 +111,8 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
                 if (a.trial_stride[k] != 0) par[k] = load_par(a, k, p, i);
         }
         double d;
-        if (a.mode == kModeMulti) {
-            if (fabs(x) != 999.) {  // src/wfpt.pyx:261-266
+        if (multi) {
+            if (a.mode == kModeMultiRL || fabs(x) != 999.) {  // src/wfpt.pyx:261-266
                 d = density(x, evals);
                 d = d * (1 - p_out) + w_out * p_out;
             } else if (x == 999.) {  // :267-268
@@ -121,7 +122,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
             }
             add_log(d);
         } else {
-            if (a.mode == kModeContaminant && a.cont[i] != 0) continue;  // src/wfpt.pyx:374
+            if (a.cont && a.cont[i] != 0) continue;  // src/wfpt.pyx:374; :134 (first trial of a condition)
             d = density(x, evals);
             d = d * (1 - p_out) + w_out * p_out;  // src/wfpt.pyx:70 (contaminant: p_out = 0)
             hit_zero |= (d == 0);                 // :71-72, :377-379
@@ -143,7 +144,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         double s = 0.0;
 #pragma unroll
         for (int w = 0; w < kLikeThreads / 32; ++w) s += warp_part[w];
-        if (a.mode != kModeMulti && any_zero) s = -INFINITY;
+        if (!multi && any_zero) s = -INFINITY;
         a.partial[p * a.chunks + chunk] = s;
     }
 }
@@ -165,7 +166,7 @@ __global__ void __launch_bounds__(128) k_like_final(const LikeArgs a)
     neg_inf = __any_sync(0xffffffffu, neg_inf);
     // wiener_like returns -inf at the FIRST zero density whatever the running sum holds
     // (src/wfpt.pyx:71-72): a -inf partial (only produced by that rule) overrides NaN.
-    if (a.mode != kModeMulti && neg_inf) s = -INFINITY;
+    if (a.mode != kModeMulti && a.mode != kModeMultiRL && neg_inf) s = -INFINITY;
     if (lane == 0) a.logp[p] = s;
 }
 

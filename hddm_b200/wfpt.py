@@ -14,6 +14,8 @@ from . import _lib
 from ._lib import as_rt_buffer, check, dptr, lib
 
 __all__ = ["full_pdf", "pdf_array", "wiener_like", "wiener_like_multi", "wiener_like_contaminant",
+           "wiener_like_rlddm", "wiener_like_rl", "wiener_like_multi_rlddm", "wiener_like_rlddm_batch",
+           "wiener_like_rl_batch",
            "gen_cdf_using_pdf", "gen_rts_from_cdf", "split_cdf", "wiener_like_batch",
            "wiener_like_multi_batch", "wiener_like_nodes", "Trials"]
 
@@ -90,6 +92,111 @@ def wiener_like_contaminant(x, cont_x, v, sv, a, z, sz, t, st, t_min, t_max, err
                                              a, z, sz, t, st, t_min, t_max, err, n_st, n_sz,
                                              int(bool(use_adaptive)), simps_err, C.byref(out)))
     return out.value
+
+
+def _as_long_buffer(a, name):
+    """`np.ndarray[long, ndim=1]` (src/wfpt.pyx:80,82): int64 1-D ndarray, any stride."""
+    if not isinstance(a, np.ndarray):
+        raise TypeError("Argument '%s' has incorrect type (expected numpy.ndarray, got %s)"
+                        % (name, type(a).__name__))
+    if a.ndim != 1:
+        raise ValueError("Buffer has wrong number of dimensions (expected 1, got %d)" % a.ndim)
+    if a.dtype != np.int64:
+        raise ValueError("Buffer dtype mismatch, expected 'long' but got '%s'" % a.dtype)
+    return np.ascontiguousarray(a)
+
+
+def _rl_task(x, response, feedback, split_by):
+    response = _as_long_buffer(response, "response")
+    feedback = as_rt_buffer(feedback, "feedback")
+    split_by = _as_long_buffer(split_by, "split_by")
+    n = response.shape[0] if x is None else x.shape[0]
+    if feedback.shape[0] < n or split_by.shape[0] < n or response.shape[0] < n:
+        raise IndexError("response / feedback / split_by shorter than the trial vector")
+    lp = _lib.c_lp
+    return response, feedback, split_by, n, response.ctypes.data_as(lp), dptr(feedback), split_by.ctypes.data_as(lp)
+
+
+def wiener_like_rlddm(x, response, feedback, split_by, q, alpha, pos_alpha, v, sv, a, z, sz, t, st, err,
+                      n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-8, p_outlier=0, w_outlier=0):
+    """src/wfpt.pyx:79-155."""
+    x = as_rt_buffer(x)
+    response, feedback, split_by, n, rp, fp, sp = _rl_task(x, response, feedback, split_by)
+    out = C.c_double()
+    check(lib().hddm_wiener_like_rlddm(dptr(x), rp, fp, sp, n, q, alpha, pos_alpha, v, sv, a, z, sz, t, st, err,
+                                       n_st, n_sz, int(bool(use_adaptive)), simps_err, p_outlier, w_outlier,
+                                       C.byref(out)))
+    return out.value
+
+
+def wiener_like_rl(response, feedback, split_by, q, alpha, pos_alpha, v, z, err=1e-4, n_st=10, n_sz=10,
+                   use_adaptive=1, simps_err=1e-8, p_outlier=0, w_outlier=0):
+    """src/wfpt.pyx:158-241 (err ... simps_err are accepted and unused, as in the reference)."""
+    response, feedback, split_by, n, rp, fp, sp = _rl_task(None, response, feedback, split_by)
+    out = C.c_double()
+    check(lib().hddm_wiener_like_rl(rp, fp, sp, n, q, alpha, pos_alpha, v, z, p_outlier, w_outlier, C.byref(out)))
+    return out.value
+
+
+_RL_PARAM_NAMES = _PARAM_NAMES + ("alpha",)
+
+
+def wiener_like_multi_rlddm(x, response, feedback, split_by, q, v, sv, a, z, sz, t, st, alpha, err, multi=None,
+                            n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-3, p_outlier=0, w_outlier=0):
+    """src/wfpt.pyx:277-320.  Parameters named in `multi` (v, sv, a, z, sz, t, st, alpha) are per-trial."""
+    x = as_rt_buffer(x)
+    if multi is None:
+        # src/wfpt.pyx:293-294 passes the whole array to the scalar full_pdf and cannot succeed
+        raise TypeError("only size-1 arrays can be converted to Python scalars")
+    response, feedback, split_by, n, rp, fp, sp = _rl_task(x, response, feedback, split_by)
+    values = dict(zip(_RL_PARAM_NAMES, (v, sv, a, z, sz, t, st, alpha)))
+    multi = set(multi)
+    keep, ptrs, strides = [], (C.POINTER(C.c_double) * 8)(), (C.c_int64 * 8)()
+    for k, name in enumerate(_RL_PARAM_NAMES):
+        if name in multi:
+            arr = np.ascontiguousarray(np.asarray(values[name], dtype=np.float64))
+            if arr.ndim != 1 or arr.shape[0] < n:
+                raise IndexError("per-trial parameter '%s' is shorter than x" % name)
+            strides[k] = 1
+        else:
+            arr = np.array([values[name]], dtype=np.float64)
+            strides[k] = 0
+        keep.append(arr)
+        ptrs[k] = dptr(arr)
+    out = C.c_double()
+    check(lib().hddm_wiener_like_multi_rlddm(dptr(x), rp, fp, sp, n, q, ptrs, strides, err, n_st, n_sz,
+                                             int(bool(use_adaptive)), simps_err, p_outlier, w_outlier,
+                                             C.byref(out)))
+    return out.value
+
+
+def wiener_like_rlddm_batch(x, response, feedback, split_by, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1,
+                            simps_err=1e-3, return_evals=False):
+    """NEW: P parameter sets against one subject's task.  params float64 [12, P]: rows v, sv, a, z, sz, t,
+    st, p_outlier, w_outlier, q, alpha, pos_alpha; returns float64[P] of wiener_like_rlddm values."""
+    x = as_rt_buffer(x)
+    response, feedback, split_by, n, rp, fp, sp = _rl_task(x, response, feedback, split_by)
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    if params.ndim != 2 or params.shape[0] != 12:
+        raise ValueError("params must be float64 [12, P]")
+    P = params.shape[1]
+    out = np.empty(P, dtype=np.double)
+    evals = C.c_ulonglong(0)
+    check(lib().hddm_wiener_like_rlddm_batch(dptr(x), rp, fp, sp, n, dptr(params), P, err, n_st, n_sz,
+                                             int(bool(use_adaptive)), simps_err, dptr(out), C.byref(evals)))
+    return (out, evals.value) if return_evals else out
+
+
+def wiener_like_rl_batch(response, feedback, split_by, params):
+    """NEW: params float64 [7, P]: rows q, alpha, pos_alpha, v, z, p_outlier, w_outlier."""
+    response, feedback, split_by, n, rp, fp, sp = _rl_task(None, response, feedback, split_by)
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    if params.ndim != 2 or params.shape[0] != 7:
+        raise ValueError("params must be float64 [7, P]")
+    P = params.shape[1]
+    out = np.empty(P, dtype=np.double)
+    check(lib().hddm_wiener_like_rl_batch(rp, fp, sp, n, dptr(params), P, dptr(out)))
+    return out
 
 
 def gen_cdf_using_pdf(v, sv, a, z, sz, t, st, err, N=500, time=5., n_st=2, n_sz=2, use_adaptive=1,

@@ -137,6 +137,42 @@ int hddm_wiener_like_multi_batch(const double *x, int64_t n, const double *v_tri
                                  int use_adaptive, double simps_err, double *logp,
                                  unsigned long long *evals);
 
+/* ---- reinforcement-learning likelihoods (src/wfpt.pyx:79-241, 277-320) -------------------------- */
+
+/* wiener_like_rlddm, src/wfpt.pyx:79-155.  response (0 = lower, 1 = upper) and split_by (condition
+ * label) are int64[n] like the reference's np.ndarray[long]; feedback is float64[n].  Conditions are
+ * visited in ascending label order, each with its trials in the caller's order; Q values restart at q
+ * per condition; the first trial of a condition updates Q but is not scored; drift of a scored trial =
+ * (Q_upper - Q_lower) * v; learning rate = logistic(alpha), or logistic(pos_alpha) after a positive
+ * prediction error unless pos_alpha == 100.0.  -inf as hddm_wiener_like.  0.0 for n == 0. */
+int hddm_wiener_like_rlddm(const double *x, const int64_t *response, const double *feedback,
+                           const int64_t *split_by, int64_t n, double q, double alpha, double pos_alpha,
+                           double v, double sv, double a, double z, double sz, double t, double st,
+                           double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                           double p_outlier, double w_outlier, double *logp);
+/* NEW: P parameter sets against one subject's task in one launch pair.  params is SoA float64 [12][P]:
+ * rows v, sv, a, z, sz, t, st, p_outlier, w_outlier, q, alpha, pos_alpha. */
+int hddm_wiener_like_rlddm_batch(const double *x, const int64_t *response, const double *feedback,
+                                 const int64_t *split_by, int64_t n, const double *params, int64_t P,
+                                 double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                                 double *logp, unsigned long long *evals);
+/* wiener_like_rl, src/wfpt.pyx:158-241: choice-only likelihood (the reference accepts and ignores
+ * err, n_st, n_sz, use_adaptive, simps_err; they are not part of this signature). */
+int hddm_wiener_like_rl(const int64_t *response, const double *feedback, const int64_t *split_by,
+                        int64_t n, double q, double alpha, double pos_alpha, double v, double z,
+                        double p_outlier, double w_outlier, double *logp);
+/* NEW: params SoA float64 [7][P]: rows q, alpha, pos_alpha, v, z, p_outlier, w_outlier. */
+int hddm_wiener_like_rl_batch(const int64_t *response, const double *feedback, const int64_t *split_by,
+                              int64_t n, const double *params, int64_t P, double *logp);
+/* wiener_like_multi_rlddm, src/wfpt.pyx:277-320.  par[k] / stride[k] for k = v, sv, a, z, sz, t, st,
+ * alpha (stride 0 scalar, 1 per trial).  Trials in the caller's order; Q values restart where split_by
+ * differs from the previous trial; every trial is scored; single learning rate; no zero-density guard
+ * and no +-999 sentinels. */
+int hddm_wiener_like_multi_rlddm(const double *x, const int64_t *response, const double *feedback,
+                                 const int64_t *split_by, int64_t n, double q, const double *const par[8],
+                                 const int64_t stride[8], double err, int n_st, int n_sz, int use_adaptive,
+                                 double simps_err, double p_outlier, double w_outlier, double *logp);
+
 /* ---- device-resident trials (one upload per observed node, reused every MCMC step) --------- */
 typedef struct hddm_trials hddm_trials; /* opaque */
 int hddm_trials_upload(const double *x, int64_t n, hddm_trials **out);

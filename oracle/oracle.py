@@ -58,6 +58,13 @@ def lib():
         L.wo_gen_cdf_using_pdf.argtypes = [c_dp, l] + [d] * 8 + [i, i, i, d, d, d, c_dp]
         L.wo_gen_rts_from_cdf.restype = None
         L.wo_gen_rts_from_cdf.argtypes = [c_dp, l] + [d] * 7 + [c_dp, c_dp, l, c_dp, c_dp]
+        L.wo_wiener_like_rlddm.restype = d
+        L.wo_wiener_like_rlddm.argtypes = [c_dp, c_lp, c_dp, c_lp, l] + [d] * 11 + [i, i, i, d, d, d]
+        L.wo_wiener_like_rl.restype = d
+        L.wo_wiener_like_rl.argtypes = [c_lp, c_dp, c_lp, l] + [d] * 7
+        L.wo_wiener_like_multi_rlddm.restype = d
+        L.wo_wiener_like_multi_rlddm.argtypes = [c_dp, c_lp, c_dp, c_lp, l, d, C.POINTER(c_dp), c_lp,
+                                                 d, i, i, i, d, d, d]
         L.wo_cdfdif.restype = d
         L.wo_cdfdif.argtypes = [d, i, c_dp, c_dp]
         L.wo_dmat_cdf_array.restype = i
@@ -138,6 +145,59 @@ def wiener_like_multi(x, v, sv, a, z, sz, t, st, err, multi=None, n_st=10, n_sz=
         args += [_p(arr), stride]
     return lib().wo_wiener_like_multi(_p(x), x.size, *args, err, n_st, n_sz, int(use_adaptive),
                                       simps_err, p_outlier, w_outlier)
+
+
+def _i64(a):
+    a = np.asarray(a)
+    if a.dtype.kind not in "iu" or a.ndim != 1:
+        raise ValueError("Buffer dtype mismatch / wrong number of dimensions")
+    return np.ascontiguousarray(a, dtype=np.int64)
+
+
+def wiener_like_rlddm(x, response, feedback, split_by, q, alpha, pos_alpha, v, sv, a, z, sz, t, st, err,
+                      n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-8, p_outlier=0, w_outlier=0):
+    x, feedback = _f64(x), _f64(feedback)
+    response, split_by = _i64(response), _i64(split_by)
+    return lib().wo_wiener_like_rlddm(_p(x), response.ctypes.data_as(c_lp), _p(feedback),
+                                      split_by.ctypes.data_as(c_lp), x.size, q, alpha, pos_alpha, v, sv, a,
+                                      z, sz, t, st, err, n_st, n_sz, int(use_adaptive), simps_err, p_outlier,
+                                      w_outlier)
+
+
+def wiener_like_rl(response, feedback, split_by, q, alpha, pos_alpha, v, z, err=1e-4, n_st=10, n_sz=10,
+                   use_adaptive=1, simps_err=1e-8, p_outlier=0, w_outlier=0):
+    feedback = _f64(feedback)
+    response, split_by = _i64(response), _i64(split_by)
+    return lib().wo_wiener_like_rl(response.ctypes.data_as(c_lp), _p(feedback), split_by.ctypes.data_as(c_lp),
+                                   response.size, q, alpha, pos_alpha, v, z, p_outlier, w_outlier)
+
+
+_RL_NAMES = _NAMES + ("alpha",)
+
+
+def wiener_like_multi_rlddm(x, response, feedback, split_by, q, v, sv, a, z, sz, t, st, alpha, err,
+                            multi=None, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-3, p_outlier=0,
+                            w_outlier=0):
+    x, feedback = _f64(x), _f64(feedback)
+    response, split_by = _i64(response), _i64(split_by)
+    vals = dict(zip(_RL_NAMES, (v, sv, a, z, sz, t, st, alpha)))
+    multi = set(multi or ())
+    keep, strides = [], []
+    for name in _RL_NAMES:
+        if name in multi:
+            arr = np.ascontiguousarray(np.asarray(vals[name], dtype=np.float64))
+            assert arr.shape == x.shape
+            strides.append(1)
+        else:
+            arr = np.array([vals[name]], dtype=np.float64)
+            strides.append(0)
+        keep.append(arr)
+    ptrs = (c_dp * 8)(*[_p(k) for k in keep])
+    st_arr = np.asarray(strides, dtype=np.int64)
+    return lib().wo_wiener_like_multi_rlddm(_p(x), response.ctypes.data_as(c_lp), _p(feedback),
+                                            split_by.ctypes.data_as(c_lp), x.size, q, ptrs,
+                                            st_arr.ctypes.data_as(c_lp), err, n_st, n_sz, int(use_adaptive),
+                                            simps_err, p_outlier, w_outlier)
 
 
 def wiener_like_contaminant(x, cont_x, v, sv, a, z, sz, t, st, t_min, t_max, err, n_st=10, n_sz=10,

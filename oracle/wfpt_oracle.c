@@ -466,3 +466,131 @@ void wo_gen_rts_from_cdf(const double *xgrid, int64_t m, double v, double sv, do
         rts[i] = rt + sgn * shift;
     }
 }
+
+/* ---- reinforcement-learning likelihoods -------------------------------- */
+
+/* learning rate on the logit scale, src/wfpt.pyx:123-126: 2.718281828459**a / (1 + 2.718281828459**a)
+ * (the reference's truncated e, lowered by Cython to pow()). */
+static double rl_rate(double logit) { return pow(2.718281828459, logit) / (1 + pow(2.718281828459, logit)); }
+
+/* Conditions in the order of np.unique(split_by) (ascending), each visited with its trials in the
+ * caller's order (boolean-mask selection, src/wfpt.pyx:112-118).  next_condition returns 0 when
+ * none is left; *cur is the condition just handled (start with have_cur = 0). */
+static int next_condition(const int64_t *split_by, int64_t n, int have_cur, int64_t cur, int64_t *out)
+{
+    int found = 0;
+    int64_t i, best = 0;
+    for (i = 0; i < n; i++)
+        if ((!have_cur || split_by[i] > cur) && (!found || split_by[i] < best)) {
+            best = split_by[i];
+            found = 1;
+        }
+    *out = best;
+    return found;
+}
+
+/* src/wfpt.pyx:79-155  wiener_like_rlddm.  response is 0 (lower) / 1 (upper), int64 like the
+ * reference's np.ndarray[long]. */
+double wo_wiener_like_rlddm(const double *x, const int64_t *response, const double *feedback,
+                            const int64_t *split_by, int64_t n, double q, double alpha,
+                            double pos_alpha, double v, double sv, double a, double z, double sz,
+                            double t, double st, double err, int n_st, int n_sz, int use_adaptive,
+                            double simps_err, double p_outlier, double w_outlier)
+{
+    double total = 0.0, mix = w_outlier * p_outlier, qs[2], alfa, pos_alfa, d;
+    int64_t s = 0, i;
+    int have = 0;
+    if (!((p_outlier >= 0) & (p_outlier <= 1))) return -INFINITY;
+    pos_alfa = (pos_alpha == 100.00) ? alpha : pos_alpha; /* :106-109 */
+    while (next_condition(split_by, n, have, s, &s)) {
+        int first = 1;
+        have = 1;
+        qs[0] = q;
+        qs[1] = q;
+        for (i = 0; i < n; i++) {
+            if (split_by[i] != s) continue;
+            if (!first) { /* :134-140: no density for the first trial of a condition */
+                d = wo_full_pdf(x[i], (qs[1] - qs[0]) * v, sv, a, z, sz, t, st, err, n_st, n_sz,
+                                use_adaptive, simps_err);
+                d = d * (1 - p_outlier) + mix;
+                if (d == 0) return -INFINITY;
+                total += log(d);
+            }
+            first = 0;
+            /* :122-131, :145-154 */
+            alfa = (feedback[i] > qs[response[i]]) ? rl_rate(pos_alfa) : rl_rate(alpha);
+            qs[response[i]] = qs[response[i]] + alfa * (feedback[i] - qs[response[i]]);
+        }
+    }
+    return total;
+}
+
+/* src/wfpt.pyx:158-241  wiener_like_rl: choice-only likelihood (softmax-like P(upper) of a unit
+ * boundary separation process), same Q-learning updates. */
+double wo_wiener_like_rl(const int64_t *response, const double *feedback, const int64_t *split_by,
+                         int64_t n, double q, double alpha, double pos_alpha, double v, double z,
+                         double p_outlier, double w_outlier)
+{
+    double total = 0.0, mix = w_outlier * p_outlier, qs[2], alfa, pos_alfa, d, drift;
+    int64_t s = 0, i;
+    int have = 0;
+    if (!((p_outlier >= 0) & (p_outlier <= 1))) return -INFINITY;
+    pos_alfa = (pos_alpha == 100.00) ? alpha : pos_alpha;
+    while (next_condition(split_by, n, have, s, &s)) {
+        int first = 1;
+        have = 1;
+        qs[0] = q;
+        qs[1] = q;
+        for (i = 0; i < n; i++) {
+            if (split_by[i] != s) continue;
+            if (!first) {
+                drift = (qs[1] - qs[0]) * v;
+                if (drift == 0) {
+                    d = 0.5;
+                } else if (response[i] == 1) { /* :213-216 */
+                    d = (pow(2.718281828459, -2 * z * drift) - 1) / (pow(2.718281828459, -2 * drift) - 1);
+                } else {
+                    d = 1 - (pow(2.718281828459, -2 * z * drift) - 1) / (pow(2.718281828459, -2 * drift) - 1);
+                }
+                d = d * (1 - p_outlier) + mix;
+                if (d == 0) return -INFINITY;
+                total += log(d);
+            }
+            first = 0;
+            alfa = (feedback[i] > qs[response[i]]) ? rl_rate(pos_alfa) : rl_rate(alpha);
+            qs[response[i]] = qs[response[i]] + alfa * (feedback[i] - qs[response[i]]);
+        }
+    }
+    return total;
+}
+
+/* src/wfpt.pyx:277-320  wiener_like_multi_rlddm: trials in the caller's order, Q values reset
+ * where split_by changes between neighbours (:300-303), every trial scored (no first-trial skip),
+ * single learning rate (no pos_alpha), no zero-density guard.  par order: v, sv, a, z, sz, t, st,
+ * alpha as (pointer, stride) pairs (stride 0 = scalar, 1 = per trial: the `multi` names). */
+double wo_wiener_like_multi_rlddm(const double *x, const int64_t *response, const double *feedback,
+                                  const int64_t *split_by, int64_t n, double q,
+                                  const double *const par[8], const int64_t stride[8], double err,
+                                  int n_st, int n_sz, int use_adaptive, double simps_err,
+                                  double p_outlier, double w_outlier)
+{
+    double total = 0.0, mix = w_outlier * p_outlier, qs[2], d, alfa;
+    int64_t i;
+    qs[0] = q;
+    qs[1] = q;
+    for (i = 0; i < n; i++) {
+        if (i != 0 && split_by[i] != split_by[i - 1]) {
+            qs[0] = q;
+            qs[1] = q;
+        }
+        d = wo_full_pdf(x[i], par[0][i * stride[0]] * (qs[1] - qs[0]), par[1][i * stride[1]],
+                        par[2][i * stride[2]], par[3][i * stride[3]], par[4][i * stride[4]],
+                        par[5][i * stride[5]], par[6][i * stride[6]], err, n_st, n_sz, use_adaptive,
+                        simps_err);
+        d = d * (1 - p_outlier) + mix;
+        total += log(d);
+        alfa = rl_rate(par[7][i * stride[7]]);
+        qs[response[i]] = qs[response[i]] + alfa * (feedback[i] - qs[response[i]]);
+    }
+    return total;
+}

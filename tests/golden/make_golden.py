@@ -206,10 +206,73 @@ def cdfs(W, CW):
     return out
 
 
+def rl_task(rng, n, n_cond, binary_feedback=True):
+    """A two-armed-bandit session in the layout of hddm/models/hddm_rl.py:61-73: split_by = condition,
+    response 0/1, feedback = reward received, signed RT by response."""
+    split_by = rng.integers(0, n_cond, n).astype(np.int64)
+    response = rng.integers(0, 2, n).astype(np.int64)
+    feedback = (rng.random(n) < np.where(response == 1, 0.8, 0.3)).astype(np.float64) if binary_feedback \
+        else rng.normal(0.5, 0.3, n)
+    x = (0.35 + rng.gamma(2.0, 0.25, n)) * np.where(response == 1, 1.0, -1.0)
+    return x, response, feedback, split_by
+
+
+def rl(W):
+    """wiener_like_rlddm / wiener_like_rl / wiener_like_multi_rlddm (src/wfpt.pyx:79-241,277-320): the
+    reference has no known-answer tests for them; pinned by these outputs of the compiled reference."""
+    rng = np.random.default_rng(7004)
+    out = {}
+    RLN = PNAMES + ("alpha",)
+    for k in range(12):
+        n, n_cond = (240, 3) if k % 3 else (90, 1)
+        x, response, feedback, split_by = rl_task(rng, n, n_cond, binary_feedback=(k % 4 != 3))
+        q = 0.5
+        alpha = rng.normal(0, 1.5)
+        pos_alpha = 100.0 if k % 2 == 0 else rng.normal(0, 1.5)
+        v = rng.uniform(0.5, 6)
+        P = draw_params(rng, 1, k & 1, k & 2, k & 4)[0]
+        P[0], P[2], P[5] = v, rng.uniform(0.8, 2.5), rng.uniform(0.1, 0.3)
+        num = (1e-4, 2, 2, 1, 1e-3) if k < 9 else (1e-4, 10, 10, 1, 1e-8)
+        outl = (0.05, 0.1) if k != 5 else (0.0, 0.1)
+        if k == 7:
+            x[5] = np.sign(x[5]) * 0.01  # zero density -> -inf only with p_outlier = 0 ... exercised at k == 5 too
+        if k == 5:
+            x[11] = np.sign(x[11]) * 0.01
+        out["rl_x_%d" % k] = x
+        out["rl_resp_%d" % k] = response
+        out["rl_fb_%d" % k] = feedback
+        out["rl_split_%d" % k] = split_by
+        out["rl_p_%d" % k] = np.array([q, alpha, pos_alpha] + list(P) + list(num) + list(outl))
+        out["rl_ddm_%d" % k] = np.array(W.wiener_like_rlddm(x, response, feedback, split_by, q, alpha, pos_alpha,
+                                                            *P, num[0], num[1], num[2], num[3], num[4], *outl))
+        out["rl_choice_%d" % k] = np.array(W.wiener_like_rl(response, feedback, split_by, q, alpha, pos_alpha,
+                                                            v, P[3], p_outlier=outl[0], w_outlier=outl[1]))
+        # regression flavour: trials in the caller's order, split_by sorted so that resets are per block
+        multi = [("v",), ("v", "alpha"), ("a", "t"), ("v", "sv", "a", "z", "sz", "t", "st", "alpha")][k % 4]
+        sb = np.sort(split_by)
+        per = np.concatenate([draw_params(rng, n), rng.normal(0, 1, (n, 1))], axis=1)
+        per[:, 0] = np.abs(per[:, 0]) + 0.5
+        cols = np.tile(np.array(list(P) + [alpha]), (n, 1))
+        for nm in multi:
+            j = RLN.index(nm)
+            cols[:, j] = per[:, j]
+        args = [cols[:, j].copy() if RLN[j] in multi else cols[0, j] for j in range(8)]
+        y = W.wiener_like_multi_rlddm(x, response, feedback, sb, q, *args, 1e-4, list(multi), 2, 2, 1, 1e-3, *outl)
+        out["rl_msplit_%d" % k] = sb
+        out["rl_mcols_%d" % k] = cols
+        out["rl_multi_%d" % k] = np.array([RLN.index(nm) for nm in multi])
+        out["rl_my_%d" % k] = np.array(y)
+    out["rl_n"] = np.array(12)
+    return out
+
+
 def main():
     if not ref.available():
         raise SystemExit("oracle/_ref not built: python oracle/build_ref.py")
     W, CW = ref.wfpt(), ref.cdfdif_wrapper()
+    if "--only-rl" in sys.argv:  # added after the first fixtures were frozen: leaves them untouched
+        np.savez_compressed(os.path.join(HERE, "ref_rl.npz"), **rl(W))
+        return
     n = matlab()
     rows, outs = pointwise(W)
     np.savez_compressed(os.path.join(HERE, "ref_full_pdf.npz"), rows=rows, out=outs)
