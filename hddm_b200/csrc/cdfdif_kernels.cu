@@ -56,17 +56,23 @@ __device__ __forceinline__ double ordered_lane_sum(double val, int count)
 __global__ void __launch_bounds__(128) k_cdf_array(const CdfArgs q)
 {
     const int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (i >= q.n) return;
+    if (i >= q.n * q.n_sets) return;
     const int lane = threadIdx.x & 31;
+    // batch: warp i evaluates RT i % n of parameter set i / n (x, y are [n_sets][n])
+    const int64_t set = q.par_sets ? i / q.n : 0;
+    if (q.ok && q.ok[set] == 0) return;
+    double par[kNumPar];
+#pragma unroll
+    for (int k = 0; k < kNumPar; ++k) par[k] = q.par_sets ? __ldg(q.par_sets + k * q.n_sets + set) : q.par[k];
 
     // wrapper rescale to DMAT units, src/cdfdif_wrapper.pyx:36-42 (par: v sv a z sz t st po wo)
-    const double a = q.par[2] / 10.;
-    const double Ter = q.par[5];
-    const double eta = q.par[1] / 10. + 1e-10;
-    const double z = q.par[3] * (q.par[2] / 10.);
-    const double sZ = q.par[4] * (q.par[2] / 10.) + 1e-10;
-    const double st = q.par[6] + 1e-10;
-    const double nu = q.par[0] / 10.;
+    const double a = par[2] / 10.;
+    const double Ter = par[5];
+    const double eta = par[1] / 10. + 1e-10;
+    const double z = par[3] * (par[2] / 10.);
+    const double sZ = par[4] * (par[2] / 10.) + 1e-10;
+    const double st = par[6] + 1e-10;
+    const double nu = par[0] / 10.;
 
     const double xs = q.x[i];
     const double t = fabs(xs);
@@ -194,7 +200,7 @@ __global__ void __launch_bounds__(128) k_cdf_array(const CdfArgs q)
     if (lane == 0) {  // src/cdfdif_wrapper.pyx:46-51
         const double sgn = (double)((xs > 0) - (xs < 0));
         double y = (1 - prob) + sgn * F;
-        const double po = q.par[7], wo = q.par[8];
+        const double po = par[7], wo = par[8];
         y = y * (1 - po) + (xs + (1. / (2 * wo))) * wo * po;
         q.y[i] = y;
     }
@@ -202,9 +208,12 @@ __global__ void __launch_bounds__(128) k_cdf_array(const CdfArgs q)
 
 cudaError_t launch_cdf_array(const CdfArgs& a, cudaStream_t stream)
 {
-    if (a.n <= 0) return cudaSuccess;
+    const int64_t warps = a.n * (a.par_sets ? a.n_sets : 1);
+    if (warps <= 0) return cudaSuccess;
+    CdfArgs b = a;
+    if (!b.par_sets) b.n_sets = 1;
     const int warps_per_block = 4;
-    k_cdf_array<<<(unsigned)((a.n + warps_per_block - 1) / warps_per_block), 128, 0, stream>>>(a);
+    k_cdf_array<<<(unsigned)((warps + warps_per_block - 1) / warps_per_block), 128, 0, stream>>>(b);
     return cudaGetLastError();
 }
 

@@ -77,6 +77,9 @@ struct LikeArgs {
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream);
 extern int g_kernel_choice;  // 0 auto, 1 generic evaluator only
 
+// par_sets == nullptr: one parameter set (par) over x[n] -> y[n].  Otherwise n_sets parameter sets, SoA
+// [9][n_sets]; set s (blockIdx.y) reads x + s * x_set_stride (0: one grid shared by all sets) and writes
+// y + s * n: the density tables of many posterior draws in one launch.
 struct PdfArgs {
     const double* x;
     double* y;
@@ -86,15 +89,23 @@ struct PdfArgs {
     Numerics nm;
     SeriesTable tab;
     unsigned long long* evals;
+    const double* par_sets = nullptr;
+    int64_t n_sets = 1;
+    int64_t x_set_stride = 0;
 };
 cudaError_t launch_pdf_array(const PdfArgs& a, cudaStream_t stream);
 
 // cdfdif (src/cdfdif.c:59-221 + src/cdfdif_wrapper.pyx:36-51): y[i] for signed RT x[i].
+// par_sets != nullptr: n_sets parameter sets (SoA [9][n_sets]), x and y are [n_sets][n]; sets whose
+// ok[s] == 0 (out of support, flagged by the host) are skipped and their y left untouched.
 struct CdfArgs {
     const double* x;
     double* y;
     int64_t n;
     double par[kNumPar];
+    const double* par_sets = nullptr;
+    const int32_t* ok = nullptr;
+    int64_t n_sets = 1;
 };
 cudaError_t launch_cdf_array(const CdfArgs& a, cudaStream_t stream);
 
@@ -105,6 +116,21 @@ cudaError_t launch_cumsum_normalise(double* table, int64_t m, cudaStream_t strea
 cudaError_t launch_sample_rts(const double* xgrid, const double* table, int64_t m, const double* f,
                               const double* u_delay, int64_t samples, double t, double st,
                               double* rts, cudaStream_t stream);
+
+// Posterior-predictive batch (ppc_kernels.cu): D draws share the grid; tables is [D][m] densities in,
+// normalised rectangle-rule cumulative tables out (src/wfpt.pyx:333-340 per draw).
+cudaError_t launch_cumsum_normalise_batch(double* tables, int64_t m, int64_t D, cudaStream_t stream);
+// rts[d][s] by inverse-CDF lookup (src/wfpt.pyx:344-353); t / st per draw; uniforms either supplied
+// (f, u_delay: [D][S]) or, when f == nullptr, drawn on the device from Philox(seed, draw0 + d, s).
+cudaError_t launch_sample_rts_batch(const double* xgrid, const double* tables, int64_t m, const double* f,
+                                    const double* u_delay, int64_t S, int64_t D, const double* t,
+                                    const double* st, unsigned long long seed, int64_t draw0, double* rts,
+                                    cudaStream_t stream);
+// Summary statistics of hddm/utils.py:241-267 (gen_ppc_stats) per draw: stats[d][15] = accuracy,
+// mean_ub, std_ub, 10/30/50/70/90 q_ub, mean_lb, std_lb, 10/30/50/70/90 q_lb.  S <= kPpcMaxSamples.
+constexpr int kPpcStats = 15;
+constexpr int64_t kPpcMaxSamples = 16384;
+cudaError_t launch_ppc_stats(const double* rts, int64_t S, int64_t D, double* stats, cudaStream_t stream);
 
 // Reinforcement-learning likelihoods (rl_kernels.cu; src/wfpt.pyx:79-241,277-320).  The Q-learning
 // recursion depends only on (response, feedback, learning rates), never on the densities: it runs as a

@@ -205,24 +205,30 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     constexpr int KT = KMAX > 0 ? KMAX : 1;
     __shared__ GridSet<KT> gs;
     WTable<KT>* wt = gs.wt;
+    double par[kNumPar];
+    const int64_t set = blockIdx.y;
+#pragma unroll
+    for (int k = 0; k < kNumPar; ++k) par[k] = a.par_sets ? __ldg(a.par_sets + k * a.n_sets + set) : a.par[k];
+    const double* __restrict__ xs = a.x + set * a.x_set_stride;
+    double* __restrict__ ys = a.y + set * a.n;
     if (GRID)
-        build_gridset<KT>(gs, a.par, a.tab);
+        build_gridset<KT>(gs, par, a.tab);
     else if (KMAX > 0)
-        build_wtables<KT>(wt, a.par[3], a.par[4]);
+        build_wtables<KT>(wt, par[3], par[4]);
     unsigned long long evals = 0;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
         double d;
         if (GRID)
-            d = full_pdf_grid<KT>(__ldg(a.x + i), a.par[0], gs, a.nm, &a.tab, evals);
+            d = full_pdf_grid<KT>(__ldg(xs + i), par[0], gs, a.nm, &a.tab, evals);
         else if (KMAX > 0)
-            d = full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(__ldg(a.x + i), a.par[0], a.par[1], a.par[2], a.par[3],
-                                                     a.par[4], a.par[5], a.par[6], a.nm, &a.tab, wt, evals);
+            d = full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(__ldg(xs + i), par[0], par[1], par[2], par[3],
+                                                     par[4], par[5], par[6], a.nm, &a.tab, wt, evals);
         else
-            d = full_pdf(__ldg(a.x + i), a.par[0], a.par[1], a.par[2], a.par[3], a.par[4], a.par[5],
-                         a.par[6], a.nm, &a.tab, evals);
-        d = d * (1 - a.par[7]) + (a.par[8] * a.par[7]);
-        a.y[i] = a.logp == 1 ? log(d) : d;
+            d = full_pdf(__ldg(xs + i), par[0], par[1], par[2], par[3], par[4], par[5],
+                         par[6], a.nm, &a.tab, evals);
+        d = d * (1 - par[7]) + (par[8] * par[7]);
+        ys[i] = a.logp == 1 ? log(d) : d;
     }
     if (a.evals) {
         evals = warp_sum_u64(evals);
@@ -233,23 +239,31 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
 cudaError_t launch_pdf_array(const PdfArgs& a, cudaStream_t stream)
 {
     if (a.n <= 0) return cudaSuccess;
-    int64_t blocks = (a.n + kLikeThreads - 1) / kLikeThreads;
-    if (blocks > 148 * 64) blocks = 148 * 64;
     PdfArgs b = a;
+    if (!b.par_sets) {
+        b.n_sets = 1;
+        b.x_set_stride = 0;
+    }
+    if (b.n_sets <= 0) return cudaSuccess;
+    if (b.n_sets > 65535) return cudaErrorInvalidValue;
+    // one CTA builds the per-set tables once, so with many sets give each CTA >= 2048 points
+    int64_t blocks = (a.n + kLikeThreads - 1) / kLikeThreads;
+    if (b.n_sets > 1) blocks = (a.n + kTrialsPerBlock - 1) / kTrialsPerBlock;
+    if (blocks > 148 * 64) blocks = 148 * 64;
     b.tab = series_table_for(a.nm.err);
     const bool fast = g_kernel_choice != 1 && a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 &&
                       b.tab.max_large_k <= 8;
     const bool gridk = fast && g_kernel_choice != 2;
     if (gridk && b.tab.max_large_k <= 4)
-        k_pdf_array<4, true><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+        k_pdf_array<4, true><<<dim3((unsigned)blocks, (unsigned)b.n_sets), kLikeThreads, 0, stream>>>(b);
     else if (gridk)
-        k_pdf_array<8, true><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+        k_pdf_array<8, true><<<dim3((unsigned)blocks, (unsigned)b.n_sets), kLikeThreads, 0, stream>>>(b);
     else if (fast && b.tab.max_large_k <= 4)
-        k_pdf_array<4, false><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+        k_pdf_array<4, false><<<dim3((unsigned)blocks, (unsigned)b.n_sets), kLikeThreads, 0, stream>>>(b);
     else if (fast)
-        k_pdf_array<8, false><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+        k_pdf_array<8, false><<<dim3((unsigned)blocks, (unsigned)b.n_sets), kLikeThreads, 0, stream>>>(b);
     else
-        k_pdf_array<0, false><<<(unsigned)blocks, kLikeThreads, 0, stream>>>(b);
+        k_pdf_array<0, false><<<dim3((unsigned)blocks, (unsigned)b.n_sets), kLikeThreads, 0, stream>>>(b);
     return cudaGetLastError();
 }
 

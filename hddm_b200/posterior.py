@@ -1,0 +1,120 @@
+"""Posterior-predictive batch on the GPU (BASELINE config 5).
+
+The reference's posterior predictive check loops in Python: for every posterior draw and every observed
+node, `node.random()` (hddm/likelihoods.py:76-81 -> hddm/generate.py:190-194 -> wfpt.gen_rts_from_cdf,
+src/wfpt.pyx:323-354) simulates one data set, and hddm/utils.py:241-298 reduces it to summary statistics
+(accuracy, mean / std / quantiles per boundary).  Here all draws of a node go through the GPU together and
+only the statistics need to come back; the chi-square / G-square quantile objectives
+(hddm/likelihoods.py:198-239) likewise evaluate `cdfdif` for many parameter sets in one launch.
+
+Draws are independent, so under torch.distributed they are sharded in contiguous blocks over the ranks
+(`shard_bounds` of hddm_b200/batch.py) and only the [D, 15] statistics / [D, n] probabilities are gathered.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check, dptr, lib
+
+STAT_NAMES = (("accuracy", "mean_ub", "std_ub") + tuple("%dq_ub" % q for q in (10, 30, 50, 70, 90)) +
+              ("mean_lb", "std_lb") + tuple("%dq_lb" % q for q in (10, 30, 50, 70, 90)))  # hddm/utils.py:250-266
+MAX_SAMPLES = 16384
+
+
+def _params7(params):
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    if params.ndim != 2 or params.shape[0] != 7:
+        raise ValueError("params must be float64 [7, D]: v, sv, a, z, sz, t, st")
+    return params
+
+
+def gen_rts_from_cdf_batch(params, samples=1000, cdf_lb=-6, cdf_ub=6, dt=1e-2, f=None, u_delay=None, seed=None,
+                           return_rts=True, return_stats=False):
+    """gen_rts_from_cdf (src/wfpt.pyx:323-354) for D posterior draws in one pass.
+
+    params: float64 [7, D] (rows v, sv, a, z, sz, t, st).  Uniforms: `f` / `u_delay` float64 [D, samples]
+    (the reference's draw order per call is f, then the delays when st != 0), or `seed` for device-side
+    Philox uniforms, or neither -- then numpy's global RNG is used draw by draw exactly as D reference
+    calls would.  Returns rts [D, samples] and/or stats [D, 15] (columns STAT_NAMES)."""
+    params = _params7(params)
+    D = params.shape[1]
+    x = np.arange(cdf_lb, cdf_ub, dt)
+    rts = np.empty((D, samples), dtype=np.double) if return_rts else None
+    stats = np.empty((D, len(STAT_NAMES)), dtype=np.double) if return_stats else None
+    rp = dptr(rts) if rts is not None else None
+    sp = dptr(stats) if stats is not None else None
+    if seed is not None:
+        check(lib().hddm_gen_rts_from_cdf_batch_seeded(dptr(x), x.shape[0], dptr(params), D, int(seed), samples, rp, sp))
+    else:
+        if f is None:
+            f = np.empty((D, samples))
+            u_delay = np.zeros((D, samples))
+            for d in range(D):  # numpy's global stream in the order of D successive reference calls
+                f[d] = np.random.rand(samples)
+                if params[6, d] != 0:
+                    u_delay[d] = np.random.rand(samples)
+        f = np.ascontiguousarray(f, dtype=np.float64)
+        if f.shape != (D, samples):
+            raise ValueError("f must be [D, samples]")
+        up = None
+        if u_delay is not None:
+            u_delay = np.ascontiguousarray(u_delay, dtype=np.float64)
+            if u_delay.shape != (D, samples):
+                raise ValueError("u_delay must be [D, samples]")
+            up = dptr(u_delay)
+        check(lib().hddm_gen_rts_from_cdf_batch(dptr(x), x.shape[0], dptr(params), D, dptr(f), up, samples, rp, sp))
+    if return_rts and return_stats:
+        return rts, stats
+    return rts if return_rts else stats
+
+
+def ppc_stats(rts):
+    """Statistics of hddm/utils.py:241-267 for D data sets: rts float64 [D, samples] of signed RTs (or a
+    single vector) -> [D, 15] (columns STAT_NAMES)."""
+    rts = np.ascontiguousarray(np.atleast_2d(np.asarray(rts, dtype=np.float64)))
+    D, S = rts.shape
+    out = np.empty((D, len(STAT_NAMES)), dtype=np.double)
+    check(lib().hddm_ppc_stats(dptr(rts), D, S, dptr(out)))
+    return out
+
+
+def dmat_cdf_batch(x, params, return_status=False):
+    """dmat_cdf_array (src/cdfdif_wrapper.pyx:16-52) for D parameter sets: x float64 [D, n] signed RTs (set
+    d's quantile edges), params float64 [9, D] (v, sv, a, z, sz, t, st, p_outlier, w_outlier).  Returns y
+    [D, n]; rows where the reference would raise (out of support, RT range) are NaN and flagged in status."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    if x.ndim != 2 or params.ndim != 2 or params.shape != (9, x.shape[0]):
+        raise ValueError("x must be [D, n] and params [9, D]")
+    if (params[8] == 0).any():
+        raise ZeroDivisionError("float division")  # src/cdfdif_wrapper.pyx:12
+    D, n = x.shape
+    y = np.empty((D, n), dtype=np.double)
+    status = np.zeros(D, dtype=np.int32)
+    check(lib().hddm_dmat_cdf_batch(dptr(x), n, dptr(params), D, dptr(y), status.ctypes.data_as(_lib.c_ip)))
+    return (y, status) if return_status else y
+
+
+def quantile_objectives(emp_rt, freq_obs, n_samples, params):
+    """chi-square and G-square of hddm/likelihoods.py:198-239 for D parameter sets against D nodes'
+    quantile statistics: emp_rt [D, n_edges] signed quantile edges, freq_obs [D, n_edges + 1] observed
+    counts per bin, n_samples [D].  Returns (chisq [D], gsq [D]); sets out of support give (inf, -inf)
+    as the reference's except-branches do (:221-223, :236-238)."""
+    from scipy import stats
+    emp_rt = np.ascontiguousarray(emp_rt, dtype=np.float64)
+    freq_obs = np.asarray(freq_obs, dtype=np.float64)
+    n_samples = np.asarray(n_samples, dtype=np.float64)
+    cdf, status = dmat_cdf_batch(emp_rt, params, return_status=True)
+    D = emp_rt.shape[0]
+    chisq, gsq = np.full(D, np.inf), np.full(D, -np.inf)
+    for d in range(D):
+        if status[d] == _lib.ERR_RT_RANGE:
+            raise AssertionError("1. / (2*w_outlier) must be smaller than RT")
+        if status[d] != _lib.OK:
+            continue
+        prop = np.diff(np.concatenate(([0.], cdf[d], [1.])))  # :207-212
+        prop[prop <= 1e-6] = 1e-6
+        chisq[d] = stats.chisquare(freq_obs[d], prop * n_samples[d])[0]
+        gsq[d] = 2 * np.sum(freq_obs[d] * np.log(prop))
+    return chisq, gsq

@@ -137,6 +137,37 @@ int hddm_wiener_like_multi_batch(const double *x, int64_t n, const double *v_tri
                                  int use_adaptive, double simps_err, double *logp,
                                  unsigned long long *evals);
 
+/* ---- NEW: posterior-predictive batch (many posterior draws per call) ------------------------- */
+
+/* gen_rts_from_cdf (src/wfpt.pyx:323-354) for D posterior draws on one shared grid xgrid[m]
+ * (= arange(cdf_lb, cdf_ub, dt)): the per-draw loop of kabuki's post_pred_gen over Wfpt.random
+ * (hddm/likelihoods.py:76-81 -> hddm/generate.py:190-194).  params is SoA float64 [7][D]: rows v, sv, a,
+ * z, sz, t, st.  f and u_delay are the caller's uniforms, [D][samples] (u_delay may be NULL when every
+ * st == 0).  rts (optional) receives [D][samples]; stats (optional) receives [D][15]: the statistics of
+ * hddm/utils.py:241-267 (gen_ppc_stats) per simulated data set -- accuracy, mean_ub, std_ub, 10/30/50/
+ * 70/90 q_ub, mean_lb, std_lb, 10/30/50/70/90 q_lb (scipy scoreatpercentile semantics; NaN where a
+ * boundary has no responses; mean_lb is of the signed RTs, as in the reference).  With stats,
+ * 1 <= samples <= 16384. */
+int hddm_gen_rts_from_cdf_batch(const double *xgrid, int64_t m, const double *params, int64_t D,
+                                const double *f, const double *u_delay, int64_t samples, double *rts,
+                                double *stats);
+/* Same with the uniforms drawn on the device: Philox4x32-10 keyed by seed, one counter sequence per
+ * (draw, sample) -- reproducible, independent of slab size and of how draws are sharded over GPUs when
+ * every rank passes its global draw offset through `params` order.  Not numpy's stream. */
+int hddm_gen_rts_from_cdf_batch_seeded(const double *xgrid, int64_t m, const double *params, int64_t D,
+                                       unsigned long long seed, int64_t samples, double *rts,
+                                       double *stats);
+/* The statistics alone, for D data sets of `samples` signed RTs each ([D][samples] -> [D][15]); used for
+ * the observed data of a posterior predictive check. */
+int hddm_ppc_stats(const double *rts, int64_t D, int64_t samples, double *stats);
+/* dmat_cdf_array (src/cdfdif_wrapper.pyx:16-52) for D parameter sets in one launch: x and y are
+ * [D][n] (set d's own quantile edges, hddm/likelihoods.py:198-203), params is SoA float64 [9][D]
+ * (v, sv, a, z, sz, t, st, p_outlier, w_outlier).  status[d] = HDDM_OK, HDDM_ERR_SUPPORT or
+ * HDDM_ERR_RT_RANGE per set (where the reference raises ValueError / AssertionError); rows of y whose
+ * status is not HDDM_OK are NaN. */
+int hddm_dmat_cdf_batch(const double *x, int64_t n, const double *params, int64_t D, double *y,
+                        int32_t *status);
+
 /* ---- reinforcement-learning likelihoods (src/wfpt.pyx:79-241, 277-320) -------------------------- */
 
 /* wiener_like_rlddm, src/wfpt.pyx:79-155.  response (0 = lower, 1 = upper) and split_by (condition

@@ -1,0 +1,189 @@
+"""Posterior-predictive batch (BASELINE config 5): many posterior draws per call.
+
+CPU part: the statistics oracle (a one-for-one restatement of hddm/utils.py:241-267) on hand-checkable
+data.  GPU part: the batched CUDA path against (a) D scalar calls of the already-pinned single-draw entry
+points (bit for bit), (b) the C oracle of gen_rts_from_cdf / dmat_cdf_array on the same uniforms, (c) the
+statistics oracle, and -- for the device-RNG variant, whose stream cannot match numpy's -- distributional
+properties: reproducibility per seed, and agreement of the simulated quantiles with the analytic CDF."""
+import numpy as np
+import pytest
+
+from tests.util import assert_parity, cdf_noise_band, draw_params
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import oracle
+    oracle.build()
+    return oracle
+
+
+def test_stats_oracle_hand_values():
+    from oracle.ppc_oracle import ppc_stats
+    x = np.array([0.5, 0.7, 0.9, 1.1, 1.3, -0.4, -0.6, -0.8, 0.0])
+    s = ppc_stats(x)
+    assert s[0] == 5 / 9.
+    np.testing.assert_allclose(s[1], 0.9)
+    np.testing.assert_allclose(s[2], np.sqrt(0.08))
+    np.testing.assert_allclose(s[3:8], [0.58, 0.74, 0.9, 1.06, 1.22])   # idx = q/100*(5-1)
+    np.testing.assert_allclose(s[8], -0.6)                                # mean of the SIGNED lower RTs
+    np.testing.assert_allclose(s[10:15], [0.44, 0.52, 0.6, 0.68, 0.76])
+    only_upper = ppc_stats(np.array([0.5, 0.6]))
+    assert only_upper[0] == 1.0 and np.isnan(only_upper[8:]).all()
+
+
+# ---- GPU ---------------------------------------------------------------------------------------
+
+def _draws(rng, D):
+    p = draw_params(rng, D)
+    p[6, ::4] = 0.0   # some draws without st (no delay uniforms are consumed for them)
+    p[4, 1::5] = 0.0  # and without sz
+    p[1, 2::7] = 0.0  # and without sv
+    return np.ascontiguousarray(p)
+
+
+@pytest.mark.gpu
+def test_batch_equals_scalar_calls_and_oracle(gpu, O):
+    from hddm_b200 import posterior, wfpt
+    rng = np.random.default_rng(41)
+    D, S = 23, 300
+    params = _draws(rng, D)
+    f, u = rng.random((D, S)), rng.random((D, S))
+    rts, stats = posterior.gen_rts_from_cdf_batch(params, S, -5.0, 5.0, 1e-3, f=f, u_delay=u, return_stats=True)
+    exact = 0
+    for d in range(D):
+        one = wfpt.gen_rts_from_cdf(*params[:, d], S, -5.0, 5.0, 1e-3, f=f[d], u_delay=u[d])
+        assert np.array_equal(one, rts[d]), d  # same kernels, same order: bit for bit
+        want = O.gen_rts_from_cdf(*params[:, d], S, -5.0, 5.0, 1e-3, f=f[d], u_delay=u[d])
+        close = np.abs(rts[d] - want) <= 1e-12
+        exact += close.sum()
+        assert np.max(np.abs(rts[d] - want)) <= 1e-3 + 1e-12  # at most one grid step (discrete lookup)
+    assert exact >= 0.995 * D * S
+    # numpy's global stream, consumed draw by draw as D reference calls would
+    np.random.seed(7)
+    a = posterior.gen_rts_from_cdf_batch(params, S, -5.0, 5.0, 1e-3)
+    np.random.seed(7)
+    b = np.stack([wfpt.gen_rts_from_cdf(*params[:, d], S, -5.0, 5.0, 1e-3) for d in range(D)])
+    assert np.array_equal(a, b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("S", [1, 2, 37, 256, 1000, 5000])
+def test_stats_against_oracle(gpu, S):
+    from hddm_b200 import posterior
+    from oracle.ppc_oracle import ppc_stats
+    rng = np.random.default_rng(100 + S)
+    D = 12
+    rts = (0.3 + rng.gamma(2.0, 0.25, (D, S))) * np.where(rng.random((D, S)) < 0.7, 1.0, -1.0)
+    rts[0] = np.abs(rts[0])           # no lower-boundary responses -> NaN block
+    rts[1] = -np.abs(rts[1])          # no upper-boundary responses
+    if S > 2:
+        rts[2, :2] = 0.0              # zeros belong to neither boundary but count in the accuracy
+        rts[3, 1] = rts[3, 0]         # ties
+    got = posterior.ppc_stats(rts)
+    want = np.stack([ppc_stats(r) for r in rts])
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    m = ~np.isnan(want)
+    # sums are reduced in a different (fixed) order than numpy's pairwise sum: 1e-12, not bitwise
+    np.testing.assert_allclose(got[m], want[m], rtol=1e-12, atol=1e-15)
+    assert np.array_equal(got[:, 0], want[:, 0])  # accuracy is a ratio of counts: exact
+
+
+@pytest.mark.gpu
+def test_fused_stats_equal_stats_of_returned_rts(gpu):
+    from hddm_b200 import posterior
+    rng = np.random.default_rng(3)
+    D, S = 40, 200
+    params = _draws(rng, D)
+    f, u = rng.random((D, S)), rng.random((D, S))
+    rts, stats = posterior.gen_rts_from_cdf_batch(params, S, -5.0, 5.0, 1e-3, f=f, u_delay=u, return_stats=True)
+    again = posterior.ppc_stats(rts)
+    assert np.array_equal(np.isnan(stats), np.isnan(again))
+    assert np.array_equal(stats[~np.isnan(stats)], again[~np.isnan(again)])
+    only = posterior.gen_rts_from_cdf_batch(params, S, -5.0, 5.0, 1e-3, f=f, u_delay=u, return_rts=False,
+                                            return_stats=True)
+    assert np.array_equal(only[~np.isnan(only)], stats[~np.isnan(stats)])
+
+
+@pytest.mark.gpu
+def test_device_rng_is_reproducible_and_follows_the_cdf(gpu, O):
+    from hddm_b200 import posterior
+    rng = np.random.default_rng(8)
+    D, S = 6, 16000
+    params = _draws(rng, D)
+    a = posterior.gen_rts_from_cdf_batch(params, S, -6.0, 6.0, 1e-4, seed=123)
+    b = posterior.gen_rts_from_cdf_batch(params, S, -6.0, 6.0, 1e-4, seed=123)
+    c = posterior.gen_rts_from_cdf_batch(params, S, -6.0, 6.0, 1e-4, seed=124)
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+    # a sub-batch reproduces its rows only when offsets agree; the first draw always does
+    first = posterior.gen_rts_from_cdf_batch(params[:, :1].copy(), S, -6.0, 6.0, 1e-4, seed=123)
+    assert np.array_equal(first[0], a[0])
+    grid = np.arange(-6.0, 6.0, 1e-3)
+    for d in range(D):
+        # Kolmogorov distance between the simulated signed RTs and the CDF obtained by integrating the
+        # oracle's full_pdf (with t and st) on a fine grid.  (Not cdfdif: the reference's own 6-node
+        # Gauss-Hermite CDF is off by 0.02 from its own density for sv ~ 2.5, e.g. draw 1 here.)
+        pdf = O.pdf_array(grid, *params[:, d], 1e-4, 0, 2, 2, 1, 1e-3, 0, 0)
+        cdf = np.cumsum(pdf) * 1e-3
+        assert abs(cdf[-1] - 1) < 1e-3
+        xs = np.sort(a[d])
+        F = np.interp(xs, grid, cdf)
+        emp = np.arange(1, S + 1) / float(S)
+        # KS 0.1 % level + slack for the rectangle rules on both sides (dt * peak density)
+        assert np.max(np.abs(emp - F)) < 1.95 / np.sqrt(S) + 4e-3, d
+
+
+@pytest.mark.gpu
+def test_cdf_batch_against_scalar_calls_and_oracle(gpu, O):
+    from hddm_b200 import cdfdif_wrapper, posterior
+    rng = np.random.default_rng(12)
+    D, n = 29, 11
+    par7 = draw_params(rng, D)
+    par7[4] = np.maximum(par7[4], 0.02)  # full DDM: away from the 1e-10-epsilon regime (see cdf_noise_band)
+    par7[6] = np.maximum(par7[6], 0.02)
+    params = np.concatenate([par7, np.full((1, D), 0.05), np.full((1, D), 0.1)])
+    params[3, 5] = 0.97                  # out of support: z + sz/2 > 1
+    params[4, 5] = 0.2
+    x = (par7[5] + par7[6] / 2 + rng.gamma(2.0, 0.3, (n, D))).T * np.where(rng.random((D, n)) < 0.5, 1.0, -1.0)
+    x = np.ascontiguousarray(x)
+    x[9, 3] = 7.0                        # beyond 1/(2 w_outlier) = 5: the reference asserts
+    y, status = posterior.dmat_cdf_batch(x, params, return_status=True)
+    for d in range(D):
+        if d == 5:
+            assert status[d] == 3 and np.isnan(y[d]).all()
+            with pytest.raises(ValueError):
+                cdfdif_wrapper.dmat_cdf_array(x[d], *params[:, d])
+            continue
+        if d == 9:
+            assert status[d] == 4 and np.isnan(y[d]).all()
+            with pytest.raises(AssertionError):
+                cdfdif_wrapper.dmat_cdf_array(x[d], *params[:, d])
+            continue
+        assert status[d] == 0
+        assert np.array_equal(y[d], cdfdif_wrapper.dmat_cdf_array(x[d], *params[:, d]))
+        want = O.dmat_cdf_array(x[d], *params[:, d])
+        band = cdf_noise_band(O, x[d], params[:7, d], params[7, d], params[8, d])
+        assert (np.abs(y[d] - want) <= 1e-10 * np.abs(want) + 4 * band + 1e-14).all(), d
+
+
+@pytest.mark.gpu
+def test_quantile_objectives_match_the_stochastic_class(gpu):
+    """chi-square / G-square for many parameter sets in one launch == the per-node methods of the wfpt
+    stochastic class (hddm/likelihoods.py:198-239), which make one cdfdif call each."""
+    from hddm_b200 import likelihoods as L, posterior, wfpt
+    rng = np.random.default_rng(19)
+    cls = L.generate_wfpt_stochastic_class()
+    D = 7
+    par7 = draw_params(rng, D)
+    emp, freq, ns, chi, gsq = [], [], [], [], []
+    for d in range(D):
+        data = wfpt.gen_rts_from_cdf(*par7[:, d], 300, -5.0, 5.0, 1e-3, f=rng.random(300), u_delay=rng.random(300))
+        other = par7[:, (d + 1) % D]   # evaluate the objective at a different parameter set
+        node = cls(value=data, **dict(zip(("v", "sv", "a", "z", "sz", "t", "st"), other)), p_outlier=0.05)
+        node.compute_quantiles_stats()
+        emp.append(node._emp_rt); freq.append(node._freq_obs); ns.append(node._n_samples)
+        chi.append(node.chisquare()); gsq.append(node.gsquare())
+    params = np.concatenate([np.roll(par7, -1, axis=1), np.full((1, D), 0.05), np.full((1, D), 0.1)])
+    c, g = posterior.quantile_objectives(np.stack(emp), np.stack(freq), np.array(ns), params)
+    np.testing.assert_array_equal(c, np.array(chi))
+    np.testing.assert_array_equal(g, np.array(gsq))
