@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
 LIB = os.path.join(HERE, "libhddm_b200.so")
-SOURCES = ["abi.cu", "abi_rl.cu", "abi_ppc.cu", "rl_kernels.cu", "ppc_kernels.cu", "wfpt_kernels.cu", "cdfdif_kernels.cu", "gen_kernels.cu", "series_table.cu", "sort_kernels.cu"]
+SOURCES = ["abi.cu", "abi_rl.cu", "abi_ppc.cu", "rl_kernels.cu", "ppc_kernels.cu", "sim_kernels.cu", "wfpt_kernels.cu", "cdfdif_kernels.cu", "gen_kernels.cu", "series_table.cu", "sort_kernels.cu"]
 HEADERS = ["kernels.cuh", "abi_runtime.cuh", "wfpt_device.cuh", "wfpt_fast.cuh", "wfpt_grid.cuh", os.path.join(ROOT, "include", "hddm_b200.h")]
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

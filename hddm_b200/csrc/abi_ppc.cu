@@ -194,3 +194,44 @@ int hddm_dmat_cdf_batch(const double* x, int64_t n, const double* params, int64_
 }
 
 }  // extern "C"
+
+extern "C" int hddm_simulate_drift_batch(const double* params, int64_t D, int64_t samples, double dt,
+                                         double intra_sv, unsigned long long seed, const double* u_init,
+                                         const double* u_steps, int64_t max_steps, double* rts)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (D < 0 || samples < 0 || max_steps < 1 || !(dt > 0) || !(intra_sv > 0) ||
+        (D > 0 && samples > 0 && (!params || !rts)) || ((u_init == nullptr) != (u_steps == nullptr)))
+        return fail(HDDM_ERR_ARG, "simulate_drift_batch: bad buffer, size, dt or intra_sv");
+    TRY(ensure_ready());
+    const int64_t n = D * samples;
+    if (n == 0) return HDDM_OK;
+    Layout L;
+    const size_t off_p = L.reserve((size_t)D * 7 * sizeof(double));
+    const size_t off_r = L.reserve((size_t)n * sizeof(double));
+    const size_t off_i = u_init ? L.reserve((size_t)n * 3 * sizeof(double)) : 0;
+    const size_t off_u = u_steps ? L.reserve((size_t)n * max_steps * sizeof(double)) : 0;
+    TRY(ensure_arena(L.total));
+    cudaStream_t s = g_rt.stream;
+    CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_p), params, (size_t)D * 7 * sizeof(double), cudaMemcpyHostToDevice, s));
+    if (u_init) {
+        CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_i), u_init, (size_t)n * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+        CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_u), u_steps, (size_t)n * max_steps * sizeof(double), cudaMemcpyHostToDevice, s));
+    }
+    SimArgs a;
+    a.params = L.at<double>(off_p);
+    a.n_draws = D;
+    a.samples = samples;
+    a.max_steps = max_steps;
+    a.draw0 = 0;
+    a.dt = dt;
+    a.intra_sv = intra_sv;
+    a.seed = seed;
+    a.u_init = u_init ? L.at<double>(off_i) : nullptr;
+    a.u_steps = u_steps ? L.at<double>(off_u) : nullptr;
+    a.rts = L.at<double>(off_r);
+    CUDA_TRY(launch_simulate_drift(a, s));
+    CUDA_TRY(cudaMemcpyAsync(rts, a.rts, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return HDDM_OK;
+}

@@ -163,6 +163,22 @@ struct RlChoiceArgs {
 };
 cudaError_t launch_rl_choice(const RlChoiceArgs& a, cudaStream_t stream);
 
+// Random-walk simulator (sim_kernels.cu; hddm/generate.py:208-319): rts[d][s] for n_draws parameter sets
+// (SoA [7][n_draws]: v, sv, a, z, sz, t, st) x `samples` trials each.  u_init / u_steps == nullptr: Philox
+// keyed by (seed, (draw0 + d) * samples + s).  Otherwise (parity mode) u_init is [n_draws*samples][3] =
+// delay uniform, start-point uniform, standard-normal drift deviate, and u_steps is
+// [n_draws*samples][max_steps] step uniforms.  A walk that has not crossed after max_steps gives NaN.
+struct SimArgs {
+    const double* params;
+    int64_t n_draws, samples, max_steps, draw0;
+    double dt, intra_sv;
+    unsigned long long seed;
+    const double* u_init;
+    const double* u_steps;
+    double* rts;
+};
+cudaError_t launch_simulate_drift(const SimArgs& a, cudaStream_t stream);
+
 double fp64_peak_probe(int iters, float* ms_out, cudaStream_t stream);
 
 // Trials ordered by |rt| (sort_kernels.cu): a one-time layout step so that the lanes of a warp take the

@@ -118,3 +118,37 @@ def quantile_objectives(emp_rt, freq_obs, n_samples, params):
         chisq[d] = stats.chisquare(freq_obs[d], prop * n_samples[d])[0]
         gsq[d] = 2 * np.sum(freq_obs[d] * np.log(prop))
     return chisq, gsq
+
+
+def simulate_drift_batch(params, samples=1000, dt=1e-4, intra_sv=1.0, seed=0, u_init=None, u_steps=None,
+                         max_steps=10000000):
+    """Random-walk simulator of hddm/generate.py:208-319 (_gen_rts_from_simulated_drift) for D parameter
+    sets x `samples` trials on the GPU: params float64 [7, D] -> signed RTs [D, samples].  Device Philox
+    uniforms keyed by `seed`, or -- parity mode -- the caller's u_init [D, samples, 3] (delay uniform,
+    start-point uniform, standard-normal drift deviate) and u_steps [D, samples, max_steps]."""
+    params = _params7(params)
+    D = params.shape[1]
+    rts = np.empty((D, samples), dtype=np.double)
+    ip = up = None
+    if u_init is not None or u_steps is not None:
+        u_init = np.ascontiguousarray(u_init, dtype=np.float64)
+        u_steps = np.ascontiguousarray(u_steps, dtype=np.float64)
+        if u_init.shape != (D, samples, 3) or u_steps.ndim != 3 or u_steps.shape[:2] != (D, samples):
+            raise ValueError("u_init must be [D, samples, 3] and u_steps [D, samples, max_steps]")
+        max_steps = u_steps.shape[2]
+        ip, up = dptr(u_init), dptr(u_steps)
+    check(lib().hddm_simulate_drift_batch(dptr(params), D, samples, dt, intra_sv, int(seed), ip, up, int(max_steps),
+                                          dptr(rts)))
+    return rts
+
+
+def gen_rts_from_simulated_drift(params, samples=1000, dt=1e-4, intra_sv=1., seed=None):
+    """hddm/generate.py:208 signature for one parameter dict (keys v, a, z, t and optionally sv, sz, st);
+    returns the RT vector (the reference also returns the drift paths, which only its plotting code uses)."""
+    if 'v_switch' in params:
+        raise NotImplementedError("the v_switch variant (hddm/generate.py:234-241) is not on the GPU path")
+    col = np.array([[params['v']], [params.get('sv', 0.)], [params['a']], [params.get('z', .5)],
+                    [params.get('sz', 0.)], [params['t']], [params.get('st', 0.)]], dtype=np.float64)
+    if seed is None:
+        seed = np.random.randint(0, 2 ** 31 - 1)
+    return simulate_drift_batch(col, 1 if samples is None else samples, dt, intra_sv, seed)[0]

@@ -168,6 +168,18 @@ int hddm_ppc_stats(const double *rts, int64_t D, int64_t samples, double *stats)
 int hddm_dmat_cdf_batch(const double *x, int64_t n, const double *params, int64_t D, double *y,
                         int32_t *status);
 
+/* Random-walk simulator, hddm/generate.py:208-319 (_gen_rts_from_simulated_drift; gen_rts(method='drift'),
+ * used by HDDMRegressor's random(), hddm/models/hddm_regression.py:62): D parameter sets (SoA float64
+ * [7][D]: v, sv, a, z, sz, t, st) x `samples` trials, one GPU thread per trial; rts is [D][samples] signed
+ * RTs.  dt = step length in seconds (reference default 1e-4), intra_sv = within-trial noise (1.0).
+ * u_init == NULL and u_steps == NULL: device Philox4x32-10 keyed by (seed, global trial index).
+ * Otherwise both must be given (parity mode): u_init [D*samples][3] = delay uniform, start-point uniform,
+ * standard-normal drift deviate; u_steps [D*samples][max_steps] = one uniform per step.  A walk that
+ * has not left [0, a] after max_steps steps yields NaN.  The v_switch variant (:234-241) is not covered. */
+int hddm_simulate_drift_batch(const double *params, int64_t D, int64_t samples, double dt, double intra_sv,
+                              unsigned long long seed, const double *u_init, const double *u_steps,
+                              int64_t max_steps, double *rts);
+
 /* ---- reinforcement-learning likelihoods (src/wfpt.pyx:79-241, 277-320) -------------------------- */
 
 /* wiener_like_rlddm, src/wfpt.pyx:79-155.  response (0 = lower, 1 = upper) and split_by (condition
