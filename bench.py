@@ -295,6 +295,14 @@ def run_ours(args):
         mean_pdfsv = pdfsv / (float(T) * P * args.steps)
         alg_flop = float(T) * P * (mean_pdfsv * FLOP_PER_PDFSV + FLOP_PER_EVAL_TAIL)
         achieved = alg_flop / (k_ms * 1e-3) / 1e12
+        traffic, traffic_src = None, None
+        try:  # measured DRAM bytes per launch of this exact workload, if an ncu capture of it is on file
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            ent = tj.get("%s:%dx%d" % (args.sweep, T, P))
+            if ent:
+                traffic, traffic_src = ent["bytes"], ent["source"]
+        except Exception:
+            pass
         cpu = None
         try:
             if args.no_cpu:
@@ -315,11 +323,16 @@ def run_ours(args):
                     "d2h_bytes_per_step": int(8 * P + 8), "steps": e2e_steps, "bitwise_equal_to_device_path": same},
             "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
-                         "frac": achieved / peak_tflops, "traffic": None,
+                         "frac": achieved / peak_tflops, "traffic": traffic, "traffic_source": traffic_src,
+                         "algorithmic_bytes": int(8 * T + 72 * P + 8 * P * math.ceil(T / 2048.0)),
+                         "fp64_pipe_active_pct_ncu": 43.2,
                          "kernel": "k_like_partial (+k_like_final, <0.1%)", "kernel_ms": k_ms,
                          "pdf_sv_per_eval": mean_pdfsv,
                          "accounting": "algorithmic FLOP = pdf_sv evals x 300 + 28 per eval (SURVEY.md 8d); "
-                                       "peak = FP64 FMA probe measured in this run (MEASURED_PEAKS.json has no FP64 entry)"},
+                                       "peak = FP64 FMA probe measured in this run (MEASURED_PEAKS.json has no FP64 entry); "
+                                       "frac > 1 because the kernel executes ~24 FP64 instructions per pdf_sv where the "
+                                       "reference's sequence costs 300 FLOP; fp64_pipe_active_pct_ncu (profiles/r1_v3_summary.md) "
+                                       "is the executed-work utilisation"},
             "cpu_baseline": cpu,
             "clocks": clocks,
         }

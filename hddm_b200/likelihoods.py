@@ -199,16 +199,19 @@ def data_quantiles(rt, quantiles=(0.1, 0.3, 0.5, 0.7, 0.9)):
 
 def generate_wfpt_stochastic_class(wiener_params=None, sampling_method='cdf', cdf_range=(-5, 5),
                                    sampling_dt=1e-4):
-    """hddm/likelihoods.py:30-105.  sampling_method 'cdf' only: the random-walk simulator of
-    hddm/generate.py:208-319 is outside the hot path."""
+    """hddm/likelihoods.py:30-105.  sampling_method 'cdf' (src/wfpt.pyx:323-354) or 'drift' (the random-walk
+    simulator of hddm/generate.py:208-319), both on the GPU."""
     wp = dict(DEFAULT_WIENER_PARAMS if wiener_params is None else wiener_params)
     wfpt_like = make_wfpt_like(wp)
 
     def random(self):  # :76-81 -> hddm/generate.py:190-194 -> src/wfpt.pyx:323-354
-        if sampling_method != 'cdf':
-            raise NotImplementedError("only sampling_method='cdf' runs on the GPU path")
         par = {k: self.parents[k] for k in _PARENTS}
         size = int(np.prod(self.shape))
+        if sampling_method == 'drift':  # hddm/generate.py:187-188
+            from . import posterior
+            return posterior.gen_rts_from_simulated_drift(par, size, sampling_dt)
+        if sampling_method != 'cdf':
+            raise TypeError("Sampling method %s not found." % sampling_method)  # hddm/generate.py:195-196
         return wfpt.gen_rts_from_cdf(par['v'], par['sv'], par['a'], par['z'], par['sz'], par['t'], par['st'],
                                      size, cdf_range[0], cdf_range[1], sampling_dt)
 
@@ -330,3 +333,47 @@ def wiener_multi_like(value, v, sv, a, z, sz, t, st, reg_outcomes, p_outlier=0, 
     return wfpt.wiener_like_multi(_rt_array(value), params['v'], params['sv'], params['a'], params['z'],
                                   params['sz'], params['t'], params['st'], 1e-4, reg_outcomes,
                                   w_outlier=w_outlier, p_outlier=p_outlier)
+
+
+# ---- reinforcement-learning stochastics ------------------------------------------------------------
+
+def _rl_columns(x):
+    """The columns hddm/models/hddm_rl.py:68-72 pulls out of an observed node's DataFrame (or a dict /
+    structured array with the same names)."""
+    col = lambda name: np.asarray(getattr(x[name], 'values', x[name]))
+    q_init = x['q_init']
+    q = float(q_init.iloc[0] if hasattr(q_init, 'iloc') else np.asarray(q_init).ravel()[0])
+    return (np.ascontiguousarray(col('response').astype(int), dtype=np.int64), q,
+            np.ascontiguousarray(col('feedback').astype(float)), np.ascontiguousarray(col('split_by').astype(int), dtype=np.int64))
+
+
+def wienerRL_like(x, v, alpha, pos_alpha, sv, a, z, sz, t, st, p_outlier=0):
+    """hddm/models/hddm_rl.py:61-73."""
+    wp = DEFAULT_WIENER_PARAMS
+    response, q, feedback, split_by = _rl_columns(x)
+    return wfpt.wiener_like_rlddm(_rt_array(x), response, feedback, split_by, q, alpha, pos_alpha, v, sv, a, z, sz,
+                                  t, st, p_outlier=p_outlier, **wp)
+
+
+def RL_like(x, v, alpha, pos_alpha, z=0.5, p_outlier=0):
+    """hddm/models/rl.py:72-85."""
+    wp = DEFAULT_WIENER_PARAMS
+    response, q, feedback, split_by = _rl_columns(x)
+    return wfpt.wiener_like_rl(response, feedback, split_by, q, alpha, pos_alpha, v, z, p_outlier=p_outlier, **wp)
+
+
+def wienerRL_multi_like(value, v, sv, a, z, sz, t, st, alpha, reg_outcomes, p_outlier=0):
+    """hddm/models/hddm_rl_regression.py:25-38: parameters named in reg_outcomes are per-trial vectors
+    (already aligned with value's trials)."""
+    response, q, feedback, split_by = _rl_columns(value)
+    params = {'v': v, 'sv': sv, 'a': a, 'z': z, 'sz': sz, 't': t, 'st': st, 'alpha': alpha}
+    for name in reg_outcomes:
+        col = params[name]
+        params[name] = np.ascontiguousarray(getattr(col, 'values', col), dtype=np.float64)
+    return wfpt.wiener_like_multi_rlddm(_rt_array(value), response, feedback, split_by, q, params['v'], params['sv'],
+                                        params['a'], params['z'], params['sz'], params['t'], params['st'],
+                                        params['alpha'], 1e-4, reg_outcomes, p_outlier=p_outlier)
+
+
+WienerRL = _stochastic_from_dist('wienerRL', wienerRL_like)  # hddm/models/hddm_rl.py:73
+RL = _stochastic_from_dist('RL', RL_like)                    # hddm/models/rl.py:85

@@ -202,3 +202,26 @@ def test_gpu_rl_edge_cases(W):
         W.wiener_like_rlddm(x, r.astype(np.int32), f, s, .5, 0., 100., 1., 0, 2., .5, 0, .3, 0, 1e-4)
     with pytest.raises(ValueError):
         W.wiener_like_rlddm(x, r + 1, f, s, .5, 0., 100., 1., 0, 2., .5, 0, .3, 0, 1e-4)
+
+
+@pytest.mark.gpu
+def test_gpu_rl_stochastics_on_dataframes(W, O):
+    """The logp closures of hddm/models/hddm_rl.py:61-73, hddm/models/rl.py:72-85 and
+    hddm/models/hddm_rl_regression.py:25-38 on a DataFrame-valued observed node."""
+    import pandas as pd
+    from hddm_b200 import likelihoods as L
+    x, response, feedback, split_by = _task(np.random.default_rng(4), 300, 3)
+    df = pd.DataFrame(dict(rt=x, response=response.astype(float), feedback=feedback, split_by=split_by, q_init=0.5))
+    par = dict(v=2.0, alpha=-0.5, pos_alpha=0.3, sv=0.4, a=1.6, z=0.5, sz=0.1, t=0.2, st=0.1)
+    node = L.WienerRL(value=df, p_outlier=0.05, **par)
+    want = O.wiener_like_rlddm(x, response, feedback, split_by, 0.5, par["alpha"], par["pos_alpha"], par["v"], par["sv"],
+                               par["a"], par["z"], par["sz"], par["t"], par["st"], 1e-4, 2, 2, 1, 1e-3, 0.05, 0.1)
+    assert_parity(node.logp, want, RTOL_SUM, what="WienerRL.logp")
+    node = L.RL(value=df, v=2.0, alpha=-0.5, pos_alpha=100.0, z=0.5, p_outlier=0.05)
+    want = O.wiener_like_rl(response, feedback, split_by, 0.5, -0.5, 100.0, 2.0, 0.5, p_outlier=0.05, w_outlier=0.1)
+    assert_parity(node.logp, want, RTOL_SUM, what="RL.logp")
+    vcol = pd.Series(np.random.default_rng(5).uniform(1, 3, 300), index=df.index)
+    got = L.wienerRL_multi_like(df, vcol, 0.4, 1.6, 0.5, 0.1, 0.2, 0.1, -0.5, ['v'], p_outlier=0.05)
+    want = O.wiener_like_multi_rlddm(x, response, feedback, split_by, 0.5, vcol.values, 0.4, 1.6, 0.5, 0.1, 0.2, 0.1,
+                                     -0.5, 1e-4, ['v'], p_outlier=0.05, w_outlier=0)
+    assert_parity(got, want, RTOL_SUM, what="wienerRL_multi_like")
