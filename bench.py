@@ -208,6 +208,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # keep stdout to the one JSON line: NCCL prints its version banner there at NCCL_DEBUG=VERSION
+        os.environ["NCCL_DEBUG"] = os.environ.get("HDDM_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=dev)
     _lib.check(_lib.lib().hddm_b200_init(local))
 
