@@ -498,10 +498,13 @@ __device__ __noinline__ double grid_fallback(double x, double v, const GridSet<K
 
 // adaptiveSimpsons_1D over z at decision time xt (src/integrate.pxi:114-141), already / ZT -- or pdf_sv at
 // the set's own start point when sz == 0.  xt is positive and inside the comfortable range.
-template <int KMAX>
+// DEFER: the first-pass flavour -- a node whose inner integration needs refinement sets *defer instead of
+// walking deeper (the caller re-evaluates the whole trial in its second pass), so that the node values never
+// have their address taken and stay in registers.
+template <int KMAX, bool DEFER = false>
 __device__ __forceinline__ double grid_inner(const GridSet<KMAX>& G, const GridTrial& c, double xt, int code,
                                              double q, const Numerics& nm, const SeriesTable* tab,
-                                             unsigned long long& extra)
+                                             unsigned long long& extra, bool* defer = nullptr)
 {
     if (G.sz != 0) {
         double f[5];
@@ -511,6 +514,10 @@ __device__ __forceinline__ double grid_inner(const GridSet<KMAX>& G, const GridT
         const double right = G.zw12 * ((f[2] + 4.0 * f[3]) + f[4]);
         const double fine = left + right;
         if (nm.n_sz <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err) return fma(fine - coarse, 1.0 / 15.0, fine);
+        if (DEFER) {
+            *defer = true;
+            return 0.0;
+        }
         return grid_refine_z<KMAX>(G, c, xt, code, q, f, coarse, nm.simps_err, nm.n_sz, extra);
     }
     double f[1];
@@ -563,10 +570,13 @@ __device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridT
 
 // full_pdf (src/pdf.pxi:104-146) for one trial of the CTA's set (v may differ per trial).  Returns through the v2 evaluator when the trial is outside the
 // comfortable range (normalised time outside [2^-9, 128], extreme drift, NaN).
-template <int KMAX>
+// DEFER (first pass of the likelihood kernel): trials that need anything beyond the first 5 x 5 level --
+// inner or outer refinement, or the out-of-range fallback -- set *need and return 0 without counting
+// evaluations; the kernel re-runs them, compacted, through full_pdf_grid_slow.
+template <int KMAX, bool DEFER = false>
 __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSet<KMAX>& G,
                                                 const Numerics& nm, const SeriesTable* tab,
-                                                unsigned long long& evals)
+                                                unsigned long long& evals, bool* need = nullptr)
 {
     const double ax = fabs(x);
     if (!G.support || (ax - G.t_onset) < 0) return 0.0;  // src/pdf.pxi:111-113
@@ -622,10 +632,11 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
                     }
                     const int code = uniform ? code_hi : grid_code(G, xt);
                     const double q = q0 * G.rho[j];
-                    if (ok && live) val = grid_inner<KMAX>(G, c, xt, code, q, nm, tab, extra);
+                    if (ok && live && !(DEFER && *need)) val = grid_inner<KMAX, DEFER>(G, c, xt, code, q, nm, tab, extra, need);
                 }
                 F[j] = val * G.inv_st;
             }
+            if (DEFER && *need) return 0.0;
             if (ok) {
                 const double coarse = G.tw6 * ((F[0] + 4.0 * F[2]) + F[4]);
                 const double left = G.tw12 * ((F[0] + 4.0 * F[1]) + F[2]);
@@ -633,7 +644,10 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
                 const double fine = left + right;
                 if (nm.n_st <= 0 || fabs(fine - coarse) <= 15.0 * nm.simps_err)
                     out = fma(fine - coarse, 1.0 / 15.0, fine);
-                else {
+                else if (DEFER) {
+                    *need = true;
+                    return 0.0;
+                } else {
                     bool bad = false, tiny2 = false;
                     out = grid_refine_t<KMAX>(G, c, ax, nm, tab, F, coarse, extra, xz, &bad, &tiny2);
                     ok = !bad;
@@ -643,9 +657,23 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
             }
         }
     }
-    if (!ok) return grid_fallback<KMAX>(x, v, G, nm, tab, evals);
+    if (!ok) {
+        if (DEFER) {
+            *need = true;
+            return 0.0;
+        }
+        return grid_fallback<KMAX>(x, v, G, nm, tab, evals);
+    }
     evals += n_eval + extra;
     return out;
+}
+
+// Second pass: the complete evaluator, one out-of-line copy.
+template <int KMAX>
+__device__ __noinline__ double full_pdf_grid_slow(double x, double v, const GridSet<KMAX>& G, const Numerics& nm,
+                                                  const SeriesTable* tab, unsigned long long& evals)
+{
+    return full_pdf_grid<KMAX, false>(x, v, G, nm, tab, evals);
 }
 
 }  // namespace hddm

@@ -79,8 +79,11 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     else if (KMAX > 0)
         build_wtables<KT>(wt, par[3], par[4]);
 
-    auto density = [&](double x, unsigned long long& ev) {
-        if (GRID) return full_pdf_grid<KT>(x, par[0], gs, a.nm, &a.tab, ev);
+    // pass 1 (GRID): need = the trial is deferred to pass 2; otherwise need stays false
+    auto density = [&](double x, unsigned long long& ev, bool first_pass, bool* need) {
+        if (GRID)
+            return first_pass ? full_pdf_grid<KT, true>(x, par[0], gs, a.nm, &a.tab, ev, need)
+                              : full_pdf_grid_slow<KT>(x, par[0], gs, a.nm, &a.tab, ev);
         if (KMAX > 0)
             return full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(x, par[0], par[1], par[2], par[3], par[4], par[5],
                                                         par[6], a.nm, &a.tab, wt, ev);
@@ -100,34 +103,59 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
             acc += log(d);
         }
     };
-    static_assert(kTrialsPerBlock / kLikeThreads <= 512, "mantissa product must stay finite");
+    static_assert(kTrialsPerBlock / kLikeThreads <= 256, "mantissa product must stay finite (two passes)");
     unsigned long long evals = 0;
     bool hit_zero = false;
-    for (int64_t i = begin + threadIdx.x; i < end; i += kLikeThreads) {
+    // One trial: load, evaluate, mix, accumulate.  Returns true when the trial was deferred.
+    auto score = [&](int64_t i, bool first_pass) {
         const double x = __ldg(a.x + i);
         if (per_trial) {
 #pragma unroll
             for (int k = 0; k < (GRID ? 1 : 7); ++k)  // GRID: only the drift can vary per trial
                 if (a.trial_stride[k] != 0) par[k] = load_par(a, k, p, i);
         }
+        bool need = false;
         double d;
         if (multi) {
             if (a.mode == kModeMultiRL || fabs(x) != 999.) {  // src/wfpt.pyx:261-266
-                d = density(x, evals);
+                d = density(x, evals, first_pass, &need);
                 d = d * (1 - p_out) + w_out * p_out;
             } else if (x == 999.) {  // :267-268
                 d = prob_ub(par[0], GRID ? gs.raw[2] : par[2], GRID ? gs.raw[3] : par[3]);
             } else {  // :269-270
                 d = 1 - prob_ub(par[0], GRID ? gs.raw[2] : par[2], GRID ? gs.raw[3] : par[3]);
             }
-            add_log(d);
+            if (!need) add_log(d);
         } else {
-            if (a.cont && a.cont[i] != 0) continue;  // src/wfpt.pyx:374; :134 (first trial of a condition)
-            d = density(x, evals);
-            d = d * (1 - p_out) + w_out * p_out;  // src/wfpt.pyx:70 (contaminant: p_out = 0)
-            hit_zero |= (d == 0);                 // :71-72, :377-379
-            add_log(d);
+            if (a.cont && a.cont[i] != 0) return false;  // src/wfpt.pyx:374; :134 (first trial of a condition)
+            d = density(x, evals, first_pass, &need);
+            if (!need) {
+                d = d * (1 - p_out) + w_out * p_out;  // src/wfpt.pyx:70 (contaminant: p_out = 0)
+                hit_zero |= (d == 0);                 // :71-72, :377-379
+                add_log(d);
+            }
         }
+        return need;
+    };
+    if (GRID) {
+        // Pass 1 evaluates the first 5 x 5 level, which settles almost every trial; the few that need more are
+        // queued per warp (ballot order: deterministic) and pass 2 runs them through the complete evaluator with
+        // full warps.  Keeps the slow paths' code, registers and local-memory arrays out of the hot loop.
+        __shared__ unsigned short queue[kLikeThreads / 32][kTrialsPerBlock / (kLikeThreads / 32)];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const int rounds = (int)((end - begin + kLikeThreads - 1) / kLikeThreads);
+        int queued = 0;  // warp-uniform
+        for (int r = 0; r < rounds; ++r) {
+            const int off = r * kLikeThreads + threadIdx.x;
+            const bool need = (begin + off < end) ? score(begin + off, true) : false;
+            const unsigned int votes = __ballot_sync(0xffffffffu, need);
+            if (need) queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] = (unsigned short)off;
+            queued += __popc(votes);
+        }
+        __syncwarp();
+        for (int k = lane; k < queued; k += 32) score(begin + queue[warp][k], false);
+    } else {
+        for (int64_t i = begin + threadIdx.x; i < end; i += kLikeThreads) score(i, true);
     }
     acc += fma((double)expo, 0.693147180559945309417, log(mant));
 
