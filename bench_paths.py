@@ -108,6 +108,24 @@ def main():
              h2d_bytes=int(v_trial.nbytes + x.nbytes + params.nbytes),
              algorithmic_GBps=16.0 * T * P / dt / 1e9)
 
+    if on("regression_design"):
+        T, P, K = 100000, 512, 3
+        x = rts(rng, T)
+        params = np.concatenate([draw(rng, P), np.full((1, P), 0.05), np.full((1, P), 0.1)])
+        design = np.concatenate([np.ones((1, T)), rng.standard_normal((K - 1, T))])
+        coef = np.concatenate([params[0][None, :], rng.uniform(-0.5, 0.5, (K - 1, P))])
+        nm = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
+        dt, lp = best_of(lambda: wfpt.wiener_like_regression_batch(x, design, coef, params, **nm), args.reps)
+        vs = np.ascontiguousarray((design[:, :5000].T @ coef[:, :4]).T)
+        t0 = time.perf_counter()
+        for p in range(4):
+            W.wiener_like_multi(x[:5000], vs[p], *params[1:7, p], 1e-4, ['v'], 2, 2, 1, 1e-3, 0.05, 0.1)
+        cdt = time.perf_counter() - t0
+        emit("regression sweep, drift built on the device from a [%d, n] design: %d trials x %d coefficient sets"
+             % (K, T, P), T * P / dt, "evals/s", 5000 * 4 / cdt, kind, "first 5000 trials x first 4 sets",
+             ms=dt * 1e3, h2d_bytes=int(design.nbytes + x.nbytes + params.nbytes + coef.nbytes),
+             algorithmic_GBps=16.0 * T * P / dt / 1e9)
+
     if on("ppc"):
         D, S = 10000, 200
         params = draw(rng, D)

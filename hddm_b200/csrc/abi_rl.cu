@@ -244,6 +244,61 @@ int hddm_wiener_like_rl_batch(const int64_t* response, const double* feedback, c
     return rl_choice_impl(response, feedback, split_by, n, params, P, logp);
 }
 
+int hddm_wiener_like_regression_batch(const double* x, int64_t n, const double* design, int64_t K,
+                                      const double* coef, const double* params, int64_t P, double err, int n_st,
+                                      int n_sz, int use_adaptive, double simps_err, double* logp,
+                                      unsigned long long* evals)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (n < 0 || K < 1 || P < 0 || (n > 0 && (!x || !design)) || (P > 0 && (!coef || !params || !logp)))
+        return fail(HDDM_ERR_ARG, "regression_batch: bad buffer or size");
+    if (P > 65535) return fail(HDDM_ERR_ARG, "regression_batch: more than 65535 coefficient sets per call");
+    const Numerics nm = make_numerics(err, n_st, n_sz, use_adaptive, simps_err);
+    TRY(check_numerics(n_st, n_sz, use_adaptive));
+    TRY(ensure_ready());
+    if (P == 0) return HDDM_OK;
+    const int64_t chunks = chunks_for(n);
+    if (chunks > 65535) return fail(HDDM_ERR_ARG, "more than 65535*2048 trials per parameter set");
+    if ((double)P * (double)n * 8.0 > 64e9) return fail(HDDM_ERR_ARG, "regression_batch: P x n drift table above 64 GB");
+    Stager S;
+    const int s_x = S.add(x, (size_t)n * sizeof(double));
+    const int s_design = S.add(design, (size_t)K * n * sizeof(double));
+    const int s_coef = S.add(coef, (size_t)K * P * sizeof(double));
+    const int s_par = S.add(params, (size_t)P * kNumPar * sizeof(double));
+    const int s_drift = S.scratch((size_t)P * (size_t)(n > 0 ? n : 1) * sizeof(double));
+    const int s_partial = S.scratch((size_t)P * chunks * sizeof(double));
+    const int s_logp = S.scratch((size_t)P * sizeof(double));
+    const int s_evals = S.scratch(sizeof(unsigned long long));
+    cudaStream_t s = g_rt.stream;
+    TRY(S.commit(s));
+    CUDA_TRY(cudaMemsetAsync(S.dev<char>(s_evals), 0, sizeof(unsigned long long), s));
+    CUDA_TRY(launch_design_drift(S.dev<double>(s_design), S.dev<double>(s_coef), n, K, P, S.dev<double>(s_drift), s));
+    const double* d_par = S.dev<double>(s_par);
+    LikeArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = S.dev<double>(s_x);
+    for (int k = 0; k < kNumPar; ++k) {
+        a.par[k] = d_par + k * P;
+        a.set_stride[k] = 1;
+    }
+    a.par[0] = S.dev<double>(s_drift);
+    a.set_stride[0] = n;
+    a.trial_stride[0] = 1;
+    a.n = n;
+    a.n_sets = P;
+    a.chunks = (int)chunks;
+    a.mode = kModeMulti;  // wiener_like_multi semantics per set (src/wfpt.pyx:244-274)
+    a.nm = nm;
+    a.partial = S.dev<double>(s_partial);
+    a.logp = S.dev<double>(s_logp);
+    a.evals = S.dev<unsigned long long>(s_evals);
+    CUDA_TRY(launch_like(a, s));
+    CUDA_TRY(cudaMemcpyAsync(logp, a.logp, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (evals) CUDA_TRY(cudaMemcpyAsync(evals, a.evals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return HDDM_OK;
+}
+
 int hddm_wiener_like_multi_rlddm(const double* x, const int64_t* response, const double* feedback,
                                  const int64_t* split_by, int64_t n, double q, const double* const par[8],
                                  const int64_t stride[8], double err, int n_st, int n_sz, int use_adaptive,

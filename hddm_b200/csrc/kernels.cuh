@@ -150,6 +150,12 @@ struct RlScanArgs {
 };
 cudaError_t launch_rl_scan(const RlScanArgs& a, cudaStream_t stream);
 
+// Regression drift built on the device: drift[p][i] = sum_k design[k][i] * coef[k][p] (k ascending, fused
+// multiply-adds), the per-trial `v` column of HDDMRegressor (hddm/models/hddm_regression.py:26-36) for P
+// coefficient proposals at once, so that only K x (n + P) numbers cross the host-device link instead of P x n.
+cudaError_t launch_design_drift(const double* design, const double* coef, int64_t n, int64_t K, int64_t P,
+                                double* drift, cudaStream_t stream);
+
 // wiener_like_rl (src/wfpt.pyx:158-241): choice-only likelihood; the same scan, scoring each trial but
 // the first of a run with the closed-form P(response), summed per set in run order.
 struct RlChoiceArgs {

@@ -73,6 +73,30 @@ cudaError_t launch_rl_scan(const RlScanArgs& a, cudaStream_t stream)
     return cudaGetLastError();
 }
 
+// drift[p][i] = sum_k design[k][i] * coef[k][p]; grid (n / 256, P), coalesced in i.
+__global__ void __launch_bounds__(256) k_design_drift(const double* __restrict__ design,
+                                                      const double* __restrict__ coef, int64_t n, int64_t K,
+                                                      int64_t P, double* __restrict__ drift)
+{
+    const int64_t p = blockIdx.y;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        double acc = 0.0;
+        for (int64_t k = 0; k < K; ++k) acc = fma(__ldg(design + k * n + i), __ldg(coef + k * P + p), acc);
+        drift[p * n + i] = acc;
+    }
+}
+
+cudaError_t launch_design_drift(const double* design, const double* coef, int64_t n, int64_t K, int64_t P,
+                                double* drift, cudaStream_t stream)
+{
+    if (n <= 0 || P <= 0) return cudaSuccess;
+    if (P > 65535) return cudaErrorInvalidValue;
+    int64_t bx = (n + 255) / 256;
+    if (bx > 1024) bx = 1024;
+    k_design_drift<<<dim3((unsigned)bx, (unsigned)P), 256, 0, stream>>>(design, coef, n, K, P, drift);
+    return cudaGetLastError();
+}
+
 // wiener_like_rl: per (set, run) sum of log P(response), -inf when a mixed probability is exactly 0.
 __global__ void __launch_bounds__(128) k_rl_choice(const RlChoiceArgs c)
 {

@@ -17,7 +17,7 @@ __all__ = ["full_pdf", "pdf_array", "wiener_like", "wiener_like_multi", "wiener_
            "wiener_like_rlddm", "wiener_like_rl", "wiener_like_multi_rlddm", "wiener_like_rlddm_batch",
            "wiener_like_rl_batch",
            "gen_cdf_using_pdf", "gen_rts_from_cdf", "split_cdf", "wiener_like_batch",
-           "wiener_like_multi_batch", "wiener_like_nodes", "Trials"]
+           "wiener_like_multi_batch", "wiener_like_regression_batch", "wiener_like_nodes", "Trials"]
 
 _PARAM_NAMES = ("v", "sv", "a", "z", "sz", "t", "st")
 
@@ -296,6 +296,27 @@ def wiener_like_multi_batch(x, v_trial, params, err=1e-4, n_st=10, n_sz=10, use_
     check(lib().hddm_wiener_like_multi_batch(dptr(x), x.shape[0], dptr(v_trial), dptr(params), P, err, n_st,
                                              n_sz, int(bool(use_adaptive)), simps_err, dptr(out),
                                              C.byref(evals)))
+    return (out, evals.value) if return_evals else out
+
+
+def wiener_like_regression_batch(x, design, coef, params, err=1e-4, n_st=10, n_sz=10, use_adaptive=1,
+                                 simps_err=1e-3, return_evals=False):
+    """Regression layout with the drift built on the GPU: design float64 [K, n] (rows = columns of the design
+    matrix of `v ~ ...`, intercept included), coef float64 [K, P] (columns = coefficient proposals), params
+    [9, P] (row 0 ignored).  Equivalent to wiener_like_multi_batch(x, (design.T @ coef).T, params) without
+    uploading the [P, n] drift table."""
+    x = as_rt_buffer(x)
+    params = _pack_params(params)
+    P = params.shape[1]
+    design = np.ascontiguousarray(design, dtype=np.float64)
+    coef = np.ascontiguousarray(coef, dtype=np.float64)
+    if design.ndim != 2 or design.shape[1] != x.shape[0] or coef.shape != (design.shape[0], P):
+        raise ValueError("design must be [K, n] and coef [K, P]")
+    out = np.empty(P, dtype=np.double)
+    evals = C.c_ulonglong(0)
+    check(lib().hddm_wiener_like_regression_batch(dptr(x), x.shape[0], dptr(design), design.shape[0], dptr(coef),
+                                                  dptr(params), P, err, n_st, n_sz, int(bool(use_adaptive)),
+                                                  simps_err, dptr(out), C.byref(evals)))
     return (out, evals.value) if return_evals else out
 
 

@@ -216,6 +216,16 @@ int hddm_wiener_like_multi_rlddm(const double *x, const int64_t *response, const
                                  const int64_t stride[8], double err, int n_st, int n_sz, int use_adaptive,
                                  double simps_err, double p_outlier, double w_outlier, double *logp);
 
+/* NEW: regression layout with the drift built on the device.  design is float64 [K][n] (one row per
+ * column of the patsy design matrix of `v ~ ...`, intercept included), coef float64 [K][P] (one column per
+ * coefficient proposal): the drift of trial i under proposal p is sum_k design[k][i] * coef[k][p].  The other
+ * eight parameters per proposal in params [9][P] (row 0 ignored).  wiener_like_multi semantics per set
+ * (hddm/models/hddm_regression.py:26-36 -> src/wfpt.pyx:244-274).  Only K (n + P) numbers are uploaded. */
+int hddm_wiener_like_regression_batch(const double *x, int64_t n, const double *design, int64_t K,
+                                      const double *coef, const double *params, int64_t P, double err,
+                                      int n_st, int n_sz, int use_adaptive, double simps_err, double *logp,
+                                      unsigned long long *evals);
+
 /* ---- device-resident trials (one upload per observed node, reused every MCMC step) --------- */
 typedef struct hddm_trials hddm_trials; /* opaque */
 int hddm_trials_upload(const double *x, int64_t n, hddm_trials **out);

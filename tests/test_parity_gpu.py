@@ -224,6 +224,31 @@ def test_multi_batch_vs_oracle(W, O):
     assert_parity(got, want, RTOL_SUM, what="multi batch")
 
 
+def test_regression_batch_builds_the_drift_on_the_device(W, O):
+    """v ~ 1 + covariates (hddm/models/hddm_regression.py:26-36): design [K, n] and coefficient proposals
+    [K, P] go up, the [P, n] drift table is built on the GPU; same values as the oracle's wiener_like_multi on
+    the numpy product, and as the uploaded-table entry point."""
+    rng = np.random.default_rng(9450)
+    T, P, K = 3000, 11, 3
+    x = draw_rts(rng, T, 0.6)
+    x[::211] = 999.0
+    x[3::307] = -999.0
+    par = draw_params(rng, P)
+    params = np.concatenate([par, np.full((1, P), 0.05), np.full((1, P), 0.1)])
+    design = np.concatenate([np.ones((1, T)), rng.standard_normal((K - 1, T))])
+    coef = np.concatenate([rng.uniform(-2, 2, (1, P)), rng.uniform(-0.8, 0.8, (K - 1, P))])
+    got, evals = W.wiener_like_regression_batch(x, design, coef, params, n_st=2, n_sz=2, return_evals=True)
+    v_trial = np.ascontiguousarray((design.T @ coef).T)
+    O.pdfsv_calls(reset=True)
+    want = np.array([O.wiener_like_multi(x, v_trial[p], *par[1:, p], 1e-4, multi=["v"], n_st=2, n_sz=2,
+                                         p_outlier=0.05, w_outlier=0.1) for p in range(P)])
+    want_evals = O.pdfsv_calls(reset=True)
+    assert_parity(got, want, RTOL_SUM, what="regression batch")
+    assert evals == want_evals
+    table = W.wiener_like_multi_batch(x, v_trial, params, n_st=2, n_sz=2)
+    assert_parity(got, table, 1e-12, what="regression batch vs uploaded drift table")
+
+
 @pytest.mark.parametrize("multi", [("v", "t"), ("a", "sv", "st"), ("z",), ("sz", "v"), ("v", "sv", "a", "z", "sz", "t", "st")])
 def test_multi_per_trial_parameters(W, O, multi):
     """wiener_like_multi with any subset of parameters per trial (src/wfpt.pyx:256-260); z or sz per
