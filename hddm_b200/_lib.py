@@ -47,7 +47,7 @@ SIGNATURES = {
     "hddm_wiener_like_batch": (_i, [c_dp, _l, c_lp, c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_wiener_like_multi_batch": (_i, [c_dp, _l, c_dp, c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_gen_rts_from_cdf_batch": (_i, [c_dp, _l, c_dp, _l, c_dp, c_dp, _l, c_dp, c_dp]),
-    "hddm_gen_rts_from_cdf_batch_seeded": (_i, [c_dp, _l, c_dp, _l, C.c_ulonglong, _l, c_dp, c_dp]),
+    "hddm_gen_rts_from_cdf_batch_seeded": (_i, [c_dp, _l, c_dp, _l, C.c_ulonglong, _l, _l, c_dp, c_dp]),
     "hddm_ppc_stats": (_i, [c_dp, _l, _l, c_dp]),
     "hddm_dmat_cdf_batch": (_i, [c_dp, _l, c_dp, _l, c_dp, c_ip]),
     "hddm_wiener_like_regression_batch": (_i, [c_dp, _l, c_dp, _l, c_dp, c_dp, _l] + _NUM + [c_dp, c_up]),

@@ -108,6 +108,23 @@ def gather_loglik(local_logp, n_sets, group=None):
     return torch.cat([gathered[r * width:r * width + sizes[r]] for r in range(world)])
 
 
+def gather_rows(local, n_rows, group=None):
+    """All-gather row blocks (contiguous shard_bounds layout over the first axis) of a 2-D tensor into
+    the full [n_rows, cols] table: per-draw statistics, quantile probabilities."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return local
+    world = dist.get_world_size(group)
+    sizes = shard_sizes(n_rows, world)
+    width, cols = max(sizes), int(local.shape[1])
+    padded = local.new_zeros((width, cols))
+    padded[:local.shape[0]] = local
+    gathered = local.new_empty((world * width, cols))
+    dist.all_gather_into_tensor(gathered, padded, group=group)
+    return torch.cat([gathered[r * width:r * width + sizes[r]] for r in range(world)])
+
+
 def wiener_like_batch_sharded(x, params, evaluate=None, group=None, **numerics):
     """Evaluate P parameter sets (params float64 [9, P], host) against x with the sets sharded over
     the ranks of `group`; every rank returns the full float64[P] vector.

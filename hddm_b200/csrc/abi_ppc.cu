@@ -14,8 +14,8 @@ constexpr size_t kTableSlabBytes = (size_t)4 << 30;  // density tables of one sl
 
 // Draws [d0, d0 + Dn) of the batch: tables -> cumulative tables -> RTs (-> statistics).
 int ppc_slab(const double* d_grid, int64_t m, const double* h_params, int64_t D, int64_t d0, int64_t Dn,
-             const double* h_f, const double* h_u, unsigned long long seed, int64_t S, double* h_rts,
-             double* h_stats, cudaStream_t s)
+             const double* h_f, const double* h_u, unsigned long long seed, int64_t first_draw, int64_t S,
+             double* h_rts, double* h_stats, cudaStream_t s)
 {
     // per-slab parameter table for the density kernel: t = st = 0, no outlier mix (src/wfpt.pyx:335)
     std::vector<double> par((size_t)kNumPar * Dn, 0.0), tt((size_t)2 * Dn);
@@ -59,7 +59,7 @@ int ppc_slab(const double* d_grid, int64_t m, const double* h_params, int64_t D,
     CUDA_TRY(launch_pdf_array(pa, s));
     CUDA_TRY(launch_cumsum_normalise_batch(at(off_tab), m, Dn, s));
     CUDA_TRY(launch_sample_rts_batch(pa.x, at(off_tab), m, h_f ? at(off_f) : nullptr, h_u ? at(off_u) : nullptr,
-                                     S, Dn, at(off_tt), at(off_tt) + Dn, seed, d0, at(off_r), s));
+                                     S, Dn, at(off_tt), at(off_tt) + Dn, seed, first_draw + d0, at(off_r), s));
     if (h_stats) {
         CUDA_TRY(launch_ppc_stats(at(off_r), S, Dn, at(off_st), s));
         CUDA_TRY(cudaMemcpyAsync(h_stats + (size_t)d0 * kPpcStats, at(off_st),
@@ -73,7 +73,7 @@ int ppc_slab(const double* d_grid, int64_t m, const double* h_params, int64_t D,
 }
 
 int ppc_impl(const double* xgrid, int64_t m, const double* params, int64_t D, const double* f, const double* u,
-             unsigned long long seed, int64_t S, double* rts, double* stats)
+             unsigned long long seed, int64_t first_draw, int64_t S, double* rts, double* stats)
 {
     if (m <= 0 || D < 0 || S < 0 || !xgrid || (D > 0 && !params) || (D > 0 && S > 0 && !rts && !stats))
         return fail(HDDM_ERR_ARG, "gen_rts_from_cdf_batch: bad buffer or size");
@@ -96,7 +96,8 @@ int ppc_impl(const double* xgrid, int64_t m, const double* params, int64_t D, co
     CUDA_TRY(cudaMemcpyAsync(g_rt.arena, xgrid, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, s));
     for (int64_t d0 = 0; d0 < D; d0 += slab) {
         const int64_t Dn = D - d0 < slab ? D - d0 : slab;
-        TRY(ppc_slab(reinterpret_cast<const double*>(g_rt.arena), m, params, D, d0, Dn, f, u, seed, S, rts, stats, s));
+        TRY(ppc_slab(reinterpret_cast<const double*>(g_rt.arena), m, params, D, d0, Dn, f, u, seed, first_draw, S, rts,
+                     stats, s));
     }
     return HDDM_OK;
 }
@@ -110,14 +111,16 @@ int hddm_gen_rts_from_cdf_batch(const double* xgrid, int64_t m, const double* pa
 {
     std::lock_guard<std::mutex> lock(g_rt.mu);
     if (D > 0 && samples > 0 && !f) return fail(HDDM_ERR_ARG, "gen_rts_from_cdf_batch: null uniforms");
-    return ppc_impl(xgrid, m, params, D, f, u_delay, 0ull, samples, rts, stats);
+    return ppc_impl(xgrid, m, params, D, f, u_delay, 0ull, 0, samples, rts, stats);
 }
 
 int hddm_gen_rts_from_cdf_batch_seeded(const double* xgrid, int64_t m, const double* params, int64_t D,
-                                       unsigned long long seed, int64_t samples, double* rts, double* stats)
+                                       unsigned long long seed, int64_t first_draw, int64_t samples, double* rts,
+                                       double* stats)
 {
     std::lock_guard<std::mutex> lock(g_rt.mu);
-    return ppc_impl(xgrid, m, params, D, nullptr, nullptr, seed, samples, rts, stats);
+    if (first_draw < 0) return fail(HDDM_ERR_ARG, "gen_rts_from_cdf_batch_seeded: negative first_draw");
+    return ppc_impl(xgrid, m, params, D, nullptr, nullptr, seed, first_draw, samples, rts, stats);
 }
 
 int hddm_ppc_stats(const double* rts, int64_t D, int64_t samples, double* stats)

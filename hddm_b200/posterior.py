@@ -30,12 +30,13 @@ def _params7(params):
 
 
 def gen_rts_from_cdf_batch(params, samples=1000, cdf_lb=-6, cdf_ub=6, dt=1e-2, f=None, u_delay=None, seed=None,
-                           return_rts=True, return_stats=False):
+                           return_rts=True, return_stats=False, first_draw=0):
     """gen_rts_from_cdf (src/wfpt.pyx:323-354) for D posterior draws in one pass.
 
     params: float64 [7, D] (rows v, sv, a, z, sz, t, st).  Uniforms: `f` / `u_delay` float64 [D, samples]
     (the reference's draw order per call is f, then the delays when st != 0), or `seed` for device-side
-    Philox uniforms, or neither -- then numpy's global RNG is used draw by draw exactly as D reference
+    Philox uniforms (keyed by the global draw index first_draw + column, so any split of the draws over
+    calls or GPUs gives the same data sets), or neither -- then numpy's global RNG is used draw by draw exactly as D reference
     calls would.  Returns rts [D, samples] and/or stats [D, 15] (columns STAT_NAMES)."""
     params = _params7(params)
     D = params.shape[1]
@@ -45,7 +46,8 @@ def gen_rts_from_cdf_batch(params, samples=1000, cdf_lb=-6, cdf_ub=6, dt=1e-2, f
     rp = dptr(rts) if rts is not None else None
     sp = dptr(stats) if stats is not None else None
     if seed is not None:
-        check(lib().hddm_gen_rts_from_cdf_batch_seeded(dptr(x), x.shape[0], dptr(params), D, int(seed), samples, rp, sp))
+        check(lib().hddm_gen_rts_from_cdf_batch_seeded(dptr(x), x.shape[0], dptr(params), D, int(seed), int(first_draw), samples,
+                                                       rp, sp))
     else:
         if f is None:
             f = np.empty((D, samples))
@@ -152,3 +154,33 @@ def gen_rts_from_simulated_drift(params, samples=1000, dt=1e-4, intra_sv=1., see
     if seed is None:
         seed = np.random.randint(0, 2 ** 31 - 1)
     return simulate_drift_batch(col, 1 if samples is None else samples, dt, intra_sv, seed)[0]
+
+
+def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=0, evaluate=None, group=None):
+    """Posterior predictive statistics for D draws with the draws sharded over the ranks of `group` (one
+    process per GPU, contiguous blocks as hddm_b200.batch.shard_bounds); every rank returns the full
+    float64 [D, 15] table.  The only collective is one all_gather of the per-draw statistics (120 bytes per
+    draw); the simulated data sets never leave their GPU.  Device uniforms are keyed by the global draw
+    index, so the table does not depend on the world size.
+
+    `evaluate(params_block, first_draw) -> float64 [block, 15]` defaults to the CUDA path; tests pass a
+    stand-in to exercise the partition / gather logic over gloo on CPU."""
+    import torch
+    import torch.distributed as dist
+    from .batch import gather_rows, shard_bounds
+    params = _params7(params)
+    D = params.shape[1]
+    if dist.is_available() and dist.is_initialized():
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+    else:
+        world, rank = 1, 0
+    lo, hi = shard_bounds(D, world, rank)
+    block = np.ascontiguousarray(params[:, lo:hi])
+    if evaluate is None:
+        evaluate = lambda b, first: gen_rts_from_cdf_batch(b, samples, cdf_lb, cdf_ub, dt, seed=seed, return_rts=False,
+                                                           return_stats=True, first_draw=first)
+    local = evaluate(block, lo) if hi > lo else np.empty((0, len(STAT_NAMES)))
+    local = torch.from_numpy(np.ascontiguousarray(local, dtype=np.float64))
+    if world > 1 and dist.get_backend(group) == "nccl":
+        local = local.cuda()
+    return gather_rows(local, D, group).cpu().numpy()

@@ -152,11 +152,12 @@ int hddm_gen_rts_from_cdf_batch(const double *xgrid, int64_t m, const double *pa
                                 const double *f, const double *u_delay, int64_t samples, double *rts,
                                 double *stats);
 /* Same with the uniforms drawn on the device: Philox4x32-10 keyed by seed, one counter sequence per
- * (draw, sample) -- reproducible, independent of slab size and of how draws are sharded over GPUs when
- * every rank passes its global draw offset through `params` order.  Not numpy's stream. */
+ * (global draw index, sample), where column d of params is global draw first_draw + d -- reproducible and
+ * independent of slab size and of how the draws are sharded over GPUs (rank r passes the first index of
+ * its block).  Not numpy's stream. */
 int hddm_gen_rts_from_cdf_batch_seeded(const double *xgrid, int64_t m, const double *params, int64_t D,
-                                       unsigned long long seed, int64_t samples, double *rts,
-                                       double *stats);
+                                       unsigned long long seed, int64_t first_draw, int64_t samples,
+                                       double *rts, double *stats);
 /* The statistics alone, for D data sets of `samples` signed RTs each ([D][samples] -> [D][15]); used for
  * the observed data of a posterior predictive check. */
 int hddm_ppc_stats(const double *rts, int64_t D, int64_t samples, double *stats);

@@ -187,3 +187,78 @@ def test_quantile_objectives_match_the_stochastic_class(gpu):
     c, g = posterior.quantile_objectives(np.stack(emp), np.stack(freq), np.array(ns), params)
     np.testing.assert_array_equal(c, np.array(chi))
     np.testing.assert_array_equal(g, np.array(gsq))
+
+
+@pytest.mark.gpu
+def test_device_rng_rows_do_not_depend_on_how_draws_are_split(gpu):
+    """Sharding invariance on one GPU: the draws evaluated as one batch, or as two blocks that pass their
+    global first_draw, give the same simulated data sets and statistics (what makes the multi-GPU table
+    independent of the world size)."""
+    from hddm_b200 import posterior
+    rng = np.random.default_rng(21)
+    D, S = 17, 150
+    params = _draws(rng, D)
+    rts, stats = posterior.gen_rts_from_cdf_batch(params, S, -5.0, 5.0, 1e-3, seed=9, return_stats=True)
+    cut = 6
+    a = posterior.gen_rts_from_cdf_batch(np.ascontiguousarray(params[:, :cut]), S, -5.0, 5.0, 1e-3, seed=9)
+    b = posterior.gen_rts_from_cdf_batch(np.ascontiguousarray(params[:, cut:]), S, -5.0, 5.0, 1e-3, seed=9, first_draw=cut)
+    assert np.array_equal(np.concatenate([a, b]), rts)
+    table = posterior.post_pred_stats_sharded(params, S, -5.0, 5.0, 1e-3, seed=9)  # world size 1
+    assert np.array_equal(np.isnan(table), np.isnan(stats))
+    assert np.array_equal(table[~np.isnan(table)], stats[~np.isnan(stats)])
+
+
+def _ppc_gloo_worker(rank, world, port, D, q):
+    import os
+    import sys
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from hddm_b200 import posterior
+    table = posterior.post_pred_stats_sharded(_ppc_params(D), 50, evaluate=_ppc_standin)
+    q.put((rank, table.copy()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _ppc_params(D):
+    return np.ascontiguousarray(draw_params(np.random.default_rng(77), D))
+
+
+def _ppc_standin(block, first_draw):
+    """Stand-in for the CUDA launch (tests only): the statistics oracle on RTs keyed by the GLOBAL draw index."""
+    from oracle.ppc_oracle import ppc_stats
+    rows = []
+    for d in range(block.shape[1]):
+        r = np.random.default_rng(1000 + first_draw + d)
+        rts = (block[5, d] + r.gamma(2.0, 0.25, 50)) * np.where(r.random(50) < 0.7, 1.0, -1.0)
+        rows.append(ppc_stats(rts))
+    return np.stack(rows)
+
+
+@pytest.mark.parametrize("D", [9, 1])
+def test_sharded_post_pred_stats_over_gloo_world2(D):
+    """N>1 host path of the posterior-predictive batch: draws split over 2 ranks, one all_gather of the
+    [D, 15] statistics, every rank sees the single-process table bit for bit."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_ppc_gloo_worker, args=(r, 2, port, D, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = _ppc_standin(_ppc_params(D), 0)
+    for r in range(2):
+        assert got[r].shape == (D, 15)
+        assert np.array_equal(np.isnan(got[r]), np.isnan(want))
+        assert np.array_equal(got[r][~np.isnan(want)], want[~np.isnan(want)])
