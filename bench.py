@@ -202,14 +202,17 @@ def run_ours(args):
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the hddm_b200 path has no CPU fallback")
+    # stdout carries exactly ONE JSON line: anything native libraries print there meanwhile (NCCL's version
+    # banner at NCCL_DEBUG=VERSION/WARN) is sent to stderr; fd 1 is restored for the final print
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # keep stdout to the one JSON line: NCCL prints its version banner there at NCCL_DEBUG=VERSION
-        os.environ["NCCL_DEBUG"] = os.environ.get("HDDM_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=dev)
     _lib.check(_lib.lib().hddm_b200_init(local))
 
@@ -338,7 +341,11 @@ def run_ours(args):
             "cpu_baseline": cpu,
             "clocks": clocks,
         }
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
         print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(2, 1)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

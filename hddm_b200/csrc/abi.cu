@@ -33,6 +33,8 @@ struct ParSpec {
     int64_t set_stride, trial_stride;
 };
 
+constexpr int64_t kZeroCopyMaxSets = 2048;  // above this the inputs are worth a real H2D copy
+
 // Core of every "sum of log densities" entry point.  x is either a host buffer (h_x) staged
 // into the arena or already device-resident (d_x).
 int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_seg, int64_t n_seg,
@@ -89,7 +91,12 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     const size_t out_bytes = L.total - off_logp;
     TRY(ensure_arena(L.total));
     const bool staged = (small_hi - small_lo) <= kPinnedMax && out_bytes <= kPinnedMax;
-    if (staged) TRY(ensure_pinned((small_hi - small_lo) > out_bytes ? (small_hi - small_lo) : out_bytes));
+    // Latency path (an MCMC step on 200-trial nodes is launch-bound): with few sets the kernels read the small
+    // inputs from, and write the log-likelihoods to, page-locked host memory directly (UVA: cudaMallocHost
+    // memory is device-accessible under the same address) -- no H2D / D2H copies, only launch + sync.
+    const size_t in_bytes = small_hi - small_lo;
+    const bool zero_copy = staged && P <= kZeroCopyMaxSets;
+    if (staged) TRY(ensure_pinned(zero_copy ? align_up(in_bytes) + out_bytes : (in_bytes > out_bytes ? in_bytes : out_bytes)));
 
     cudaStream_t s = g_rt.stream;
     if (h_x && n > 0)
@@ -102,7 +109,8 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
         if (h_node) memcpy(ph + off_node, h_node, (size_t)P * sizeof(int64_t));
         for (int u = 0; u < n_uploads; ++u)
             if (uploads[u].bytes) memcpy(ph + off_up[u], uploads[u].host, uploads[u].bytes);
-        CUDA_TRY(cudaMemcpyAsync(L.at<char>(small_lo), g_rt.pinned, small_hi - small_lo, cudaMemcpyHostToDevice, s));
+        if (!zero_copy)
+            CUDA_TRY(cudaMemcpyAsync(L.at<char>(small_lo), g_rt.pinned, in_bytes, cudaMemcpyHostToDevice, s));
     } else {
         if (h_seg)
             CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_seg), h_seg, (size_t)(n_seg + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
@@ -112,21 +120,28 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
             if (uploads[u].bytes)
                 CUDA_TRY(cudaMemcpyAsync(L.at<char>(off_up[u]), uploads[u].host, uploads[u].bytes, cudaMemcpyHostToDevice, s));
     }
-    CUDA_TRY(cudaMemsetAsync(L.at<char>(off_evals), 0, sizeof(unsigned long long), s));
+    if (evals) CUDA_TRY(cudaMemsetAsync(L.at<char>(off_evals), 0, sizeof(unsigned long long), s));
 
+    // where the kernels find the small inputs: the arena copy, or the page-locked staging itself
+    char* small_base = zero_copy ? g_rt.pinned - small_lo : g_rt.arena;
+    auto small_at = [&](size_t off) { return small_base + off; };
     LikeArgs a;
     memset(&a, 0, sizeof(a));
     a.x = h_x ? L.at<double>(off_x) : d_x;
-    a.seg = h_seg ? L.at<int64_t>(off_seg) : nullptr;
-    a.set_node = h_node ? L.at<int64_t>(off_node) : nullptr;
+    a.seg = h_seg ? reinterpret_cast<const int64_t*>(small_at(off_seg)) : nullptr;
+    a.set_node = h_node ? reinterpret_cast<const int64_t*>(small_at(off_node)) : nullptr;
     if (sortable) {
-        CUDA_TRY(sort_trials(L.at<double>(off_x), L.at<double>(off_xs), n, a.seg, h_seg ? n_seg : 0,
-                             L.at<char>(off_sort), sort_bytes, s));
+        // (the sort reads the segment table from device memory: sortable launches carry host trials and are
+        // not the latency path; give it the arena copy)
+        if (zero_copy && h_seg)
+            CUDA_TRY(cudaMemcpyAsync(L.at<int64_t>(off_seg), h_seg, (size_t)(n_seg + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+        CUDA_TRY(sort_trials(L.at<double>(off_x), L.at<double>(off_xs), n, h_seg ? L.at<int64_t>(off_seg) : nullptr,
+                             h_seg ? n_seg : 0, L.at<char>(off_sort), sort_bytes, s));
         a.x = L.at<double>(off_xs);
     }
     a.cont = h_cont ? L.at<int32_t>(off_cont) : nullptr;
     for (int k = 0; k < kNumPar; ++k) {
-        a.par[k] = L.at<double>(off_up[spec[k].upload]) + spec[k].offset;
+        a.par[k] = reinterpret_cast<const double*>(small_at(off_up[spec[k].upload])) + spec[k].offset;
         a.set_stride[k] = spec[k].set_stride;
         a.trial_stride[k] = spec[k].trial_stride;
     }
@@ -136,9 +151,16 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     a.mode = mode;
     a.nm = nm;
     a.partial = L.at<double>(off_partial);
-    a.logp = L.at<double>(off_logp);
-    a.evals = L.at<unsigned long long>(off_evals);
+    double* host_out = reinterpret_cast<double*>(g_rt.pinned + align_up(in_bytes));  // zero-copy result block
+    a.logp = zero_copy ? host_out : L.at<double>(off_logp);
+    a.evals = evals ? L.at<unsigned long long>(off_evals) : nullptr;
     CUDA_TRY(launch_like(a, s));
+    if (zero_copy) {
+        if (evals) CUDA_TRY(cudaMemcpyAsync(evals, a.evals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+        memcpy(logp, host_out, (size_t)P * sizeof(double));
+        return HDDM_OK;
+    }
     if (staged) {  // the upload has been consumed by the kernels queued before this copy: reuse the staging
         CUDA_TRY(cudaMemcpyAsync(g_rt.pinned, L.at<char>(off_logp), out_bytes, cudaMemcpyDeviceToHost, s));
         CUDA_TRY(cudaStreamSynchronize(s));

@@ -60,7 +60,10 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     const bool multi = a.mode == kModeMulti || a.mode == kModeMultiRL;  // no range / zero guards
     const bool range_ok = multi || ((p_out >= 0) & (p_out <= 1));
     if (begin >= hi || !range_ok) {  // (ragged batch: shorter sets have empty trailing chunks)
-        if (threadIdx.x == 0) a.partial[p * a.chunks + chunk] = range_ok ? 0.0 : -INFINITY;
+        if (threadIdx.x == 0) {
+            a.partial[p * a.chunks + chunk] = range_ok ? 0.0 : -INFINITY;
+            if (a.chunks == 1) a.logp[p] = range_ok ? 0.0 : -INFINITY;  // single chunk: no k_like_final
+        }
         return;
     }
     const int64_t end = begin + kTrialsPerBlock < hi ? begin + kTrialsPerBlock : hi;
@@ -174,6 +177,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         for (int w = 0; w < kLikeThreads / 32; ++w) s += warp_part[w];
         if (!multi && any_zero) s = -INFINITY;
         a.partial[p * a.chunks + chunk] = s;
+        if (a.chunks == 1) a.logp[p] = s;  // single chunk: this IS the set's log-likelihood (no k_like_final)
     }
 }
 
@@ -220,6 +224,7 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
         k_like_partial<8, false><<<grid, kLikeThreads, 0, stream>>>(b);
     else
         k_like_partial<0, false><<<grid, kLikeThreads, 0, stream>>>(b);
+    if (a.chunks == 1) return cudaGetLastError();  // short nodes: one launch, k_like_partial wrote logp
     const int sets_per_block = 128 / 32;
     k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(b);
     return cudaGetLastError();

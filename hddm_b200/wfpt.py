@@ -183,7 +183,7 @@ def wiener_like_rlddm_batch(x, response, feedback, split_by, params, err=1e-4, n
     out = np.empty(P, dtype=np.double)
     evals = C.c_ulonglong(0)
     check(lib().hddm_wiener_like_rlddm_batch(dptr(x), rp, fp, sp, n, dptr(params), P, err, n_st, n_sz,
-                                             int(bool(use_adaptive)), simps_err, dptr(out), C.byref(evals)))
+                                             int(bool(use_adaptive)), simps_err, dptr(out), C.byref(evals) if return_evals else None))
     return (out, evals.value) if return_evals else out
 
 
@@ -277,7 +277,7 @@ def wiener_like_batch(x, params, seg=None, err=1e-4, n_st=2, n_sz=2, use_adaptiv
     out = np.empty(P, dtype=np.double)
     evals = C.c_ulonglong(0)
     check(lib().hddm_wiener_like_batch(dptr(x), x.shape[0], segp, dptr(params), P, err, n_st, n_sz,
-                                       int(bool(use_adaptive)), simps_err, dptr(out), C.byref(evals)))
+                                       int(bool(use_adaptive)), simps_err, dptr(out), C.byref(evals) if return_evals else None))
     return (out, evals.value) if return_evals else out
 
 
@@ -295,7 +295,7 @@ def wiener_like_multi_batch(x, v_trial, params, err=1e-4, n_st=10, n_sz=10, use_
     evals = C.c_ulonglong(0)
     check(lib().hddm_wiener_like_multi_batch(dptr(x), x.shape[0], dptr(v_trial), dptr(params), P, err, n_st,
                                              n_sz, int(bool(use_adaptive)), simps_err, dptr(out),
-                                             C.byref(evals)))
+                                             C.byref(evals) if return_evals else None))
     return (out, evals.value) if return_evals else out
 
 
@@ -316,7 +316,7 @@ def wiener_like_regression_batch(x, design, coef, params, err=1e-4, n_st=10, n_s
     evals = C.c_ulonglong(0)
     check(lib().hddm_wiener_like_regression_batch(dptr(x), x.shape[0], dptr(design), design.shape[0], dptr(coef),
                                                   dptr(params), P, err, n_st, n_sz, int(bool(use_adaptive)),
-                                                  simps_err, dptr(out), C.byref(evals)))
+                                                  simps_err, dptr(out), C.byref(evals) if return_evals else None))
     return (out, evals.value) if return_evals else out
 
 
@@ -344,7 +344,7 @@ def wiener_like_nodes(x, node_off, set_node, params, err=1e-4, n_st=2, n_sz=2, u
     check(lib().hddm_wiener_like_nodes(dptr(x), x.shape[0], node_off.ctypes.data_as(_lib.c_lp),
                                        node_off.shape[0] - 1, set_node.ctypes.data_as(_lib.c_lp), dptr(params),
                                        P, err, n_st, n_sz, int(bool(use_adaptive)), simps_err, dptr(out),
-                                       C.byref(evals)))
+                                       C.byref(evals) if return_evals else None))
     return (out, evals.value) if return_evals else out
 
 
@@ -378,7 +378,7 @@ class Trials(object):
         evals = C.c_ulonglong(0)
         check(lib().hddm_trials_wiener_like_batch(self._h, segp, dptr(params), P, err, n_st, n_sz,
                                                   int(bool(use_adaptive)), simps_err, dptr(out),
-                                                  C.byref(evals)))
+                                                  C.byref(evals) if return_evals else None))
         return (out, evals.value) if return_evals else out
 
     def wiener_like_nodes(self, node_off, set_node, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1,
@@ -392,7 +392,7 @@ class Trials(object):
         check(lib().hddm_trials_wiener_like_nodes(self._h, node_off.ctypes.data_as(_lib.c_lp),
                                                   node_off.shape[0] - 1, set_node.ctypes.data_as(_lib.c_lp),
                                                   dptr(params), P, err, n_st, n_sz, int(bool(use_adaptive)),
-                                                  simps_err, dptr(out), C.byref(evals)))
+                                                  simps_err, dptr(out), C.byref(evals) if return_evals else None))
         return (out, evals.value) if return_evals else out
 
     def close(self):
