@@ -147,6 +147,7 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     }
     a.n = n;
     a.n_sets = P;
+    a.max_seg_len = max_len;
     a.chunks = (int)chunks;
     a.mode = mode;
     a.nm = nm;
@@ -272,7 +273,8 @@ int hddm_b200_fp64_peak(int iters, double* flops, float* ms)
 
 int hddm_b200_set_kernel(int which)
 {
-    if (which < 0 || which > 2) return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto), 1 (generic) or 2 (no grid)");
+    if (which < 0 || which > 3)
+        return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto), 1 (generic), 2 (no grid) or 3 (grid, one pass)");
     std::lock_guard<std::mutex> lock(g_rt.mu);
     g_kernel_choice = which;
     return HDDM_OK;
@@ -684,6 +686,7 @@ int hddm_wiener_like_batch_dev(const double* d_x, int64_t n, const int64_t* d_se
     }
     a.n = n;
     a.n_sets = P;
+    a.max_seg_len = d_seg ? max_seg_len : n;
     a.chunks = (int)chunks;
     a.mode = kModeWienerLike;
     a.nm = make_numerics(err, n_st, n_sz, use_adaptive, simps_err);

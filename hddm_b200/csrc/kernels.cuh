@@ -65,6 +65,7 @@ struct LikeArgs {
     int64_t trial_stride[kNumPar];
     int64_t n;
     int64_t n_sets;
+    int64_t max_seg_len;  // longest segment (0: unknown, n is assumed): picks the one- or two-pass kernel
     int chunks;  // ceil(max segment length / kTrialsPerBlock)
     int mode;
     Numerics nm;
@@ -75,7 +76,7 @@ struct LikeArgs {
 };
 
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream);
-extern int g_kernel_choice;  // 0 auto, 1 generic evaluator only
+extern int g_kernel_choice;  // 0 auto, 1 generic evaluator only, 2 no grid evaluator, 3 grid evaluator in one pass only
 
 // par_sets == nullptr: one parameter set (par) over x[n] -> y[n].  Otherwise n_sets parameter sets, SoA
 // [9][n_sets]; set s (blockIdx.y) reads x + s * x_set_stride (0: one grid shared by all sets) and writes

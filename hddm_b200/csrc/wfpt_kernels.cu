@@ -42,7 +42,9 @@ __device__ __forceinline__ double load_par(const LikeArgs& a, int k, int64_t p, 
 // integration, large-time series of at most KMAX terms).  KMAX == 0: the generic evaluator of
 // wfpt_device.cuh (any per-trial parameter, fixed-grid Simpson, no table).
 // GRID: additionally sv, a, t, st uniform per set -> the v3 grid evaluator of wfpt_grid.cuh.
-template <int KMAX, bool GRID>
+// TWO_PASS (GRID only): see the trial loop.  Pays off when a thread owns several trials (long segments);
+// short observed nodes (one round per thread) take the one-pass flavour, whose critical path is shorter.
+template <int KMAX, bool GRID, bool TWO_PASS = false>
 __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     k_like_partial(const __grid_constant__ LikeArgs a)
 {
@@ -84,9 +86,10 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
 
     // pass 1 (GRID): need = the trial is deferred to pass 2; otherwise need stays false
     auto density = [&](double x, unsigned long long& ev, bool first_pass, bool* need) {
-        if (GRID)
+        if (GRID && TWO_PASS)
             return first_pass ? full_pdf_grid<KT, true>(x, par[0], gs, a.nm, &a.tab, ev, need)
                               : full_pdf_grid_slow<KT>(x, par[0], gs, a.nm, &a.tab, ev);
+        if (GRID) return full_pdf_grid<KT, false>(x, par[0], gs, a.nm, &a.tab, ev);
         if (KMAX > 0)
             return full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(x, par[0], par[1], par[2], par[3], par[4], par[5],
                                                         par[6], a.nm, &a.tab, wt, ev);
@@ -140,7 +143,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         }
         return need;
     };
-    if (GRID) {
+    if (GRID && TWO_PASS) {
         // Pass 1 evaluates the first 5 x 5 level, which settles almost every trial; the few that need more are
         // queued per warp (ballot order: deterministic) and pass 2 runs them through the complete evaluator with
         // full warps.  Keeps the slow paths' code, registers and local-memory arrays out of the hot loop.
@@ -214,7 +217,14 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     bool uniform = true;  // everything but the drift is uniform per set
     for (int k = 1; k < 7; ++k) uniform &= a.trial_stride[k] == 0;
     const bool gridk = fast && uniform && g_kernel_choice != 2;
-    if (gridk && b.tab.max_large_k <= 4)
+    // two passes when threads own several trials each (segments longer than two rounds of the CTA)
+    const int64_t longest = a.max_seg_len > 0 ? a.max_seg_len : a.n;
+    const bool two_pass = gridk && g_kernel_choice != 3 && longest > 2 * kLikeThreads;
+    if (two_pass && b.tab.max_large_k <= 4)
+        k_like_partial<4, true, true><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (two_pass)
+        k_like_partial<8, true, true><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (gridk && b.tab.max_large_k <= 4)
         k_like_partial<4, true><<<grid, kLikeThreads, 0, stream>>>(b);
     else if (gridk)
         k_like_partial<8, true><<<grid, kLikeThreads, 0, stream>>>(b);

@@ -23,13 +23,14 @@ def W(gpu):
     return wfpt
 
 
-@pytest.fixture(autouse=True, params=["auto", "walk", "generic"])
+@pytest.fixture(autouse=True, params=["auto", "onepass", "walk", "generic"])
 def evaluator(request, gpu):
-    """Every parity test runs three times: with the per-launch choice (the grid evaluator of
-    csrc/wfpt_grid.cuh where it applies), with the grid evaluator disabled (table-driven walk of
+    """Every parity test runs four times: with the per-launch choice (the grid evaluator of
+    csrc/wfpt_grid.cuh where it applies, in two passes for long segments), with the grid evaluator forced
+    into one pass, with the grid evaluator disabled (table-driven walk of
     csrc/wfpt_fast.cuh) and with the generic evaluator forced.  All three are CUDA."""
     from hddm_b200 import _lib
-    _lib.check(_lib.lib().hddm_b200_set_kernel({"auto": 0, "generic": 1, "walk": 2}[request.param]))
+    _lib.check(_lib.lib().hddm_b200_set_kernel({"auto": 0, "generic": 1, "walk": 2, "onepass": 3}[request.param]))
     yield request.param
     _lib.check(_lib.lib().hddm_b200_set_kernel(0))
 
