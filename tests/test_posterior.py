@@ -262,3 +262,33 @@ def test_sharded_post_pred_stats_over_gloo_world2(D):
         assert got[r].shape == (D, 15)
         assert np.array_equal(np.isnan(got[r]), np.isnan(want))
         assert np.array_equal(got[r][~np.isnan(want)], want[~np.isnan(want)])
+
+
+@pytest.mark.gpu
+def test_batch_edge_cases(gpu):
+    """Empty and maximum sizes of the batched entry points (the reference's own edge behaviour: an empty
+    trial vector gives 0.0, src/wfpt.pyx:62-75; empty batches give empty results)."""
+    from hddm_b200 import posterior, wfpt
+    rng = np.random.default_rng(2)
+    none = np.zeros((7, 0))
+    assert posterior.gen_rts_from_cdf_batch(none, 10, -3, 3, 1e-2, seed=1).shape == (0, 10)
+    assert posterior.ppc_stats(np.zeros((0, 5))).shape == (0, 15)
+    assert posterior.dmat_cdf_batch(np.zeros((0, 4)), np.zeros((9, 0))).shape == (0, 4)
+    assert posterior.simulate_drift_batch(none, 5).shape == (0, 5)
+    # the largest data set the statistics kernel takes, and one beyond
+    big = (0.3 + rng.gamma(2.0, 0.25, (2, posterior.MAX_SAMPLES))) * np.where(rng.random((2, posterior.MAX_SAMPLES)) < 0.6, 1., -1.)
+    from oracle.ppc_oracle import ppc_stats
+    np.testing.assert_allclose(posterior.ppc_stats(big), np.stack([ppc_stats(r) for r in big]), rtol=1e-12)
+    with pytest.raises(ValueError):
+        posterior.ppc_stats(np.ones((1, posterior.MAX_SAMPLES + 1)))
+    # batched likelihoods: no sets, no trials
+    x = (0.8 + rng.gamma(2.0, 0.25, 50)) * np.where(rng.random(50) < 0.6, 1., -1.)
+    assert wfpt.wiener_like_batch(x, np.zeros((9, 0))).shape == (0,)
+    p = np.array([[1.], [.5], [2.], [.5], [.1], [.3], [.1], [.05], [.1]])
+    assert wfpt.wiener_like_batch(np.zeros(0), p)[0] == 0.0
+    assert wfpt.wiener_like_regression_batch(np.zeros(0), np.zeros((2, 0)), np.ones((2, 1)), p)[0] == 0.0
+    one = wfpt.wiener_like_regression_batch(x, np.ones((1, 50)), np.array([[1.0]]), p, n_st=2, n_sz=2)
+    assert one[0] == wfpt.wiener_like_multi(x, np.full(50, 1.0), .5, 2., .5, .1, .3, .1, 1e-4, ['v'], 2, 2, 1, 1e-3, .05, .1)
+    l = np.zeros(0, dtype=np.int64)
+    assert wfpt.wiener_like_rlddm_batch(np.zeros(0), l, np.zeros(0), l, np.zeros((12, 0))).shape == (0,)
+    assert wfpt.wiener_like_rl_batch(l, np.zeros(0), l, np.zeros((7, 0))).shape == (0,)
