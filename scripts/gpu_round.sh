@@ -13,3 +13,5 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 3 -c 1 -o gpurun_out/${TAG}_like -f python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/${TAG}_ncu_f.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 3 -c 1 -o gpurun_out/${TAG}_like_B -f python bench.py --steps 1 --warmup 3 --no-cpu --sweep B --trials 20000 --sets 2000 > gpurun_out/${TAG}_ncu_fB.log 2>&1
 ls -la gpurun_out | tail -20
+# large-trial corner (1e7 trials, few sets): achieved HBM traffic of the likelihood kernel
+timeout 900 ncu --set full --clock-control none -k regex:k_like_partial -s 3 -c 1 -o gpurun_out/${TAG}_like_T1e7 -f python bench.py --steps 1 --warmup 3 --no-cpu --trials 10000000 --sets 148 > gpurun_out/${TAG}_ncu_fT.log 2>&1

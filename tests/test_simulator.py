@@ -83,3 +83,17 @@ def test_reference_shaped_single_call(gpu):
     assert 0.6 < (r > 0).mean() < 0.95
     with pytest.raises(NotImplementedError):
         posterior.gen_rts_from_simulated_drift(dict(p, v_switch=1.0, t_switch=0.2), samples=5)
+
+
+def test_stochastic_class_random_with_drift_sampling(gpu):
+    """Wfpt.random() with sampling_method='drift' (hddm/likelihoods.py:76-81 -> hddm/generate.py:187-188),
+    the path HDDMRegressor's posterior predictive uses (hddm/models/hddm_regression.py:62)."""
+    from hddm_b200 import likelihoods as L
+    cls = L.generate_wfpt_stochastic_class(sampling_method='drift', sampling_dt=1e-3)
+    node = cls(value=np.zeros(400), v=1.5, sv=0.3, a=1.5, z=0.5, sz=0.1, t=0.3, st=0.1)
+    np.random.seed(3)
+    r = node.random()
+    assert r.shape == (400,) and not np.isnan(r).any()
+    assert (np.abs(r) >= 0.3 - 0.05 - 1e-9).all() and 0.7 < (r > 0).mean() < 0.99
+    with pytest.raises(TypeError):
+        L.generate_wfpt_stochastic_class(sampling_method='nope')(value=np.zeros(3), v=1, sv=0, a=1, z=.5, sz=0, t=.3, st=0).random()
