@@ -37,7 +37,8 @@ const SeriesTable& series_table_for(double err);
 
 // Parameter order used everywhere: v, sv, a, z, sz, t, st, p_outlier, w_outlier.
 constexpr int kNumPar = 9;
-constexpr int kTrialsPerBlock = 2048;  // one CTA reduces this many trials of one parameter set
+constexpr int kTrialsPerBlock = 2048;  // one CTA reduces this many trials of one parameter set ...
+constexpr int kTrialsPerBigBlock = 8192;  // ... or this many when the grid is large enough anyway (launch_like)
 constexpr int kLikeThreads = 256;
 
 enum LikeMode : int {
@@ -66,7 +67,8 @@ struct LikeArgs {
     int64_t n;
     int64_t n_sets;
     int64_t max_seg_len;  // longest segment (0: unknown, n is assumed): picks the one- or two-pass kernel
-    int chunks;  // ceil(max segment length / kTrialsPerBlock)
+    int chunks;  // ceil(max segment length / kTrialsPerBlock): CTAs per set as the caller sized `partial`
+    int trials_per_block;  // set by launch_like (callers leave 0)
     int mode;
     Numerics nm;
     SeriesTable tab;

@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     const int64_t node = a.set_node ? a.set_node[p] : p;
     const int64_t lo = a.seg ? a.seg[node] : 0;
     const int64_t hi = a.seg ? a.seg[node + 1] : a.n;
-    const int64_t begin = lo + (int64_t)chunk * kTrialsPerBlock;
+    const int64_t begin = lo + (int64_t)chunk * a.trials_per_block;
     const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
     // src/wfpt.pyx:50-51,63-64: p_outlier outside [0,1] -> -inf before any trial is looked at
     const bool multi = a.mode == kModeMulti || a.mode == kModeMultiRL;  // no range / zero guards
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         }
         return;
     }
-    const int64_t end = begin + kTrialsPerBlock < hi ? begin + kTrialsPerBlock : hi;
+    const int64_t end = begin + a.trials_per_block < hi ? begin + a.trials_per_block : hi;
 
     // Set-uniform parameters are read once; per-trial ones (trial_stride != 0) inside the loop.
     double par[7];
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
             acc += log(d);
         }
     };
-    static_assert(kTrialsPerBlock / kLikeThreads <= 256, "mantissa product must stay finite (two passes)");
+    static_assert(kTrialsPerBigBlock / kLikeThreads <= 256, "mantissa product must stay finite (two passes)");
     unsigned long long evals = 0;
     bool hit_zero = false;
     // One trial: load, evaluate, mix, accumulate.  Returns true when the trial was deferred.
@@ -147,7 +147,8 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         // Pass 1 evaluates the first 5 x 5 level, which settles almost every trial; the few that need more are
         // queued per warp (ballot order: deterministic) and pass 2 runs them through the complete evaluator with
         // full warps.  Keeps the slow paths' code, registers and local-memory arrays out of the hot loop.
-        __shared__ unsigned short queue[kLikeThreads / 32][kTrialsPerBlock / (kLikeThreads / 32)];
+        __shared__ unsigned short queue[kLikeThreads / 32][kTrialsPerBigBlock / (kLikeThreads / 32)];
+        static_assert(kTrialsPerBigBlock <= 65536, "queue entries are 16-bit offsets into the CTA's block of trials");
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         const int rounds = (int)((end - begin + kLikeThreads - 1) / kLikeThreads);
         int queued = 0;  // warp-uniform
@@ -210,7 +211,20 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     if (a.n_sets <= 0) return cudaSuccess;
     LikeArgs b = a;
     b.tab = series_table_for(a.nm.err);
-    dim3 grid((unsigned)a.n_sets, (unsigned)a.chunks);
+    b.trials_per_block = kTrialsPerBlock;
+    {
+        // The per-set tables are rebuilt by every CTA of a set (~15k warp-instructions, mostly serial): with
+        // plenty of CTAs to fill the GPU anyway, give each one four times the trials.  (Pass 2 stays at the end
+        // of the CTA: running it in instalments as the queue fills was measured 20 % slower on onset-mixed data,
+        // the two code regions evict each other from the instruction cache.)
+        const int64_t longest = a.max_seg_len > 0 ? a.max_seg_len : a.n;
+        const int64_t big_chunks = (longest + kTrialsPerBigBlock - 1) / kTrialsPerBigBlock;
+        if (a.chunks >= 4 && (int64_t)a.n_sets * big_chunks >= 148 * 2 * 8) {
+            b.trials_per_block = kTrialsPerBigBlock;
+            b.chunks = (int)(big_chunks < 1 ? 1 : big_chunks);
+        }
+    }
+    dim3 grid((unsigned)b.n_sets, (unsigned)b.chunks);
     // z (3) and sz (4) must be uniform per set for the shared start-point tables
     const bool fast = g_kernel_choice != 1 && a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 &&
                       b.tab.max_large_k <= 8 && a.trial_stride[3] == 0 && a.trial_stride[4] == 0;
@@ -234,7 +248,7 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
         k_like_partial<8, false><<<grid, kLikeThreads, 0, stream>>>(b);
     else
         k_like_partial<0, false><<<grid, kLikeThreads, 0, stream>>>(b);
-    if (a.chunks == 1) return cudaGetLastError();  // short nodes: one launch, k_like_partial wrote logp
+    if (b.chunks == 1) return cudaGetLastError();  // short nodes: one launch, k_like_partial wrote logp
     const int sets_per_block = 128 / 32;
     k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(b);
     return cudaGetLastError();
