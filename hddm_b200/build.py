@@ -13,7 +13,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
-LIB = os.path.join(HERE, "libhddm_b200.so")
+# HDDM_B200_LIB: load (and build) another file name -- kernel variants built with HDDM_B200_NVCC_EXTRA
+# (space-separated extra nvcc flags, e.g. -DHDDM_LIKE_THREADS=128) can be measured side by side on the GPU box.
+LIB = os.environ.get("HDDM_B200_LIB") or os.path.join(HERE, "libhddm_b200.so")
 SOURCES = ["abi.cu", "abi_rl.cu", "abi_ppc.cu", "rl_kernels.cu", "ppc_kernels.cu", "sim_kernels.cu", "wfpt_kernels.cu", "cdfdif_kernels.cu", "gen_kernels.cu", "series_table.cu", "sort_kernels.cu"]
 HEADERS = ["kernels.cuh", "abi_runtime.cuh", "wfpt_device.cuh", "wfpt_fast.cuh", "wfpt_grid.cuh", os.path.join(ROOT, "include", "hddm_b200.h")]
 
@@ -39,7 +41,8 @@ def up_to_date():
 def build_library(force=False, verbose=False):
     if up_to_date() and not force:
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+    cmd = [_nvcc()] + NVCC_FLAGS + os.environ.get("HDDM_B200_NVCC_EXTRA", "").split() + \
+          (["-Xptxas", "-v"] if verbose else []) + \
           ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if verbose or r.returncode != 0:

@@ -38,7 +38,16 @@ const SeriesTable& series_table_for(double err);
 // Parameter order used everywhere: v, sv, a, z, sz, t, st, p_outlier, w_outlier.
 constexpr int kNumPar = 9;
 constexpr int kTrialsPerBlock = 2048;  // one CTA reduces this many trials of one parameter set ...
-constexpr int kTrialsPerBigBlock = 8192;  // ... or this many when the grid is large enough anyway (launch_like)
+// Build-time tuning knobs (python -m hddm_b200.build with HDDM_B200_NVCC_EXTRA="-DHDDM_BIG_BLOCK=..." and
+// HDDM_B200_LIB=<other file> builds a variant to measure beside the default; profiles/r1_v7_summary.md).
+#ifndef HDDM_BIG_BLOCK
+#define HDDM_BIG_BLOCK 8192
+#endif
+#ifndef HDDM_UNROLL_J
+#define HDDM_UNROLL_J 5
+#endif
+constexpr int kTrialsPerBigBlock = HDDM_BIG_BLOCK;  // ... or this many when the grid is large enough anyway (launch_like)
+constexpr int kUnrollJ = HDDM_UNROLL_J;  // first pass: the five decision-time nodes of a trial are unrolled (5) or looped (1)
 constexpr int kLikeThreads = 256;
 
 enum LikeMode : int {

@@ -47,6 +47,9 @@ __device__ const double g_exp2_tab[kExpTab] = {
     0x1.d5818dcfba487p+0, 0x1.da9e603db3285p+0, 0x1.dfc97337b9b5fp+0, 0x1.e502ee78b3ff6p+0,
     0x1.ea4afa2a490dap+0, 0x1.efa1bee615a27p+0, 0x1.f50765b6e4540p+0, 0x1.fa7c1819e90d8p+0};
 
+__constant__ double g_exp_c[6] = {0x1.71547652b82fep+6, -0x1.62e42fefa39efp-7, -0x1.abc9e3b39803fp-62,
+                                  1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0};
+
 // exp(x) for -700 <= x <= 700 (CLAMP: -2e7 <= x <= 700; results below 2^-1021 come out as exactly 0,
 // used only where such a term is added to one that is larger by tens of orders of magnitude).
 // x = (64 n' + i) ln2/64 + r, |r| <= ln2/128: exp(x) = 2^n' * T[i] * (1 + r + r^2/2 + ... + r^5/120).
@@ -54,14 +57,14 @@ template <bool CLAMP>
 __device__ __forceinline__ double exp_tab(double x, const double* __restrict__ T)
 {
     const double magic = 6755399441055744.0;  // 1.5 * 2^52: adding it leaves rint(.) in the low word
-    const double t = fma(x, 0x1.71547652b82fep+6, magic);
+    const double t = fma(x, g_exp_c[0], magic);
     const int n = __double2loint(t);
     const double nd = t - magic;
-    double r = fma(nd, -0x1.62e42fefa39efp-7, x);
-    r = fma(nd, -0x1.abc9e3b39803fp-62, r);
+    double r = fma(nd, g_exp_c[1], x);
+    r = fma(nd, g_exp_c[2], r);
     const double r2 = r * r;
-    double c = fma(r, 1.0 / 120.0, 1.0 / 24.0);
-    c = fma(c, r, 1.0 / 6.0);
+    double c = fma(r, g_exp_c[3], g_exp_c[4]);
+    c = fma(c, r, g_exp_c[5]);
     c = fma(c, r, 0.5);
     const double p = fma(r2, c, r);
     const double tv = T[n & (kExpTab - 1)];
@@ -197,8 +200,8 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
                (asw * asw <= 600.0) ? 1 : 0;
     }
     if (tid >= 96 && tid < 96 + kMaxRegions) G.code[tid - 96] = tid - 96 <= tab.n_thr ? tab.code[tid - 96] : 0;
-    if (tid >= 128 && tid < 130) {
-        const int b = tid - 128;
+    if (tid >= 80 && tid < 82) {
+        const int b = tid - 80;
         double sw[3], aw[3];
         for (int i = 0; i < 3; ++i) {
             const double w = G.wt[b].w[4 * i];
@@ -613,17 +616,29 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
             }
         } else {  // :131-134, :143-146: five decision times, then the outer Simpson level
             double F[5];
+            // First pass: a trial with a decision time at or before the onset, or below the comfortable range,
+            // is left to the complete evaluator, so the node loop below carries no per-node range logic.
+            if (DEFER && !(ax - G.tn[4] >= G.xt_lo[c.b])) {
+                *need = true;
+                return 0.0;
+            }
             // the decision is monotone in x_t: if both ends agree every node does
             const int code_hi = grid_code(G, xt_max);
             int j_last = 4;
-            while (j_last > 0 && !(ax - G.tn[j_last] > 0.0)) --j_last;
+            if (!DEFER)
+                while (j_last > 0 && !(ax - G.tn[j_last] > 0.0)) --j_last;
             const int code_lo = grid_code(G, ax - G.tn[j_last]);
             const bool uniform = code_hi == code_lo;
-#pragma unroll 1
+#pragma unroll(DEFER ? kUnrollJ : 1)
             for (int j = 0; j < 5; ++j) {
                 const double xt = ax - G.tn[j];
                 n_eval += over_z ? 5 : 1;
                 double val = 0.0;
+                if (DEFER) {
+                    const int code = uniform ? code_hi : grid_code(G, xt);
+                    const double q = q0 * G.rho[j];
+                    if (!*need) val = grid_inner<KMAX, DEFER>(G, c, xt, code, q, nm, tab, extra, need);
+                } else
                 if (xt > 0.0) {
                     const bool live = !(xt < G.xt_lo[c.b]);
                     if (!live) {
