@@ -48,7 +48,10 @@ constexpr int kTrialsPerBlock = 2048;  // one CTA reduces this many trials of on
 #endif
 constexpr int kTrialsPerBigBlock = HDDM_BIG_BLOCK;  // ... or this many when the grid is large enough anyway (launch_like)
 constexpr int kUnrollJ = HDDM_UNROLL_J;  // first pass: the five decision-time nodes of a trial are unrolled (5) or looped (1)
-constexpr int kLikeThreads = 256;
+#ifndef HDDM_LIKE_THREADS
+#define HDDM_LIKE_THREADS 256
+#endif
+constexpr int kLikeThreads = HDDM_LIKE_THREADS;  // >= 256 (build_gridset gives threads 0..255 a table entry each), multiple of 32
 
 enum LikeMode : int {
     kModeWienerLike = 0,  // src/wfpt.pyx:54-76   outlier mix, p==0 -> -inf

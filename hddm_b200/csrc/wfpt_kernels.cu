@@ -109,7 +109,8 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
             acc += log(d);
         }
     };
-    static_assert(kTrialsPerBigBlock / kLikeThreads <= 256, "mantissa product must stay finite (two passes)");
+    static_assert(kLikeThreads >= 256 && kLikeThreads % 32 == 0 && kTrialsPerBigBlock / kLikeThreads <= 256,
+                  "table build needs 256 threads; mantissa product must stay finite (two passes)");
     unsigned long long evals = 0;
     bool hit_zero = false;
     // One trial: load, evaluate, mix, accumulate.  Returns true when the trial was deferred.
@@ -147,7 +148,8 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         // Pass 1 evaluates the first 5 x 5 level, which settles almost every trial; the few that need more are
         // queued per warp (ballot order: deterministic) and pass 2 runs them through the complete evaluator with
         // full warps.  Keeps the slow paths' code, registers and local-memory arrays out of the hot loop.
-        __shared__ unsigned short queue[kLikeThreads / 32][kTrialsPerBigBlock / (kLikeThreads / 32)];
+        constexpr int kMaxRounds = (kTrialsPerBigBlock + kLikeThreads - 1) / kLikeThreads;
+        __shared__ unsigned short queue[kLikeThreads / 32][kMaxRounds * 32];
         static_assert(kTrialsPerBigBlock <= 65536, "queue entries are 16-bit offsets into the CTA's block of trials");
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         const int rounds = (int)((end - begin + kLikeThreads - 1) / kLikeThreads);
