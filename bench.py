@@ -330,13 +330,13 @@ def run_ours(args):
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
                          "frac": achieved / peak_tflops, "traffic": traffic, "traffic_source": traffic_src,
                          "algorithmic_bytes": int(8 * T + 72 * P + 8 * P * math.ceil(T / 2048.0)),
-                         "fp64_pipe_active_pct_ncu": 52.7,
+                         "fp64_pipe_active_pct_ncu": 57.5,
                          "kernel": "k_like_partial (+k_like_final, <0.1%)", "kernel_ms": k_ms,
                          "pdf_sv_per_eval": mean_pdfsv,
                          "accounting": "algorithmic FLOP = pdf_sv evals x 300 + 28 per eval (SURVEY.md 8d); "
                                        "peak = FP64 FMA probe measured in this run (MEASURED_PEAKS.json has no FP64 entry); "
-                                       "frac > 1 because the kernel executes ~24 FP64 instructions per pdf_sv where the "
-                                       "reference's sequence costs 300 FLOP; fp64_pipe_active_pct_ncu (profiles/r1_v6_summary.md) "
+                                       "frac > 1 because the kernel executes ~22 FP64 instructions per pdf_sv where the "
+                                       "reference's sequence costs 300 FLOP; fp64_pipe_active_pct_ncu (profiles/r1_v7_summary.md) "
                                        "is the executed-work utilisation"},
             "cpu_baseline": cpu,
             "clocks": clocks,
