@@ -120,6 +120,7 @@ struct alignas(16) GridSet {
     double a, sv, t, st, sz;  // st, sz after the 1e-3 snap of src/pdf.pxi:122-125
     double a_sq, inv_a_sq, sv_sq, qk;  // qk = -pi^2 / (2 a^2)
     double inv_zt, inv_st; // 1/(ub_z - lb_z) (1 when sz == 0), 1/(ub_t - lb_t)
+    double inv_a_sq_zt;    // inv_a_sq * inv_zt
     double zw, zw6, zw12;  // ub_z - lb_z, and that / 6, / 12 (src/integrate.pxi:99-100,137)
     double tw, tw6, tw12;  // ub_t - lb_t, / 6, / 12
     double raw[7];         // the set's v, sv, a, z, sz, t, st as given (for the out-of-range fallback)
@@ -158,6 +159,7 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
         G.zw6 = G.zw / 6.0; G.zw12 = G.zw / 12.0;
         G.tw = hi - lo; G.tw6 = G.tw / 6.0; G.tw12 = G.tw / 12.0;
         G.inv_zt = sz == 0 ? 1.0 : 1.0 / G.zw;
+        G.inv_a_sq_zt = (1.0 / a_sq) * G.inv_zt;
         G.inv_st = st == 0 ? 1.0 : 1.0 / (hi - lo);
         // Comfortable range of normalised time: [max(2^-20, w_0^2 / 1300), 128].  Lower end: the largest
         // small-time term exp(-w_0^2 / (2 tt)) stays above e^-650 (every term that underflows is then < 1e-25 of
@@ -398,9 +400,11 @@ __device__ __forceinline__ void grid_node(const GridSet<KMAX>& G, const GridTria
         r = rsqrt_fast(fma(G.sv_sq, xt, 1.0));
         d = 0.5 * (r * r);
     }
-    const double scale = (post * r) * (G.inv_a_sq * G.inv_zt);
-    double E = exp_tab<false>(fma(-c.v_sq, xt, c.c0) * d, G.etab);
-    f[0] = (p[0] * scale) * E;
+    const double scale = (post * r) * G.inv_a_sq_zt;
+    // scale rides on the exponential chain: one multiplication instead of one per start point (|log| of
+    // either factor is far below the exponent range: a^2 in [1e-100, 1e100], exponent in [-600, 300])
+    double E = exp_tab<false>(fma(-c.v_sq, xt, c.c0) * d, G.etab) * scale;
+    f[0] = p[0] * E;
     if (NW == 5) {
         double g = exp_tab<false>(c.dc0 * d, G.etab);
         const double r2 = exp_tab<false>(G.d2c[c.b] * d, G.etab);
@@ -408,7 +412,7 @@ __device__ __forceinline__ void grid_node(const GridSet<KMAX>& G, const GridTria
         for (int i = 1; i < NW; ++i) {
             E *= g;
             if (i < NW - 1) g *= r2;
-            f[i] = (p[i] * scale) * E;
+            f[i] = p[i] * E;
         }
     }
     if (!sv_zero) {  // exp(log(p) + ...) with p < 0 is NaN (src/pdf.pxi:102); never seen for err <= 1e-3
@@ -446,7 +450,7 @@ __device__ __noinline__ double grid_refine_z(const GridSet<KMAX>& G, const GridT
         r = rsqrt_fast(fma(G.sv_sq, xt, 1.0));
         d = 0.5 * (r * r);
     }
-    const double scale = (post * r) * (G.inv_a_sq * G.inv_zt);
+    const double scale = (post * r) * G.inv_a_sq_zt;
     const double vx = c.v_sq * xt;
     const double asv = G.a * G.sv, av2 = (2.0 * G.a) * c.v;
     const WTable<KMAX>& T = G.wt[c.b];
