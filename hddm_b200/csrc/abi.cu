@@ -273,8 +273,9 @@ int hddm_b200_fp64_peak(int iters, double* flops, float* ms)
 
 int hddm_b200_set_kernel(int which)
 {
-    if (which < 0 || which > 3)
-        return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto), 1 (generic), 2 (no grid) or 3 (grid, one pass)");
+    if (which < 0 || which > 4)
+        return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto), 1 (generic), 2 (no grid), 3 (grid, one pass) or "
+                                  "4 (grid, two passes in one launch)");
     std::lock_guard<std::mutex> lock(g_rt.mu);
     g_kernel_choice = which;
     return HDDM_OK;

@@ -47,6 +47,7 @@ constexpr int kTrialsPerBlock = 2048;  // one CTA reduces this many trials of on
 #define HDDM_UNROLL_J 5
 #endif
 constexpr int kTrialsPerBigBlock = HDDM_BIG_BLOCK;  // ... or this many when the grid is large enough anyway (launch_like)
+constexpr int kBlocksPerDeferredCta = 8;  // second launch of a split sweep: blocks of trials per CTA (one table build)
 constexpr int kUnrollJ = HDDM_UNROLL_J;  // first pass: the five decision-time nodes of a trial are unrolled (5) or looped (1)
 #ifndef HDDM_LIKE_THREADS
 #define HDDM_LIKE_THREADS 256
@@ -87,10 +88,16 @@ struct LikeArgs {
     double* partial;             // [n_sets * chunks]
     double* logp;                // [n_sets]
     unsigned long long* evals;   // device counter of pdf_sv evaluations (may be nullptr)
+    // Split two-pass sweep (set by launch_like): pass 1 leaves one bit per trial of its CTA's block
+    // ("needs the complete evaluator"), a second launch scores those trials and writes partial2.
+    unsigned int* defer_bits = nullptr;  // [n_sets * chunks][trials_per_block / 32]
+    double* partial2 = nullptr;          // [n_sets * chunks2]
+    int chunks2 = 0;                     // ceil(chunks / kBlocksPerDeferredCta)
 };
 
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream);
-extern int g_kernel_choice;  // 0 auto, 1 generic evaluator only, 2 no grid evaluator, 3 grid evaluator in one pass only
+extern int g_kernel_choice;  // 0 auto, 1 generic evaluator only, 2 no grid evaluator, 3 grid evaluator in one pass only,
+                             // 4 grid evaluator with both passes in one launch
 
 // par_sets == nullptr: one parameter set (par) over x[n] -> y[n].  Otherwise n_sets parameter sets, SoA
 // [9][n_sets]; set s (blockIdx.y) reads x + s * x_set_stride (0: one grid shared by all sets) and writes

@@ -200,8 +200,16 @@ __device__ __forceinline__ double simpson_walk(F&& f, Span cur, bool have_top, d
             fe = fe0;
             have_top = false;
         } else {
-            fd = f((cur.lo + c) / 2., (cur.ilo + ic) >> 1);
-            fe = f((c + cur.hi) / 2., (ic + cur.ihi) >> 1);
+            // one inlined copy of f serves both new abscissae (the walks run in the instruction-fetch-bound
+            // part of the kernels: code size matters more than the loop overhead)
+            fd = fe = 0.0;
+#pragma unroll 1
+            for (int side = 0; side < 2; ++side) {
+                const double at = side ? (c + cur.hi) / 2. : (cur.lo + c) / 2.;
+                const int pos = side ? (ic + cur.ihi) >> 1 : (cur.ilo + ic) >> 1;
+                const double val = f(at, pos);
+                if (side) fe = val; else fd = val;
+            }
         }
         const double left = (h / 12.0) * ((cur.f_lo + 4.0 * fd) + cur.f_mid);
         const double right = (h / 12.0) * ((cur.f_mid + 4.0 * fe) + cur.f_hi);

@@ -117,6 +117,7 @@ struct alignas(16) GridSet {
     double t_onset;        // t - st/2 with the raw st (the per-trial part of that test)
     double xt_lo[2], xt_hi;  // comfortable decision-time range per boundary, see build_gridset
     double xt_zero[2];       // below this decision time every start point's density is < 1e-230, see build_gridset
+    double mix_floor;        // w_outlier * p_outlier the caller adds to every density (0: none), see full_pdf_grid
     double a, sv, t, st, sz;  // st, sz after the 1e-3 snap of src/pdf.pxi:122-125
     double a_sq, inv_a_sq, sv_sq, qk;  // qk = -pi^2 / (2 a^2)
     double inv_zt, inv_st; // 1/(ub_z - lb_z) (1 when sz == 0), 1/(ub_t - lb_t)
@@ -137,7 +138,8 @@ __device__ __forceinline__ double xt_threshold(double thr, double a_sq)
 
 // Block-cooperative build.  par = v, sv, a, z, sz, t, st of the set (v unused).
 template <int KMAX>
-__device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par[7], const SeriesTable& tab)
+__device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par[7], const SeriesTable& tab,
+                                              double mix_floor = 0.0)
 {
     build_wtables<KMAX>(G.wt, par[3], par[4]);  // ends with __syncthreads()
     const int tid = threadIdx.x;
@@ -152,6 +154,7 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
         const double lo = par[5] - st / 2., hi = par[5] + st / 2.;
         const double c = (lo + hi) / 2.;
         G.tn[0] = lo; G.tn[4] = hi; G.tn[2] = c;
+        G.mix_floor = mix_floor;
         G.tn[1] = (lo + c) / 2.; G.tn[3] = (c + hi) / 2.;
         G.a = a; G.sv = sv; G.t = par[5]; G.st = st; G.sz = sz;
         G.a_sq = a_sq; G.inv_a_sq = 1.0 / a_sq; G.sv_sq = sv * sv; G.qk = -kPiSq / (2.0 * a_sq);
@@ -580,11 +583,12 @@ __device__ __noinline__ double grid_refine_t(const GridSet<KMAX>& G, const GridT
 // DEFER (first pass of the likelihood kernel): trials that need anything beyond the first 5 x 5 level --
 // inner or outer refinement, or the out-of-range fallback -- set *need and return 0 without counting
 // evaluations; the kernel re-runs them, compacted, through full_pdf_grid_slow.
-template <int KMAX, bool DEFER = false>
+template <int KMAX, int STAGE = 0>
 __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSet<KMAX>& G,
                                                 const Numerics& nm, const SeriesTable* tab,
                                                 unsigned long long& evals, bool* need = nullptr)
 {
+    constexpr bool DEFER = STAGE == 1;
     const double ax = fabs(x);
     if (!G.support || (ax - G.t_onset) < 0) return 0.0;  // src/pdf.pxi:111-113
     GridTrial c;
@@ -651,7 +655,11 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
                     }
                     const int code = uniform ? code_hi : grid_code(G, xt);
                     const double q = q0 * G.rho[j];
-                    if (ok && live && !(DEFER && *need)) val = grid_inner<KMAX, DEFER>(G, c, xt, code, q, nm, tab, extra, need);
+                    // (second pass: the out-of-line copy that grid_refine_t calls anyway -- one node evaluator
+                    // in the instruction cache instead of two)
+                    if (ok && live && !(DEFER && *need))
+                        val = STAGE == 2 ? grid_inner_ool<KMAX>(G, c, xt, code, q, nm, tab, extra)
+                                         : grid_inner<KMAX, DEFER>(G, c, xt, code, q, nm, tab, extra, need);
                 }
                 F[j] = val * G.inv_st;
             }
@@ -672,12 +680,15 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
                     ok = !bad;
                     tiny |= tiny2;
                 }
-                if (tiny && !(fabs(out) > 1e-150)) ok = false;
+                // Negligible nodes were taken as 0: fine unless the whole result is that small too -- and even
+                // then when the caller's outlier term swamps it (fl(out (1 - p) + w p) = w p for any out <=
+                // 1e-150 once w p > 1e-120; the recursion tree is the minimal one either way).
+                if (tiny && !(fabs(out) > 1e-150) && !(fabs(out) <= 1e-150 && G.mix_floor > 1e-120)) ok = false;
             }
         }
     }
     if (!ok) {
-        if (DEFER) {
+        if (STAGE != 0) {  // stage 1: to the complete evaluator; stage 2: to the out-of-range fallback
             *need = true;
             return 0.0;
         }
@@ -687,12 +698,14 @@ __device__ __forceinline__ double full_pdf_grid(double x, double v, const GridSe
     return out;
 }
 
-// Second pass: the complete evaluator, one out-of-line copy.
+// Second pass: the complete evaluator, one out-of-line copy.  A trial outside the comfortable range sets
+// *fallback instead of walking through the v2 evaluator on its own while the rest of its warp idles: the
+// kernel collects those and runs grid_fallback over them with full warps (third stage).
 template <int KMAX>
 __device__ __noinline__ double full_pdf_grid_slow(double x, double v, const GridSet<KMAX>& G, const Numerics& nm,
-                                                  const SeriesTable* tab, unsigned long long& evals)
+                                                  const SeriesTable* tab, unsigned long long& evals, bool* fallback)
 {
-    return full_pdf_grid<KMAX, false>(x, v, G, nm, tab, evals);
+    return full_pdf_grid<KMAX, 2>(x, v, G, nm, tab, evals, fallback);
 }
 
 }  // namespace hddm

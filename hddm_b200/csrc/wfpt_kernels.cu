@@ -44,10 +44,17 @@ __device__ __forceinline__ double load_par(const LikeArgs& a, int k, int64_t p, 
 // GRID: additionally sv, a, t, st uniform per set -> the v3 grid evaluator of wfpt_grid.cuh.
 // TWO_PASS (GRID only): see the trial loop.  Pays off when a thread owns several trials (long segments);
 // short observed nodes (one round per thread) take the one-pass flavour, whose critical path is shorter.
-template <int KMAX, bool GRID, bool TWO_PASS = false>
-__global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
+// PASSES (GRID only): 0 one pass; 1 two passes in one launch; 2 / 3 the two passes as separate launches
+// (kSplitFirst leaves a bit per deferred trial in a.defer_bits, kSplitSecond scores those trials).
+enum : int { kOnePass = 0, kTwoPass = 1, kSplitFirst = 2, kSplitSecond = 3 };
+#ifndef HDDM_SECOND_MIN_BLOCKS
+#define HDDM_SECOND_MIN_BLOCKS 2
+#endif
+template <int KMAX, bool GRID, int PASSES = kOnePass>
+__global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSecond ? HDDM_SECOND_MIN_BLOCKS : 2) : 1)
     k_like_partial(const __grid_constant__ LikeArgs a)
 {
+    constexpr bool TWO_PASS = PASSES != kOnePass;
     constexpr int KT = KMAX > 0 ? KMAX : 1;
     __shared__ GridSet<KT> gs;
     WTable<KT>* wt = gs.wt;
@@ -56,19 +63,41 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     const int64_t node = a.set_node ? a.set_node[p] : p;
     const int64_t lo = a.seg ? a.seg[node] : 0;
     const int64_t hi = a.seg ? a.seg[node + 1] : a.n;
-    const int64_t begin = lo + (int64_t)chunk * a.trials_per_block;
+    // kSplitSecond: the CTA covers kBlocksPerDeferredCta consecutive blocks of the set's trials
+    constexpr int kSpan = PASSES == kSplitSecond ? kBlocksPerDeferredCta : 1;
+    const int64_t begin = lo + (int64_t)chunk * kSpan * a.trials_per_block;
+    double* const slot = PASSES == kSplitSecond ? a.partial2 + p * a.chunks2 + chunk : a.partial + p * a.chunks + chunk;
+    const bool single = PASSES < kSplitFirst && a.chunks == 1;  // this CTA's sum IS the set's log-likelihood
     const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
     // src/wfpt.pyx:50-51,63-64: p_outlier outside [0,1] -> -inf before any trial is looked at
     const bool multi = a.mode == kModeMulti || a.mode == kModeMultiRL;  // no range / zero guards
     const bool range_ok = multi || ((p_out >= 0) & (p_out <= 1));
     if (begin >= hi || !range_ok) {  // (ragged batch: shorter sets have empty trailing chunks)
         if (threadIdx.x == 0) {
-            a.partial[p * a.chunks + chunk] = range_ok ? 0.0 : -INFINITY;
-            if (a.chunks == 1) a.logp[p] = range_ok ? 0.0 : -INFINITY;  // single chunk: no k_like_final
+            // (kSplitSecond adds nothing: the first launch's partial already carries the -inf)
+            *slot = (range_ok || PASSES == kSplitSecond) ? 0.0 : -INFINITY;
+            if (single) a.logp[p] = range_ok ? 0.0 : -INFINITY;  // single chunk: no k_like_final
         }
         return;
     }
-    const int64_t end = begin + a.trials_per_block < hi ? begin + a.trials_per_block : hi;
+    const int64_t span = (int64_t)kSpan * a.trials_per_block;
+    const int64_t end = begin + span < hi ? begin + span : hi;
+    const int words_per_block = a.trials_per_block / 32;
+    if (PASSES == kSplitSecond) {  // nothing deferred in this CTA's blocks: leave before the table build
+        unsigned int any = 0;
+        for (int c = 0; c < kSpan; ++c) {
+            const int64_t b0 = begin + (int64_t)c * a.trials_per_block;
+            if (b0 >= end) break;
+            const int64_t cnt = end - b0 < a.trials_per_block ? end - b0 : a.trials_per_block;
+            const int words = (int)((cnt + kLikeThreads - 1) / kLikeThreads) * (kLikeThreads / 32);
+            const unsigned int* w = a.defer_bits + (p * a.chunks + (int64_t)chunk * kSpan + c) * words_per_block;
+            for (int k = threadIdx.x; k < words; k += kLikeThreads) any |= w[k];
+        }
+        if (!__syncthreads_or(any != 0)) {
+            if (threadIdx.x == 0) *slot = 0.0;
+            return;
+        }
+    }
 
     // Set-uniform parameters are read once; per-trial ones (trial_stride != 0) inside the loop.
     double par[7];
@@ -80,16 +109,21 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     }
 
     if (GRID)
-        build_gridset<KT>(gs, par, a.tab);
+        build_gridset<KT>(gs, par, a.tab,
+                          (a.mode != kModeContaminant && p_out >= 0 && p_out <= 1) ? w_out * p_out : 0.0);
     else if (KMAX > 0)
         build_wtables<KT>(wt, par[3], par[4]);
 
-    // pass 1 (GRID): need = the trial is deferred to pass 2; otherwise need stays false
-    auto density = [&](double x, unsigned long long& ev, bool first_pass, bool* need) {
-        if (GRID && TWO_PASS)
-            return first_pass ? full_pdf_grid<KT, true>(x, par[0], gs, a.nm, &a.tab, ev, need)
-                              : full_pdf_grid_slow<KT>(x, par[0], gs, a.nm, &a.tab, ev);
-        if (GRID) return full_pdf_grid<KT, false>(x, par[0], gs, a.nm, &a.tab, ev);
+    // Stages of the two-pass flavours (GRID): 0 = first pass, the first 5 x 5 level only (*need: the trial goes
+    // to stage 1); 1 = the complete grid evaluator (*need: out of its range, goes to stage 2); 2 = the v2
+    // evaluator.  The one-pass flavours have stage 0 only, and it is complete.
+    auto density = [&](double x, unsigned long long& ev, int stage, bool* need) {
+        if (GRID && TWO_PASS) {
+            if (stage == 0) return full_pdf_grid<KT, 1>(x, par[0], gs, a.nm, &a.tab, ev, need);
+            if (stage == 1) return full_pdf_grid_slow<KT>(x, par[0], gs, a.nm, &a.tab, ev, need);
+            return grid_fallback<KT>(x, par[0], gs, a.nm, &a.tab, ev);
+        }
+        if (GRID) return full_pdf_grid<KT, 0>(x, par[0], gs, a.nm, &a.tab, ev);
         if (KMAX > 0)
             return full_pdf_fast<(KMAX > 0 ? KMAX : 1)>(x, par[0], par[1], par[2], par[3], par[4], par[5],
                                                         par[6], a.nm, &a.tab, wt, ev);
@@ -114,7 +148,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     unsigned long long evals = 0;
     bool hit_zero = false;
     // One trial: load, evaluate, mix, accumulate.  Returns true when the trial was deferred.
-    auto score = [&](int64_t i, bool first_pass) {
+    auto score = [&](int64_t i, int stage) {
         const double x = __ldg(a.x + i);
         if (per_trial) {
 #pragma unroll
@@ -125,7 +159,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         double d;
         if (multi) {
             if (a.mode == kModeMultiRL || fabs(x) != 999.) {  // src/wfpt.pyx:261-266
-                d = density(x, evals, first_pass, &need);
+                d = density(x, evals, stage, &need);
                 d = d * (1 - p_out) + w_out * p_out;
             } else if (x == 999.) {  // :267-268
                 d = prob_ub(par[0], GRID ? gs.raw[2] : par[2], GRID ? gs.raw[3] : par[3]);
@@ -135,7 +169,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
             if (!need) add_log(d);
         } else {
             if (a.cont && a.cont[i] != 0) return false;  // src/wfpt.pyx:374; :134 (first trial of a condition)
-            d = density(x, evals, first_pass, &need);
+            d = density(x, evals, stage, &need);
             if (!need) {
                 d = d * (1 - p_out) + w_out * p_out;  // src/wfpt.pyx:70 (contaminant: p_out = 0)
                 hit_zero |= (d == 0);                 // :71-72, :377-379
@@ -151,20 +185,66 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         constexpr int kMaxRounds = (kTrialsPerBigBlock + kLikeThreads - 1) / kLikeThreads;
         __shared__ unsigned short queue[kLikeThreads / 32][kMaxRounds * 32];
         static_assert(kTrialsPerBigBlock <= 65536, "queue entries are 16-bit offsets into the CTA's block of trials");
+        static_assert(kBlocksPerDeferredCta * kTrialsPerBigBlock <= 65536, "16-bit offsets (second launch)");
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        const int rounds = (int)((end - begin + kLikeThreads - 1) / kLikeThreads);
         int queued = 0;  // warp-uniform
-        for (int r = 0; r < rounds; ++r) {
-            const int off = r * kLikeThreads + threadIdx.x;
-            const bool need = (begin + off < end) ? score(begin + off, true) : false;
-            const unsigned int votes = __ballot_sync(0xffffffffu, need);
-            if (need) queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] = (unsigned short)off;
-            queued += __popc(votes);
+        // Stage 1 over the warp's queue, 32 trials at a time; the few that need stage 2 are compacted into the
+        // part of the queue already consumed (ballot order again) and run last.  Returns the new fill (0).
+        auto run_queue = [&](int n_queued) {
+            __syncwarp();
+            int n_fallback = 0;
+            for (int k0 = 0; k0 < n_queued; k0 += 32) {
+                const int k = k0 + lane;
+                const unsigned short off = k < n_queued ? queue[warp][k] : 0;
+                const bool need = k < n_queued ? score(begin + off, 1) : false;
+                const unsigned int votes = __ballot_sync(0xffffffffu, need);
+                if (need) queue[warp][n_fallback + __popc(votes & ((1u << lane) - 1u))] = off;
+                n_fallback += __popc(votes);
+                __syncwarp();
+            }
+            for (int k = lane; k < n_fallback; k += 32) score(begin + queue[warp][k], 2);
+            __syncwarp();
+            return 0;
+        };
+        if (PASSES == kSplitSecond) {
+            // Second launch: the deferred trials of this CTA's blocks, compacted per warp in the same (block,
+            // round, lane) order as the one-launch flavour queues them, scored whenever a queue is nearly full.
+            auto drain = [&]() { queued = run_queue(queued); };
+            for (int c = 0; c < kSpan; ++c) {
+                const int64_t b0 = begin + (int64_t)c * a.trials_per_block;
+                if (b0 >= end) break;
+                const int64_t cnt = end - b0 < a.trials_per_block ? end - b0 : a.trials_per_block;
+                const int rounds = (int)((cnt + kLikeThreads - 1) / kLikeThreads);
+                const unsigned int* w = a.defer_bits + (p * a.chunks + (int64_t)chunk * kSpan + c) * words_per_block;
+                for (int r = 0; r < rounds; ++r) {
+                    const unsigned int votes = w[r * (kLikeThreads / 32) + warp];
+                    if ((votes >> lane) & 1u)
+                        queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] =
+                            (unsigned short)(c * a.trials_per_block + r * kLikeThreads + threadIdx.x);
+                    queued += __popc(votes);
+                    if (queued > kMaxRounds * 32 - 32) drain();
+                }
+            }
+            drain();
+        } else {
+            const int rounds = (int)((end - begin + kLikeThreads - 1) / kLikeThreads);
+            unsigned int* const bits = PASSES == kSplitFirst
+                                           ? a.defer_bits + (p * a.chunks + chunk) * words_per_block : nullptr;
+            for (int r = 0; r < rounds; ++r) {
+                const int off = r * kLikeThreads + threadIdx.x;
+                const bool need = (begin + off < end) ? score(begin + off, 0) : false;
+                const unsigned int votes = __ballot_sync(0xffffffffu, need);
+                if (PASSES == kSplitFirst) {
+                    if (lane == 0) bits[r * (kLikeThreads / 32) + warp] = votes;
+                } else {
+                    if (need) queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] = (unsigned short)off;
+                    queued += __popc(votes);
+                }
+            }
+            if (PASSES == kTwoPass) run_queue(queued);
         }
-        __syncwarp();
-        for (int k = lane; k < queued; k += 32) score(begin + queue[warp][k], false);
     } else {
-        for (int64_t i = begin + threadIdx.x; i < end; i += kLikeThreads) score(i, true);
+        for (int64_t i = begin + threadIdx.x; i < end; i += kLikeThreads) score(i, 0);
     }
     acc += fma((double)expo, 0.693147180559945309417, log(mant));
 
@@ -182,8 +262,8 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
 #pragma unroll
         for (int w = 0; w < kLikeThreads / 32; ++w) s += warp_part[w];
         if (!multi && any_zero) s = -INFINITY;
-        a.partial[p * a.chunks + chunk] = s;
-        if (a.chunks == 1) a.logp[p] = s;  // single chunk: this IS the set's log-likelihood (no k_like_final)
+        *slot = s;
+        if (single) a.logp[p] = s;  // single chunk: this IS the set's log-likelihood (no k_like_final)
     }
 }
 
@@ -201,6 +281,16 @@ __global__ void __launch_bounds__(128) k_like_final(const LikeArgs a)
         s += v;
     }
     s = warp_sum(s);
+    if (a.partial2) {  // split sweep: the deferred trials' sums, after the first launch's
+        const double* row2 = a.partial2 + p * a.chunks2;
+        double s2 = 0.0;
+        for (int c = lane; c < a.chunks2; c += 32) {
+            const double v = row2[c];
+            neg_inf |= (v == -INFINITY);
+            s2 += v;
+        }
+        s += warp_sum(s2);
+    }
     neg_inf = __any_sync(0xffffffffu, neg_inf);
     // wiener_like returns -inf at the FIRST zero density whatever the running sum holds
     // (src/wfpt.pyx:71-72): a -inf partial (only produced by that rule) overrides NaN.
@@ -236,12 +326,50 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     // two passes when threads own several trials each (segments longer than two rounds of the CTA)
     const int64_t longest = a.max_seg_len > 0 ? a.max_seg_len : a.n;
     const bool two_pass = gridk && g_kernel_choice != 3 && longest > 2 * kLikeThreads;
+    // Big sweeps run the two passes as two launches: the first-pass code and the complete evaluator
+    // together overflow the instruction cache when warps of one SM are in different passes (onset-mixed
+    // data spent half of its cycles waiting for instructions).  One bit per trial travels between them.
+    unsigned int* bits = nullptr;
+    if (two_pass && b.trials_per_block == kTrialsPerBigBlock && g_kernel_choice != 4) {
+        static bool pool_ready = false;
+        if (!pool_ready) {  // keep freed blocks in the stream-ordered pool instead of returning them to the OS
+            int dev = 0;
+            cudaMemPool_t pool;
+            unsigned long long keep = ~0ull;
+            if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess)
+                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            pool_ready = true;
+        }
+        const size_t bytes = (size_t)b.n_sets * b.chunks * (kTrialsPerBigBlock / 32) * sizeof(unsigned int);
+        if (cudaMallocAsync((void**)&bits, bytes, stream) != cudaSuccess) {
+            (void)cudaGetLastError();  // no room for the bitmap: the one-launch flavour needs none
+            bits = nullptr;
+        }
+    }
+    if (bits) {
+        b.defer_bits = bits;
+        b.chunks2 = (b.chunks + kBlocksPerDeferredCta - 1) / kBlocksPerDeferredCta;
+        b.partial2 = b.partial + (size_t)b.n_sets * b.chunks;  // callers sized partial for 2048-trial chunks
+        const dim3 grid2((unsigned)b.n_sets, (unsigned)b.chunks2);
+        if (b.tab.max_large_k <= 4) {
+            k_like_partial<4, true, kSplitFirst><<<grid, kLikeThreads, 0, stream>>>(b);
+            k_like_partial<4, true, kSplitSecond><<<grid2, kLikeThreads, 0, stream>>>(b);
+        } else {
+            k_like_partial<8, true, kSplitFirst><<<grid, kLikeThreads, 0, stream>>>(b);
+            k_like_partial<8, true, kSplitSecond><<<grid2, kLikeThreads, 0, stream>>>(b);
+        }
+        const int sets_per_block = 128 / 32;
+        k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(b);
+        const cudaError_t e = cudaGetLastError();
+        cudaFreeAsync(bits, stream);
+        return e;
+    }
     if (two_pass && b.tab.max_large_k <= 4)
-        k_like_partial<4, true, true><<<grid, kLikeThreads, 0, stream>>>(b);
+        k_like_partial<4, true, kTwoPass><<<grid, kLikeThreads, 0, stream>>>(b);
     else if (two_pass)
-        k_like_partial<8, true, true><<<grid, kLikeThreads, 0, stream>>>(b);
+        k_like_partial<8, true, kTwoPass><<<grid, kLikeThreads, 0, stream>>>(b);
     else if (gridk && b.tab.max_large_k <= 4)
-        k_like_partial<4, true><<<grid, kLikeThreads, 0, stream>>>(b);
+        k_like_partial<4, true, kOnePass><<<grid, kLikeThreads, 0, stream>>>(b);
     else if (gridk)
         k_like_partial<8, true><<<grid, kLikeThreads, 0, stream>>>(b);
     else if (fast && b.tab.max_large_k <= 4)

@@ -51,8 +51,10 @@ int hddm_b200_fp64_peak(int iters, double *flops, float *ms);
 /* Evaluator selection for the likelihood kernels: 0 = per launch (the grid evaluator when every
  * parameter but the drift is uniform per set and integration is adaptive; else the table-driven walk
  * when z and sz are uniform per set; else the generic one; the grid evaluator runs in two passes when
- * segments are longer than 512 trials), 1 = always the generic evaluator, 2 = never the grid evaluator,
- * 3 = grid evaluator in one pass only.  All run on the GPU; this exists for A/B parity tests and profiling. */
+ * segments are longer than 512 trials, and as two launches when the sweep has thousands of 8192-trial
+ * blocks), 1 = always the generic evaluator, 2 = never the grid evaluator, 3 = grid evaluator in one pass
+ * only, 4 = its two passes always in one launch.  All run on the GPU; this exists for A/B parity tests
+ * and profiling. */
 int hddm_b200_set_kernel(int which);
 /* Trial layout: 1 (default) = entry points whose result is a sum over trials with set-uniform
  * parameters (wiener_like, wiener_like_batch, the trials handle) evaluate the trials ordered by |rt|

@@ -23,14 +23,18 @@ def W(gpu):
     return wfpt
 
 
-@pytest.fixture(autouse=True, params=["auto", "onepass", "walk", "generic"])
+KERNEL_CHOICE = {"auto": 0, "generic": 1, "walk": 2, "onepass": 3, "fused": 4}
+
+
+@pytest.fixture(autouse=True, params=["auto", "onepass", "fused", "walk", "generic"])
 def evaluator(request, gpu):
-    """Every parity test runs four times: with the per-launch choice (the grid evaluator of
-    csrc/wfpt_grid.cuh where it applies, in two passes for long segments), with the grid evaluator forced
-    into one pass, with the grid evaluator disabled (table-driven walk of
-    csrc/wfpt_fast.cuh) and with the generic evaluator forced.  All three are CUDA."""
+    """Every parity test runs five times: with the per-launch choice (the grid evaluator of
+    csrc/wfpt_grid.cuh where it applies, in two passes for long segments, as two launches for big sweeps),
+    with the grid evaluator forced into one pass, with its two passes forced into one launch, with the grid
+    evaluator disabled (table-driven walk of csrc/wfpt_fast.cuh) and with the generic evaluator forced.
+    All of them are CUDA."""
     from hddm_b200 import _lib
-    _lib.check(_lib.lib().hddm_b200_set_kernel({"auto": 0, "generic": 1, "walk": 2, "onepass": 3}[request.param]))
+    _lib.check(_lib.lib().hddm_b200_set_kernel(KERNEL_CHOICE[request.param]))
     yield request.param
     _lib.check(_lib.lib().hddm_b200_set_kernel(0))
 
@@ -346,6 +350,30 @@ def test_full_size_properties(W, O):
     for p in (3, 500, 1023):
         want = O.wiener_like(x, *params[:7, p], p_outlier=0.05, w_outlier=0.1, **HDDM)
         assert_parity(a[p], want, RTOL_SUM, what="subsample set %d" % p)
+
+
+@pytest.mark.parametrize("onset", [0.70, 0.30])
+def test_split_sweep_equals_one_launch(W, O, evaluator, onset):
+    """A sweep big enough for the two-launch flavour (>= 2368 CTAs of 8192 trials): same log-likelihoods
+    (to summation rounding: the deferred trials are added in another order) and the same pdf_sv count as the
+    one-launch and one-pass flavours, oracle parity on a subsample of sets."""
+    from hddm_b200 import _lib
+    if evaluator != "auto":
+        pytest.skip("compares the grid evaluator's flavours itself")
+    x, params = sweep_inputs(16500, 800, onset=onset)
+    got = {}
+    for name in ("auto", "fused", "onepass"):
+        _lib.check(_lib.lib().hddm_b200_set_kernel(KERNEL_CHOICE[name]))
+        got[name] = W.wiener_like_batch(x, params, return_evals=True, **HDDM)
+    _lib.check(_lib.lib().hddm_b200_set_kernel(0))
+    again = W.wiener_like_batch(x, params, **HDDM)
+    assert np.array_equal(again, got["auto"][0])                 # deterministic
+    for name in ("fused", "onepass"):
+        assert got[name][1] == got["auto"][1], name              # identical decisions
+        assert_parity(got["auto"][0], got[name][0], 1e-12, what="split vs " + name)
+    for p in (0, 411, 799):
+        want = O.wiener_like(x, *params[:7, p], p_outlier=params[7, p], w_outlier=params[8, p], **HDDM)
+        assert_parity(got["auto"][0][p], want, RTOL_SUM, what="split sweep, set %d" % p)
 
 
 def test_nodes_batch_vs_oracle(W, O):
