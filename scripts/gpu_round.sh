@@ -1,7 +1,7 @@
 # One GPU round: parity tests, smoke, bench lines (S-A with CPU baseline, S-B, reference arm), ncu launch list and
 # full captures (each after the same command exited 0 without ncu).  TAG names the outputs under gpurun_out/.
 set -x
-TAG=${TAG:-r1_v4}
+TAG=${TAG:-r1_v8}
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${TAG}_pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1
@@ -10,8 +10,11 @@ timeout 600 python bench.py --sweep B --no-cpu > gpurun_out/${TAG}_bench_sweepB.
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_reference.json 2>> gpurun_out/${TAG}_bench.err
 timeout 300 python bench.py --steps 1 --warmup 3 --trials 20000 --sets 2000 --no-cpu > gpurun_out/${TAG}_bench_small.json 2>&1 && \
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 1 --warmup 3 --trials 20000 --sets 2000 --no-cpu > gpurun_out/${TAG}_ncu_l.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 3 -c 1 -o gpurun_out/${TAG}_like -f python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/${TAG}_ncu_f.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 3 -c 1 -o gpurun_out/${TAG}_like_B -f python bench.py --steps 1 --warmup 3 --no-cpu --sweep B --trials 20000 --sets 2000 > gpurun_out/${TAG}_ncu_fB.log 2>&1
+# (a big sweep is two launches of k_like_partial per step: first pass, then the deferred trials)
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 4 -c 1 -o gpurun_out/${TAG}_like -f python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/${TAG}_ncu_f.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 5 -c 1 -o gpurun_out/${TAG}_like_second -f python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/${TAG}_ncu_f2.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 4 -c 1 -o gpurun_out/${TAG}_like_B -f python bench.py --steps 1 --warmup 3 --no-cpu --sweep B --trials 20000 --sets 2000 > gpurun_out/${TAG}_ncu_fB.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 5 -c 1 -o gpurun_out/${TAG}_like_B_second -f python bench.py --steps 1 --warmup 3 --no-cpu --sweep B --trials 20000 --sets 2000 > gpurun_out/${TAG}_ncu_fB2.log 2>&1
 ls -la gpurun_out | tail -20
 # large-trial corner (1e7 trials, few sets): achieved HBM traffic of the likelihood kernel
-timeout 900 ncu --set full --clock-control none -k regex:k_like_partial -s 3 -c 1 -o gpurun_out/${TAG}_like_T1e7 -f python bench.py --steps 1 --warmup 3 --no-cpu --trials 10000000 --sets 148 > gpurun_out/${TAG}_ncu_fT.log 2>&1
+timeout 900 ncu --set full --clock-control none -k regex:k_like_partial -s 4 -c 1 -o gpurun_out/${TAG}_like_T1e7 -f python bench.py --steps 1 --warmup 3 --no-cpu --trials 10000000 --sets 148 > gpurun_out/${TAG}_ncu_fT.log 2>&1
