@@ -330,15 +330,17 @@ def run_ours(args):
             "gpu_launches": (3 if (T > 6144 and P * math.ceil(T / 8192.0) >= 2368) else 2) * args.steps,
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
                          "frac": achieved / peak_tflops, "traffic": traffic, "traffic_source": traffic_src,
-                         "algorithmic_bytes": int(8 * T + 72 * P + 8 * P * math.ceil(T / 2048.0)),
-                         "fp64_pipe_active_pct_ncu": 57.5,
+                         "algorithmic_bytes": int(8 * T + 72 * P + 8 * P * math.ceil(T / 2048.0) +
+                                                  (2 * 1024 * P * math.ceil(T / 8192.0)
+                                                   if (T > 6144 and P * math.ceil(T / 8192.0) >= 2368) else 0)),
+                         "fp64_pipe_active_pct_ncu": 57.0,
                          "kernel": "k_like_partial: first pass + deferred-trial pass (S-A: 97 % + 3 %) + k_like_final (<0.1 %)",
                          "kernel_ms": k_ms,
                          "pdf_sv_per_eval": mean_pdfsv,
                          "accounting": "algorithmic FLOP = pdf_sv evals x 300 + 28 per eval (SURVEY.md 8d); "
                                        "peak = FP64 FMA probe measured in this run (MEASURED_PEAKS.json has no FP64 entry); "
                                        "frac > 1 because the kernel executes ~22 FP64 instructions per pdf_sv where the "
-                                       "reference's sequence costs 300 FLOP; fp64_pipe_active_pct_ncu (profiles/r1_v7_summary.md) "
+                                       "reference's sequence costs 300 FLOP; fp64_pipe_active_pct_ncu (profiles/r1_v8_summary.md) "
                                        "is the executed-work utilisation"},
             "cpu_baseline": cpu,
             "clocks": clocks,

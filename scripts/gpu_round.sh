@@ -18,3 +18,13 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_li
 ls -la gpurun_out | tail -20
 # large-trial corner (1e7 trials, few sets): achieved HBM traffic of the likelihood kernel
 timeout 900 ncu --set full --clock-control none -k regex:k_like_partial -s 4 -c 1 -o gpurun_out/${TAG}_like_T1e7 -f python bench.py --steps 1 --warmup 3 --no-cpu --trials 10000000 --sets 148 > gpurun_out/${TAG}_ncu_fT.log 2>&1
+# gpurun brings back at most 64 MiB: keep the headline first-pass report, reduce the others to text on the box
+for r in like_second like_B like_B_second like_T1e7; do
+  f=gpurun_out/${TAG}_$r.ncu-rep
+  [ -f $f ] || continue
+  ncu -i $f --page details > gpurun_out/${TAG}_ncu_details_$r.txt 2>&1
+  python profiles/ncu_digest.py $f > gpurun_out/${TAG}_ncu_digest_$r.txt 2>&1
+  ncu -i $f --page raw --csv 2>/dev/null | gzip > gpurun_out/${TAG}_ncu_raw_$r.csv.gz
+  rm -f $f
+done
+du -sh gpurun_out
