@@ -93,6 +93,7 @@ struct LikeArgs {
     unsigned int* defer_bits = nullptr;  // [n_sets * chunks][trials_per_block / 32]
     double* partial2 = nullptr;          // [n_sets * chunks2]
     int chunks2 = 0;                     // ceil(chunks / kBlocksPerDeferredCta)
+    const void* set_tables = nullptr;    // [n_sets] GridSet tables built once per set by k_build_tables (else per CTA)
 };
 
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream);

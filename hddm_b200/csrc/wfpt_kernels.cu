@@ -108,7 +108,13 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         per_trial |= a.trial_stride[k] != 0;
     }
 
-    if (GRID)
+    if (GRID && a.set_tables) {  // split sweep: the set's tables were built once, by k_build_tables
+        static_assert(sizeof(GridSet<KT>) % sizeof(uint4) == 0, "tables are copied 16 bytes at a time");
+        const uint4* src = reinterpret_cast<const uint4*>(a.set_tables) + p * (sizeof(GridSet<KT>) / sizeof(uint4));
+        uint4* dst = reinterpret_cast<uint4*>(&gs);
+        for (int k = threadIdx.x; k < (int)(sizeof(GridSet<KT>) / sizeof(uint4)); k += kLikeThreads) dst[k] = __ldg(src + k);
+        __syncthreads();
+    } else if (GRID)
         build_gridset<KT>(gs, par, a.tab,
                           (a.mode != kModeContaminant && p_out >= 0 && p_out <= 1) ? w_out * p_out : 0.0);
     else if (KMAX > 0)
@@ -267,6 +273,25 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
     }
 }
 
+// The per-set tables of the grid evaluator, once per set (split sweeps: every CTA of the set, in both
+// launches, copies them instead of rebuilding them).
+template <int KMAX>
+__global__ void __launch_bounds__(kLikeThreads) k_build_tables(const __grid_constant__ LikeArgs a, void* out)
+{
+    __shared__ GridSet<KMAX> gs;
+    const int64_t p = blockIdx.x;
+    double par[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) par[k] = load_par(a, k, p, 0);
+    const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
+    build_gridset<KMAX>(gs, par, a.tab,
+                        (a.mode != kModeContaminant && p_out >= 0 && p_out <= 1) ? w_out * p_out : 0.0);
+    __syncthreads();
+    const uint4* src = reinterpret_cast<const uint4*>(&gs);
+    uint4* dst = reinterpret_cast<uint4*>(out) + p * (sizeof(GridSet<KMAX>) / sizeof(uint4));
+    for (int k = threadIdx.x; k < (int)(sizeof(GridSet<KMAX>) / sizeof(uint4)); k += kLikeThreads) dst[k] = src[k];
+}
+
 __global__ void __launch_bounds__(128) k_like_final(const LikeArgs a)
 {
     const int64_t p = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -330,6 +355,7 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     // together overflow the instruction cache when warps of one SM are in different passes (onset-mixed
     // data spent half of its cycles waiting for instructions).  One bit per trial travels between them.
     unsigned int* bits = nullptr;
+    size_t map_bytes = 0;
     if (two_pass && b.trials_per_block == kTrialsPerBigBlock && g_kernel_choice != 4) {
         static bool pool_ready = false;
         if (!pool_ready) {  // keep freed blocks in the stream-ordered pool instead of returning them to the OS
@@ -340,8 +366,9 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
                 cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
             pool_ready = true;
         }
-        const size_t bytes = (size_t)b.n_sets * b.chunks * (kTrialsPerBigBlock / 32) * sizeof(unsigned int);
-        if (cudaMallocAsync((void**)&bits, bytes, stream) != cudaSuccess) {
+        map_bytes = (size_t)b.n_sets * b.chunks * (kTrialsPerBigBlock / 32) * sizeof(unsigned int);
+        const size_t table_bytes = (size_t)b.n_sets * (b.tab.max_large_k <= 4 ? sizeof(GridSet<4>) : sizeof(GridSet<8>));
+        if (cudaMallocAsync((void**)&bits, map_bytes + table_bytes, stream) != cudaSuccess) {
             (void)cudaGetLastError();  // no room for the bitmap: the one-launch flavour needs none
             bits = nullptr;
         }
@@ -351,6 +378,12 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
         b.chunks2 = (b.chunks + kBlocksPerDeferredCta - 1) / kBlocksPerDeferredCta;
         b.partial2 = b.partial + (size_t)b.n_sets * b.chunks;  // callers sized partial for 2048-trial chunks
         const dim3 grid2((unsigned)b.n_sets, (unsigned)b.chunks2);
+        void* tables = reinterpret_cast<char*>(bits) + map_bytes;  // map_bytes is a multiple of 1024
+        if (b.tab.max_large_k <= 4)
+            k_build_tables<4><<<(unsigned)b.n_sets, kLikeThreads, 0, stream>>>(b, tables);
+        else
+            k_build_tables<8><<<(unsigned)b.n_sets, kLikeThreads, 0, stream>>>(b, tables);
+        b.set_tables = tables;
         if (b.tab.max_large_k <= 4) {
             k_like_partial<4, true, kSplitFirst><<<grid, kLikeThreads, 0, stream>>>(b);
             k_like_partial<4, true, kSplitSecond><<<grid2, kLikeThreads, 0, stream>>>(b);
