@@ -85,11 +85,12 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
     const int words_per_block = a.trials_per_block / 32;
     if (PASSES == kSplitSecond) {  // nothing deferred in this CTA's blocks: leave before the table build
         unsigned int any = 0;
-        for (int c = 0; c < kSpan; ++c) {
+#pragma unroll
+        for (int c = 0; c < kSpan; ++c) {  // (no early exit: the blocks' loads are independent and overlap)
             const int64_t b0 = begin + (int64_t)c * a.trials_per_block;
-            if (b0 >= end) break;
-            const int64_t cnt = end - b0 < a.trials_per_block ? end - b0 : a.trials_per_block;
-            const int words = (int)((cnt + kLikeThreads - 1) / kLikeThreads) * (kLikeThreads / 32);
+            const int64_t left = end - b0;
+            const int64_t cnt = left < a.trials_per_block ? left : a.trials_per_block;
+            const int words = cnt > 0 ? (int)((cnt + kLikeThreads - 1) / kLikeThreads) * (kLikeThreads / 32) : 0;
             const unsigned int* w = a.defer_bits + (p * a.chunks + (int64_t)chunk * kSpan + c) * words_per_block;
             for (int k = threadIdx.x; k < words; k += kLikeThreads) any |= w[k];
         }
@@ -222,8 +223,12 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
                 const int64_t cnt = end - b0 < a.trials_per_block ? end - b0 : a.trials_per_block;
                 const int rounds = (int)((cnt + kLikeThreads - 1) / kLikeThreads);
                 const unsigned int* w = a.defer_bits + (p * a.chunks + (int64_t)chunk * kSpan + c) * words_per_block;
+                // lane r fetches the warp's word of round r: one load per block instead of one per round
+                static_assert(kMaxRounds <= 32, "a warp's words of one block fit one per lane");
+                const unsigned int mine = lane < rounds ? w[lane * (kLikeThreads / 32) + warp] : 0u;
                 for (int r = 0; r < rounds; ++r) {
-                    const unsigned int votes = w[r * (kLikeThreads / 32) + warp];
+                    const unsigned int votes = __shfl_sync(0xffffffffu, mine, r);
+                    if (votes == 0) continue;  // warp-uniform
                     if ((votes >> lane) & 1u)
                         queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] =
                             (unsigned short)(c * a.trials_per_block + r * kLikeThreads + threadIdx.x);

@@ -1,7 +1,7 @@
 # One GPU round: parity tests, smoke, bench lines (S-A with CPU baseline, S-B, reference arm), ncu launch list and
 # full captures (each after the same command exited 0 without ncu).  TAG names the outputs under gpurun_out/.
 set -x
-TAG=${TAG:-r1_v8}
+TAG=${TAG:-r1_v9}
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${TAG}_pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1
