@@ -326,21 +326,24 @@ def run_ours(args):
             "config": workload_config(args, world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(x.nbytes + params.nbytes),
                     "d2h_bytes_per_step": int(8 * P + 8), "steps": e2e_steps, "bitwise_equal_to_device_path": same},
-            # big sweeps (>= 2368 blocks of 8192 trials): first pass, deferred-trial pass, final sum; else 2 launches
-            "gpu_launches": (3 if (T > 6144 and P * math.ceil(T / 8192.0) >= 2368) else 2) * args.steps,
+            # big sweeps (>= 2368 blocks of 8192 trials): per-set tables, first pass, deferred-trial pass, final sum; else 2
+            "gpu_launches": (4 if (T > 6144 and P * math.ceil(T / 8192.0) >= 2368) else 2) * args.steps,
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
                          "frac": achieved / peak_tflops, "traffic": traffic, "traffic_source": traffic_src,
                          "algorithmic_bytes": int(8 * T + 72 * P + 8 * P * math.ceil(T / 2048.0) +
-                                                  (2 * 1024 * P * math.ceil(T / 8192.0)
+                                                  # split sweep: bit map out and back, per-set tables out and
+                                                  # into every CTA of both launches
+                                                  ((2 * 1024 + 3072) * P * math.ceil(T / 8192.0) +
+                                                   3072 * P * (1 + math.ceil(math.ceil(T / 8192.0) / 8.0))
                                                    if (T > 6144 and P * math.ceil(T / 8192.0) >= 2368) else 0)),
-                         "fp64_pipe_active_pct_ncu": 57.0,
-                         "kernel": "k_like_partial: first pass + deferred-trial pass (S-A: 97 % + 3 %) + k_like_final (<0.1 %)",
+                         "fp64_pipe_active_pct_ncu": 57.7,
+                         "kernel": "k_like_partial: first pass + deferred-trial pass (S-A: 97 % + 3 %) + k_build_tables, k_like_final (0.1 %)",
                          "kernel_ms": k_ms,
                          "pdf_sv_per_eval": mean_pdfsv,
                          "accounting": "algorithmic FLOP = pdf_sv evals x 300 + 28 per eval (SURVEY.md 8d); "
                                        "peak = FP64 FMA probe measured in this run (MEASURED_PEAKS.json has no FP64 entry); "
                                        "frac > 1 because the kernel executes ~22 FP64 instructions per pdf_sv where the "
-                                       "reference's sequence costs 300 FLOP; fp64_pipe_active_pct_ncu (profiles/r1_v8_summary.md) "
+                                       "reference's sequence costs 300 FLOP; fp64_pipe_active_pct_ncu (profiles/r1_v9_summary.md) "
                                        "is the executed-work utilisation"},
             "cpu_baseline": cpu,
             "clocks": clocks,
