@@ -376,6 +376,31 @@ def test_split_sweep_equals_one_launch(W, O, evaluator, onset):
         assert_parity(got["auto"][0][p], want, RTOL_SUM, what="split sweep, set %d" % p)
 
 
+def test_split_sweep_with_per_trial_drift(W, O, evaluator):
+    """The two-launch flavour with a drift per trial (regression sweep built on the device, wiener_like_multi
+    semantics: no zero guard) equals the one-launch flavour; oracle parity on one coefficient set."""
+    from hddm_b200 import _lib
+    if evaluator != "auto":
+        pytest.skip("compares the grid evaluator's flavours itself")
+    T, P = 16500, 800
+    x, params = sweep_inputs(T, P, onset=0.30)
+    rng = np.random.default_rng(11)
+    design = np.concatenate([np.ones((1, T)), rng.standard_normal((1, T))])
+    coef = np.concatenate([params[0][None, :], rng.uniform(-0.5, 0.5, (1, P))])
+    got = {}
+    for name in ("auto", "fused"):
+        _lib.check(_lib.lib().hddm_b200_set_kernel(KERNEL_CHOICE[name]))
+        got[name] = W.wiener_like_regression_batch(x, design, coef, params, **HDDM)
+    _lib.check(_lib.lib().hddm_b200_set_kernel(0))
+    assert_parity(got["auto"], got["fused"], 1e-12, what="split vs fused, per-trial drift")
+    p = 123
+    v = np.ascontiguousarray(design.T @ coef[:, p])
+    want = O.wiener_like_multi(x, v, *params[1:7, p], HDDM["err"], multi=["v"], n_st=HDDM["n_st"], n_sz=HDDM["n_sz"],
+                               use_adaptive=HDDM["use_adaptive"], simps_err=HDDM["simps_err"],
+                               p_outlier=params[7, p], w_outlier=params[8, p])
+    assert_parity(got["auto"][p], want, RTOL_SUM, what="regression split sweep, set %d" % p)
+
+
 def test_nodes_batch_vs_oracle(W, O):
     """Hierarchical layout: many parameter sets per observed node in one launch (host-buffer entry point
     and the device-resident handle), against one oracle call per set."""
