@@ -328,6 +328,19 @@ __global__ void __launch_bounds__(128) k_like_final(const LikeArgs a)
     if (lane == 0) a.logp[p] = s;
 }
 
+// Freed blocks stay in the stream-ordered pool instead of going back to the OS (launch_like's scratch).
+static void keep_pool_memory()
+{
+    static bool done = false;
+    if (done) return;
+    int dev = 0;
+    cudaMemPool_t pool;
+    unsigned long long keep = ~0ull;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess)
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    done = true;
+}
+
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
 {
     if (a.n_sets <= 0) return cudaSuccess;
@@ -362,15 +375,7 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     unsigned int* bits = nullptr;
     size_t map_bytes = 0;
     if (two_pass && b.trials_per_block == kTrialsPerBigBlock && g_kernel_choice != 4) {
-        static bool pool_ready = false;
-        if (!pool_ready) {  // keep freed blocks in the stream-ordered pool instead of returning them to the OS
-            int dev = 0;
-            cudaMemPool_t pool;
-            unsigned long long keep = ~0ull;
-            if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess)
-                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-            pool_ready = true;
-        }
+        keep_pool_memory();
         map_bytes = (size_t)b.n_sets * b.chunks * (kTrialsPerBigBlock / 32) * sizeof(unsigned int);
         const size_t table_bytes = (size_t)b.n_sets * (b.tab.max_large_k <= 4 ? sizeof(GridSet<4>) : sizeof(GridSet<8>));
         if (cudaMallocAsync((void**)&bits, map_bytes + table_bytes, stream) != cudaSuccess) {
@@ -402,6 +407,22 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
         cudaFreeAsync(bits, stream);
         return e;
     }
+    // Several CTAs per set and more CTAs than the GPU holds at once: build each set's tables once here too.
+    void* shared_tables = nullptr;
+    if (gridk && b.chunks >= 2 && (int64_t)b.n_sets * b.chunks >= 148 * 2 * 2) {
+        keep_pool_memory();
+        const size_t bytes = (size_t)b.n_sets * (b.tab.max_large_k <= 4 ? sizeof(GridSet<4>) : sizeof(GridSet<8>));
+        if (cudaMallocAsync(&shared_tables, bytes, stream) != cudaSuccess) {
+            (void)cudaGetLastError();
+            shared_tables = nullptr;
+        } else {
+            if (b.tab.max_large_k <= 4)
+                k_build_tables<4><<<(unsigned)b.n_sets, kLikeThreads, 0, stream>>>(b, shared_tables);
+            else
+                k_build_tables<8><<<(unsigned)b.n_sets, kLikeThreads, 0, stream>>>(b, shared_tables);
+            b.set_tables = shared_tables;
+        }
+    }
     if (two_pass && b.tab.max_large_k <= 4)
         k_like_partial<4, true, kTwoPass><<<grid, kLikeThreads, 0, stream>>>(b);
     else if (two_pass)
@@ -419,7 +440,9 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     if (b.chunks == 1) return cudaGetLastError();  // short nodes: one launch, k_like_partial wrote logp
     const int sets_per_block = 128 / 32;
     k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(b);
-    return cudaGetLastError();
+    const cudaError_t e = cudaGetLastError();
+    if (shared_tables) cudaFreeAsync(shared_tables, stream);
+    return e;
 }
 
 // pdf_array (src/wfpt.pyx:32-48): per-trial density, outlier mix, optional log.
