@@ -52,6 +52,7 @@ SIGNATURES = {
     "hddm_dmat_cdf_batch": (_i, [c_dp, _l, c_dp, _l, c_dp, c_ip]),
     "hddm_wiener_like_regression_batch": (_i, [c_dp, _l, c_dp, _l, c_dp, c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_simulate_drift_batch": (_i, [c_dp, _l, _l, _d, _d, C.c_ulonglong, c_dp, c_dp, _l, c_dp]),
+    "hddm_simulate_drift_switch_batch": (_i, [c_dp, c_dp, _l, _l, _d, _d, C.c_ulonglong, c_dp, c_dp, _l, c_dp]),
     "hddm_wiener_like_rlddm": (_i, [c_dp, c_lp, c_dp, c_lp, _l] + [_d] * 10 + _NUM + [_d, _d, c_dp]),
     "hddm_wiener_like_rlddm_batch": (_i, [c_dp, c_lp, c_dp, c_lp, _l, c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_wiener_like_rl": (_i, [c_lp, c_dp, c_lp, _l] + [_d] * 7 + [c_dp]),

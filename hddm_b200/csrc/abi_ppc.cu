@@ -198,31 +198,42 @@ int hddm_dmat_cdf_batch(const double* x, int64_t n, const double* params, int64_
 
 }  // extern "C"
 
-extern "C" int hddm_simulate_drift_batch(const double* params, int64_t D, int64_t samples, double dt,
-                                         double intra_sv, unsigned long long seed, const double* u_init,
-                                         const double* u_steps, int64_t max_steps, double* rts)
+// Shared body of the two simulator entry points.  switch_par == nullptr: no switch, u_init has 3 columns.
+static int simulate_drift_impl(const double* params, const double* switch_par, int64_t D, int64_t samples, double dt,
+                               double intra_sv, unsigned long long seed, const double* u_init,
+                               const double* u_steps, int64_t max_steps, double* rts)
 {
     std::lock_guard<std::mutex> lock(g_rt.mu);
     if (D < 0 || samples < 0 || max_steps < 1 || !(dt > 0) || !(intra_sv > 0) ||
         (D > 0 && samples > 0 && (!params || !rts)) || ((u_init == nullptr) != (u_steps == nullptr)))
         return fail(HDDM_ERR_ARG, "simulate_drift_batch: bad buffer, size, dt or intra_sv");
+    if (switch_par)  // the reference draws blocks of round(t_switch / dt) steps: a block of 0 steps fails there
+        for (int64_t d = 0; d < D; ++d)
+            if (!(nearbyint(switch_par[2 * D + d] / dt) >= 1))
+                return fail(HDDM_ERR_ARG, "simulate_drift_batch: round(t_switch / dt) must be >= 1");
     TRY(ensure_ready());
     const int64_t n = D * samples;
     if (n == 0) return HDDM_OK;
+    const int cols = switch_par ? 4 : 3;
     Layout L;
     const size_t off_p = L.reserve((size_t)D * 7 * sizeof(double));
+    const size_t off_w = switch_par ? L.reserve((size_t)D * 3 * sizeof(double)) : 0;
     const size_t off_r = L.reserve((size_t)n * sizeof(double));
-    const size_t off_i = u_init ? L.reserve((size_t)n * 3 * sizeof(double)) : 0;
+    const size_t off_i = u_init ? L.reserve((size_t)n * cols * sizeof(double)) : 0;
     const size_t off_u = u_steps ? L.reserve((size_t)n * max_steps * sizeof(double)) : 0;
     TRY(ensure_arena(L.total));
     cudaStream_t s = g_rt.stream;
     CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_p), params, (size_t)D * 7 * sizeof(double), cudaMemcpyHostToDevice, s));
+    if (switch_par)
+        CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_w), switch_par, (size_t)D * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
     if (u_init) {
-        CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_i), u_init, (size_t)n * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+        CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_i), u_init, (size_t)n * cols * sizeof(double), cudaMemcpyHostToDevice, s));
         CUDA_TRY(cudaMemcpyAsync(L.at<double>(off_u), u_steps, (size_t)n * max_steps * sizeof(double), cudaMemcpyHostToDevice, s));
     }
     SimArgs a;
     a.params = L.at<double>(off_p);
+    a.switch_par = switch_par ? L.at<double>(off_w) : nullptr;
+    a.init_cols = cols;
     a.n_draws = D;
     a.samples = samples;
     a.max_steps = max_steps;
@@ -237,4 +248,23 @@ extern "C" int hddm_simulate_drift_batch(const double* params, int64_t D, int64_
     CUDA_TRY(cudaMemcpyAsync(rts, a.rts, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));
     return HDDM_OK;
+}
+
+extern "C" int hddm_simulate_drift_batch(const double* params, int64_t D, int64_t samples, double dt,
+                                         double intra_sv, unsigned long long seed, const double* u_init,
+                                         const double* u_steps, int64_t max_steps, double* rts)
+{
+    return simulate_drift_impl(params, nullptr, D, samples, dt, intra_sv, seed, u_init, u_steps, max_steps, rts);
+}
+
+extern "C" int hddm_simulate_drift_switch_batch(const double* params, const double* switch_par, int64_t D,
+                                                int64_t samples, double dt, double intra_sv,
+                                                unsigned long long seed, const double* u_init,
+                                                const double* u_steps, int64_t max_steps, double* rts)
+{
+    if (D > 0 && !switch_par) {
+        std::lock_guard<std::mutex> lock(g_rt.mu);
+        return fail(HDDM_ERR_ARG, "simulate_drift_switch_batch: switch_par is NULL");
+    }
+    return simulate_drift_impl(params, switch_par, D, samples, dt, intra_sv, seed, u_init, u_steps, max_steps, rts);
 }

@@ -197,8 +197,12 @@ cudaError_t launch_rl_choice(const RlChoiceArgs& a, cudaStream_t stream);
 // keyed by (seed, (draw0 + d) * samples + s).  Otherwise (parity mode) u_init is [n_draws*samples][3] =
 // delay uniform, start-point uniform, standard-normal drift deviate, and u_steps is
 // [n_draws*samples][max_steps] step uniforms.  A walk that has not crossed after max_steps gives NaN.
+// switch_par != nullptr: the v_switch variant (hddm/generate.py:234-241,272-276,283-285), SoA [3][n_draws] =
+// v_switch, V_switch, t_switch; u_init then has a fourth column, the standard-normal deviate of the switched drift.
 struct SimArgs {
     const double* params;
+    const double* switch_par = nullptr;
+    int init_cols = 3;
     int64_t n_draws, samples, max_steps, draw0;
     double dt, intra_sv;
     unsigned long long seed;

@@ -9,6 +9,9 @@
 // supplied uniforms (parity mode) the crossing step and the RT equal a numpy run of the reference loop.
 // In production mode every trial owns a Philox4x32-10 counter sequence: 4 steps per generator call,
 // each a 32-bit integer compared with the up-probability scaled to 2^32.
+// v_switch variant (:234-241,272-276,283-285): the reference draws its steps in blocks of
+// nn = round(t_switch / dt) and from the second block on walks with the switched drift
+// normal(v_switch, V_switch), i.e. steps 0..nn-1 use the first up-probability, all later ones the second.
 #include <curand_kernel.h>
 
 #include "kernels.cuh"
@@ -25,18 +28,27 @@ __global__ void __launch_bounds__(128) k_simulate_drift(const SimArgs a)
     const double sz = a.params[4 * a.n_draws + d], t = a.params[5 * a.n_draws + d];
     const double st = a.params[6 * a.n_draws + d];
 
+    const bool sw = a.switch_par != nullptr;
+    const double v_sw = sw ? a.switch_par[0 * a.n_draws + d] : 0.0, sv_sw = sw ? a.switch_par[1 * a.n_draws + d] : 0.0;
+    // steps before the switch: int(round(t_switch / dt)), round-half-even like Python's round (:236-239)
+    const int64_t n_first = sw ? (int64_t)rint(a.switch_par[2 * a.n_draws + d] / a.dt) : a.max_steps;
+
     curandStatePhilox4_32_10_t rng;
-    double u_delay, u_start, n_drift;
+    double u_delay, u_start, n_drift, n_drift_sw = 0.0;
     if (a.u_init) {
-        u_delay = a.u_init[id * 3 + 0];
-        u_start = a.u_init[id * 3 + 1];
-        n_drift = a.u_init[id * 3 + 2];
+        const double* u = a.u_init + id * a.init_cols;
+        u_delay = u[0];
+        u_start = u[1];
+        n_drift = u[2];
+        if (sw) n_drift_sw = u[3];
     } else {
         curand_init(a.seed, (unsigned long long)(a.draw0 * a.samples + id), 0, &rng);
         const double2 u = curand_uniform2_double(&rng);
         u_delay = 1.0 - u.x;  // [0, 1)
         u_start = 1.0 - u.y;
-        n_drift = curand_normal_double(&rng);
+        const double2 g = curand_normal2_double(&rng);
+        n_drift = g.x;
+        n_drift_sw = g.y;
     }
     // scipy uniform.rvs(loc, scale) = loc + scale*u; norm.rvs(loc, scale) = loc + scale*n
     const double delay = __dadd_rn(__dadd_rn(t, __dmul_rn(st, u_delay)), -(st / 2.));
@@ -45,6 +57,8 @@ __global__ void __launch_bounds__(128) k_simulate_drift(const SimArgs a)
     const double root_dt = sqrt(a.dt);
     const double step = __dmul_rn(root_dt, a.intra_sv);
     const double prob_up = __dmul_rn(0.5, __dadd_rn(1.0, __dmul_rn(root_dt / a.intra_sv, drift)));
+    const double drift_sw = sv_sw != 0 ? __dadd_rn(v_sw, __dmul_rn(sv_sw, n_drift_sw)) : v_sw;  // :272-276
+    const double prob_up_sw = sw ? __dmul_rn(0.5, __dadd_rn(1.0, __dmul_rn(root_dt / a.intra_sv, drift_sw))) : prob_up;
 
     int64_t k = 0;       // 0-based index of the step being taken
     double prev = y;
@@ -53,7 +67,7 @@ __global__ void __launch_bounds__(128) k_simulate_drift(const SimArgs a)
         const double* u = a.u_steps + id * a.max_steps;
         for (; k < a.max_steps; ++k) {
             prev = y;
-            y = __dadd_rn(y, (u[k] < prob_up) ? step : -step);
+            y = __dadd_rn(y, (u[k] < (k < n_first ? prob_up : prob_up_sw)) ? step : -step);
             if (y < 0 || y > bound) {
                 crossed = true;
                 break;
@@ -61,9 +75,11 @@ __global__ void __launch_bounds__(128) k_simulate_drift(const SimArgs a)
         }
     } else {
         // P(r < thr) with r uniform on 0..2^32-1: thr = prob_up * 2^32 clamped to [0, 2^32]
-        const double scaled = prob_up * 4294967296.0;
-        const unsigned long long thr = scaled <= 0 ? 0ull : (scaled >= 4294967296.0 ? 4294967296ull
-                                                                                   : (unsigned long long)scaled);
+        auto threshold = [](double p) {
+            const double scaled = p * 4294967296.0;
+            return scaled <= 0 ? 0ull : (scaled >= 4294967296.0 ? 4294967296ull : (unsigned long long)scaled);
+        };
+        const unsigned long long thr_first = threshold(prob_up), thr_sw = threshold(prob_up_sw);
         while (k < a.max_steps && !crossed) {
             const uint4 r = curand4(&rng);
             const unsigned int w[4] = {r.x, r.y, r.z, r.w};
@@ -71,7 +87,7 @@ __global__ void __launch_bounds__(128) k_simulate_drift(const SimArgs a)
             for (int j = 0; j < 4; ++j) {
                 if (!crossed && k < a.max_steps) {
                     prev = y;
-                    y = __dadd_rn(y, ((unsigned long long)w[j] < thr) ? step : -step);
+                    y = __dadd_rn(y, ((unsigned long long)w[j] < (k < n_first ? thr_first : thr_sw)) ? step : -step);
                     if (y < 0 || y > bound) crossed = true; else ++k;
                 }
             }

@@ -123,37 +123,52 @@ def quantile_objectives(emp_rt, freq_obs, n_samples, params):
 
 
 def simulate_drift_batch(params, samples=1000, dt=1e-4, intra_sv=1.0, seed=0, u_init=None, u_steps=None,
-                         max_steps=10000000):
+                         max_steps=10000000, switch=None):
     """Random-walk simulator of hddm/generate.py:208-319 (_gen_rts_from_simulated_drift) for D parameter
     sets x `samples` trials on the GPU: params float64 [7, D] -> signed RTs [D, samples].  Device Philox
     uniforms keyed by `seed`, or -- parity mode -- the caller's u_init [D, samples, 3] (delay uniform,
-    start-point uniform, standard-normal drift deviate) and u_steps [D, samples, max_steps]."""
+    start-point uniform, standard-normal drift deviate) and u_steps [D, samples, max_steps].
+    `switch`: float64 [3, D] = v_switch, V_switch, t_switch, the variant of :234-241,272-276,283-285 (the
+    drift becomes normal(v_switch, V_switch) from step round(t_switch / dt) on); u_init then has a fourth
+    column, the standard-normal deviate of the switched drift."""
     params = _params7(params)
     D = params.shape[1]
+    cols = 3
+    if switch is not None:
+        switch = np.ascontiguousarray(switch, dtype=np.float64)
+        if switch.shape != (3, D):
+            raise ValueError("switch must be float64 [3, D]: v_switch, V_switch, t_switch")
+        cols = 4
     rts = np.empty((D, samples), dtype=np.double)
     ip = up = None
     if u_init is not None or u_steps is not None:
         u_init = np.ascontiguousarray(u_init, dtype=np.float64)
         u_steps = np.ascontiguousarray(u_steps, dtype=np.float64)
-        if u_init.shape != (D, samples, 3) or u_steps.ndim != 3 or u_steps.shape[:2] != (D, samples):
-            raise ValueError("u_init must be [D, samples, 3] and u_steps [D, samples, max_steps]")
+        if u_init.shape != (D, samples, cols) or u_steps.ndim != 3 or u_steps.shape[:2] != (D, samples):
+            raise ValueError("u_init must be [D, samples, %d] and u_steps [D, samples, max_steps]" % cols)
         max_steps = u_steps.shape[2]
         ip, up = dptr(u_init), dptr(u_steps)
-    check(lib().hddm_simulate_drift_batch(dptr(params), D, samples, dt, intra_sv, int(seed), ip, up, int(max_steps),
-                                          dptr(rts)))
+    if switch is None:
+        check(lib().hddm_simulate_drift_batch(dptr(params), D, samples, dt, intra_sv, int(seed), ip, up,
+                                              int(max_steps), dptr(rts)))
+    else:
+        check(lib().hddm_simulate_drift_switch_batch(dptr(params), dptr(switch), D, samples, dt, intra_sv, int(seed),
+                                                     ip, up, int(max_steps), dptr(rts)))
     return rts
 
 
 def gen_rts_from_simulated_drift(params, samples=1000, dt=1e-4, intra_sv=1., seed=None):
-    """hddm/generate.py:208 signature for one parameter dict (keys v, a, z, t and optionally sv, sz, st);
-    returns the RT vector (the reference also returns the drift paths, which only its plotting code uses)."""
-    if 'v_switch' in params:
-        raise NotImplementedError("the v_switch variant (hddm/generate.py:234-241) is not on the GPU path")
+    """hddm/generate.py:208 signature for one parameter dict (keys v, a, z, t and optionally sv, sz, st, and
+    v_switch, t_switch[, V_switch] for the switched-drift variant); returns the RT vector (the reference
+    also returns the drift paths, which only its plotting code uses)."""
     col = np.array([[params['v']], [params.get('sv', 0.)], [params['a']], [params.get('z', .5)],
                     [params.get('sz', 0.)], [params['t']], [params.get('st', 0.)]], dtype=np.float64)
+    switch = None
+    if 'v_switch' in params:
+        switch = np.array([[params['v_switch']], [params.get('V_switch', 0.)], [params['t_switch']]], dtype=np.float64)
     if seed is None:
         seed = np.random.randint(0, 2 ** 31 - 1)
-    return simulate_drift_batch(col, 1 if samples is None else samples, dt, intra_sv, seed)[0]
+    return simulate_drift_batch(col, 1 if samples is None else samples, dt, intra_sv, seed, switch=switch)[0]
 
 
 def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=0, evaluate=None, group=None):

@@ -179,10 +179,18 @@ int hddm_dmat_cdf_batch(const double *x, int64_t n, const double *params, int64_
  * u_init == NULL and u_steps == NULL: device Philox4x32-10 keyed by (seed, global trial index).
  * Otherwise both must be given (parity mode): u_init [D*samples][3] = delay uniform, start-point uniform,
  * standard-normal drift deviate; u_steps [D*samples][max_steps] = one uniform per step.  A walk that
- * has not left [0, a] after max_steps steps yields NaN.  The v_switch variant (:234-241) is not covered. */
+ * has not left [0, a] after max_steps steps yields NaN. */
 int hddm_simulate_drift_batch(const double *params, int64_t D, int64_t samples, double dt, double intra_sv,
                               unsigned long long seed, const double *u_init, const double *u_steps,
                               int64_t max_steps, double *rts);
+/* The v_switch variant of the same function (hddm/generate.py:234-241,272-276,283-285): switch_par is SoA
+ * float64 [3][D] = v_switch, V_switch, t_switch.  The reference walks in blocks of nn = round(t_switch / dt)
+ * steps and uses the switched drift normal(v_switch, V_switch) from its second block on, i.e. from step nn.
+ * Parity mode: u_init is [D*samples][4], the fourth column the standard-normal deviate of the switched
+ * drift.  HDDM_ERR_ARG when round(t_switch / dt) < 1 (the reference fails on an empty block). */
+int hddm_simulate_drift_switch_batch(const double *params, const double *switch_par, int64_t D, int64_t samples,
+                                     double dt, double intra_sv, unsigned long long seed, const double *u_init,
+                                     const double *u_steps, int64_t max_steps, double *rts);
 
 /* ---- reinforcement-learning likelihoods (src/wfpt.pyx:79-241, 277-320) -------------------------- */
 

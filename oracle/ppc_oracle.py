@@ -1,9 +1,14 @@
 """CPU restatement of the posterior-predictive summary statistics.  TEST INFRASTRUCTURE ONLY.
 
-hddm/utils.py:241-267 (gen_ppc_stats) cannot be imported here (hddm/utils.py imports kabuki and pymc at
-module level), so its fifteen lambdas are restated one for one with the same numpy / scipy calls; the
-simulated data sets themselves come from oracle.gen_rts_from_cdf (the C restatement of
-src/wfpt.pyx:323-354) or from the compiled reference."""
+The fifteen lambdas of gen_ppc_stats (hddm/utils.py:241-267) restated one for one with the same numpy /
+scipy calls; the simulated data sets themselves come from oracle.gen_rts_from_cdf (the C restatement of
+src/wfpt.pyx:323-354) or from the compiled reference.
+
+PINNED: tests/test_oracle.py::test_ppc_oracle_reproduces_reference_gen_ppc_stats requires this function to
+return, bit for bit (NaN classes included), what the reference's own gen_ppc_stats() returned for the 19
+data sets of tests/golden/ref_ppc_stats.npz (made by tests/golden/make_golden_py.py, which executes
+/root/reference/hddm/utils.py unmodified with empty stand-ins for its unused kabuki / pymc / matplotlib
+imports)."""
 import warnings
 
 import numpy as np

@@ -1,13 +1,18 @@
 """CPU restatement of the random-walk simulator, hddm/generate.py:208-319
-(_gen_rts_from_simulated_drift).  TEST INFRASTRUCTURE ONLY.
+(_gen_rts_from_simulated_drift), incl. its v_switch variant (:234-241,272-276,283-285).
+TEST INFRASTRUCTURE ONLY.
 
-hddm/generate.py imports the hddm package (kabuki, pymc: absent), so the loop is restated with the same
-numpy operations -- np.cumsum over blocks of nn = 1000 steps, np.where for the crossing, the linear
-interpolation of :304-315 -- taking its random numbers from the caller instead of the global RNG:
-u_init[i] = (delay uniform, start-point uniform, standard-normal drift deviate) and u_steps[i, k] = the
-k-th step uniform of trial i (scipy's uniform.rvs(loc, scale) is loc + scale*u, norm.rvs(loc, scale) is
-loc + scale*n).  "parity unpinned" by any reference test; pinned here against the CDF sampler
-statistically, as hddm/tests/test_generate.py:21-29 does.  The v_switch branch is left out."""
+The loop is restated with the same numpy operations -- np.cumsum over blocks of nn steps (nn = 1000, or
+round(t_switch / dt) with a switch, :233-239), np.where for the crossing, the linear interpolation of
+:304-315 -- taking its random numbers from the caller instead of the global RNG: u_init[i] = (delay
+uniform, start-point uniform, standard-normal drift deviate[, standard-normal deviate of the switched
+drift]) and u_steps[i, k] = the k-th step uniform of trial i (scipy's uniform.rvs(loc, scale) is
+loc + scale*u, norm.rvs(loc, scale) is loc + scale*n).
+
+PINNED: tests/test_oracle.py::test_simulator_oracle_reproduces_reference_runs requires this function to
+return, bit for bit, what the reference's own function returned for the ten runs stored in
+tests/golden/ref_simdrift.npz (made by tests/golden/make_golden_py.py, which executes
+/root/reference/hddm/generate.py unmodified and records the random numbers it consumed)."""
 import numpy as np
 
 
@@ -15,22 +20,39 @@ def gen_rts_from_simulated_drift(params, u_init, u_steps, dt=1e-4, intra_sv=1.):
     samples = u_init.shape[0]
     nn = 1000
     a, v = params['a'], params['v']
-    st, sz = params.get('st', 0.), params.get('sz', 0.)
-    start_delay = (params['t'] + st * u_init[:, 0]) - st / 2.                 # :244-248
-    starting_points = ((params['z'] + sz * u_init[:, 1]) - sz / 2.) * a       # :251-255
+    switch = 'v_switch' in params
+    if switch:
+        nn = int(round(params['t_switch'] / dt))                              # :234-239
+    if 'st' in params:                                                        # :244-248
+        start_delay = (params['st'] * u_init[:, 0] + params['t']) - params['st'] / 2.
+    else:
+        start_delay = np.ones(samples) * params['t']
+    if 'sz' in params:                                                        # :251-255
+        starting_points = ((params['sz'] * u_init[:, 1] + params['z']) - params['sz'] / 2.) * a
+    else:
+        starting_points = np.ones(samples) * params['z'] * a
     rts = np.full(samples, np.nan)
     step_size = np.sqrt(dt) * intra_sv                                        # :258
     for i in range(samples):
         y_0 = starting_points[i]
         if 'sv' in params and params['sv'] != 0:                              # :266-269
-            drift_rate = v + params['sv'] * u_init[i, 2]
+            drift_rate = u_init[i, 2] * params['sv'] + v
         else:
             drift_rate = v
+        if switch:                                                            # :271-276
+            if 'V_switch' in params and params['V_switch'] != 0:
+                drift_rate_switch = u_init[i, 3] * params['V_switch'] + params['v_switch']
+            else:
+                drift_rate_switch = params['v_switch']
         prob_up = 0.5 * (1 + np.sqrt(dt) / intra_sv * drift_rate)             # :278
         it, crossed = 0, False
         while not crossed and it * nn < u_steps.shape[1]:
             it += 1
+            if it == 2 and switch:                                            # :283-285
+                prob_up = 0.5 * (1 + np.sqrt(dt) / intra_sv * drift_rate_switch)
             u = u_steps[i, (it - 1) * nn: it * nn]
+            if np.isnan(u).any():                                             # ran out of supplied uniforms
+                break
             position = ((u < prob_up) * 2 - 1) * step_size                    # :286
             position[0] += y_0
             position = np.cumsum(position)

@@ -209,3 +209,49 @@ def test_eval_counter_matches_survey():
     O.wiener_like_batch(x, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
     mean = O.pdfsv_calls(reset=True) / 6000.0
     assert 20.0 < mean < 27.0, mean   # 10 sets only: a near-zero sz or st draw lowers it
+
+
+# ---- the Python-side oracles, pinned on outputs of the reference's own functions ----
+
+def test_ppc_oracle_reproduces_reference_gen_ppc_stats(golden_dir):
+    """oracle/ppc_oracle.py against tests/golden/ref_ppc_stats.npz: the fifteen lambdas of gen_ppc_stats()
+    (hddm/utils.py:241-267), executed from the unmodified reference file by tests/golden/make_golden_py.py, on
+    19 data sets (empty boundary, ties, zeros, single RTs, zero variance).  Bit for bit, NaN classes included."""
+    from oracle.ppc_oracle import ppc_stats
+    d = np.load(os.path.join(golden_dir, "ref_ppc_stats.npz"))
+    assert [str(n) for n in d["names"]] == ["accuracy", "mean_ub", "std_ub", "10q_ub", "30q_ub", "50q_ub", "70q_ub",
+                                            "90q_ub", "mean_lb", "std_lb", "10q_lb", "30q_lb", "50q_lb", "70q_lb",
+                                            "90q_lb"]
+    assert int(d["n"]) >= 19
+    nan_rows = 0
+    for k in range(int(d["n"])):
+        want = d["y_%d" % k]
+        assert same(ppc_stats(d["x_%d" % k]), want), k
+        nan_rows += bool(np.isnan(want).any())
+    assert nan_rows >= 6
+
+
+def simdrift_cases(golden_dir):
+    d = np.load(os.path.join(golden_dir, "ref_simdrift.npz"))
+    keys = [str(k) for k in d["keys"]]
+    for k in range(int(d["n"])):
+        cfg = d["cfg_%d" % k]
+        params = {n: float(v) for n, v in zip(keys, d["par_%d" % k]) if not np.isnan(v)}  # NaN: key absent
+        yield k, params, int(cfg[0]), float(cfg[1]), float(cfg[2]), d["u_init_%d" % k], d["u_steps_%d" % k], \
+            d["rts_%d" % k], d["blocks_%d" % k]
+
+
+def test_simulator_oracle_reproduces_reference_runs(golden_dir):
+    """oracle/sim_oracle.py against tests/golden/ref_simdrift.npz: ten runs of _gen_rts_from_simulated_drift
+    (hddm/generate.py:208-319, executed unmodified by make_golden_py.py with numpy's global RNG seeded and the
+    consumed random numbers recorded), four of them with v_switch.  Bit for bit."""
+    from oracle import sim_oracle
+    n, switched, multi_block = 0, 0, 0
+    for k, params, S, dt, intra_sv, u_init, u_steps, want, blocks in simdrift_cases(golden_dir):
+        got = sim_oracle.gen_rts_from_simulated_drift(params, u_init, u_steps, dt=dt, intra_sv=intra_sv)
+        assert same(got, want), k
+        assert not np.isnan(want).any()
+        n += 1
+        switched += "v_switch" in params
+        multi_block += bool((blocks > 1).any())
+    assert n >= 10 and switched >= 4 and multi_block >= 6

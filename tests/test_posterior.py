@@ -90,6 +90,21 @@ def test_stats_against_oracle(gpu, S):
 
 
 @pytest.mark.gpu
+def test_stats_against_reference_fixture(gpu, golden_dir):
+    """k_ppc_stats against the reference's OWN gen_ppc_stats() (hddm/utils.py:241-267) outputs,
+    tests/golden/ref_ppc_stats.npz (made by tests/golden/make_golden_py.py from the unmodified file)."""
+    import os
+    from hddm_b200 import posterior
+    d = np.load(os.path.join(golden_dir, "ref_ppc_stats.npz"))
+    for k in range(int(d["n"])):
+        got, want = posterior.ppc_stats(d["x_%d" % k])[0], d["y_%d" % k]
+        assert np.array_equal(np.isnan(got), np.isnan(want)), k
+        m = ~np.isnan(want)
+        np.testing.assert_allclose(got[m], want[m], rtol=1e-12, atol=1e-15, err_msg="data set %d" % k)
+        assert got[0] == want[0]
+
+
+@pytest.mark.gpu
 def test_fused_stats_equal_stats_of_returned_rts(gpu):
     from hddm_b200 import posterior
     rng = np.random.default_rng(3)

@@ -43,6 +43,43 @@ def test_supplied_randomness_reproduces_the_reference_loop(gpu):
         assert np.array_equal(np.sign(got[d][m]), np.sign(want[m]))
 
 
+def test_reference_runs_reproduced(gpu, golden_dir):
+    """The kernel against the reference's OWN outputs: tests/golden/ref_simdrift.npz holds ten runs of
+    _gen_rts_from_simulated_drift (hddm/generate.py:208-319, four with v_switch) together with the random
+    numbers each run consumed.  Same crossing boundary on every trial, RT to 1e-12."""
+    from hddm_b200 import posterior
+    from tests.test_oracle import simdrift_cases
+    n = 0
+    for k, p, S, dt, intra_sv, u_init, u_steps, want, _ in simdrift_cases(golden_dir):
+        col = np.array([[p['v']], [p.get('sv', 0.)], [p['a']], [p['z']], [p.get('sz', 0.)], [p['t']], [p.get('st', 0.)]])
+        switch = None
+        if 'v_switch' in p:
+            switch = np.array([[p['v_switch']], [p.get('V_switch', 0.)], [p['t_switch']]])
+        init = u_init[None, :, :4 if switch is not None else 3]
+        got = posterior.simulate_drift_batch(col, S, dt=dt, intra_sv=intra_sv, u_init=init, u_steps=u_steps[None],
+                                             switch=switch)[0]
+        assert not np.isnan(got).any(), k
+        assert np.array_equal(np.sign(got), np.sign(want)), k
+        np.testing.assert_allclose(got, want, rtol=1e-12, atol=0, err_msg="case %d" % k)
+        n += 1
+    assert n >= 10
+
+
+def test_switch_variant_device_rng(gpu):
+    """v_switch with the device RNG: a strong negative switched drift after 50 ms turns a mostly-upper
+    process into a mostly-lower one; V_switch = 0 and t_switch beyond every walk leave the plain process."""
+    from hddm_b200 import posterior
+    p = dict(v=2.0, a=2.0, z=0.5, t=0.3, sv=0.2, sz=0.1, st=0.1)
+    plain = posterior.gen_rts_from_simulated_drift(p, samples=4000, dt=1e-3, seed=9)
+    late = posterior.gen_rts_from_simulated_drift(dict(p, v_switch=-4.0, t_switch=50.0), samples=4000, dt=1e-3, seed=9)
+    assert np.array_equal(plain, late)
+    flipped = posterior.gen_rts_from_simulated_drift(dict(p, v_switch=-4.0, V_switch=0.5, t_switch=0.05),
+                                                     samples=4000, dt=1e-3, seed=9)
+    assert (plain > 0).mean() > 0.9 and (flipped > 0).mean() < 0.35
+    with pytest.raises(ValueError):
+        posterior.gen_rts_from_simulated_drift(dict(p, v_switch=1.0, t_switch=1e-5), samples=5, dt=1e-3)
+
+
 def test_walk_that_never_crosses_is_nan(gpu):
     from hddm_b200 import posterior
     params = np.array([[0.0], [0.0], [50.0], [0.5], [0.0], [0.3], [0.0]])
@@ -81,8 +118,8 @@ def test_reference_shaped_single_call(gpu):
     r = posterior.gen_rts_from_simulated_drift(p, samples=500, seed=3)
     assert r.shape == (500,) and (np.abs(r) > 0.3 - 0.05).all()
     assert 0.6 < (r > 0).mean() < 0.95
-    with pytest.raises(NotImplementedError):
-        posterior.gen_rts_from_simulated_drift(dict(p, v_switch=1.0, t_switch=0.2), samples=5)
+    sw = posterior.gen_rts_from_simulated_drift(dict(p, v_switch=1.0, t_switch=0.2), samples=5, seed=3)
+    assert sw.shape == (5,) and not np.isnan(sw).any()
 
 
 def test_stochastic_class_random_with_drift_sampling(gpu):
