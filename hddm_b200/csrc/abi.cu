@@ -8,6 +8,8 @@
 #include <new>
 #include <vector>
 
+#include <cstdlib>
+
 #include "abi_runtime.cuh"
 
 using namespace hddm;
@@ -241,6 +243,11 @@ const char* hddm_b200_last_error(void) { return g_err; }
 int hddm_b200_init(int device)
 {
     std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (g_rt.ready && device >= 0 && device != g_rt.device) {
+        snprintf(g_err, sizeof(g_err), "hddm_b200 is already bound to CUDA device %d; one process per GPU "
+                 "(asked for device %d)", g_rt.device, device);
+        return HDDM_ERR_ARG;
+    }
     if (device >= 0) CUDA_TRY(cudaSetDevice(device));
     return ensure_ready();
 }
@@ -271,8 +278,18 @@ int hddm_b200_fp64_peak(int iters, double* flops, float* ms)
     return *flops > 0 ? HDDM_OK : fail(HDDM_ERR_CUDA, "fp64 probe failed");
 }
 
+// The two knobs below change perf-critical behaviour for every caller in the process: they are for A/B
+// parity tests and profiling only and are refused unless HDDM_B200_DEBUG_KNOBS=1 is in the environment.
+static bool debug_knobs_enabled()
+{
+    const char* v = getenv("HDDM_B200_DEBUG_KNOBS");
+    return v && v[0] == '1';
+}
+
 int hddm_b200_set_kernel(int which)
 {
+    if (!debug_knobs_enabled())
+        return fail(HDDM_ERR_ARG, "set_kernel is a debug knob: set HDDM_B200_DEBUG_KNOBS=1 to enable it");
     if (which < 0 || which > 4)
         return fail(HDDM_ERR_ARG, "set_kernel: 0 (auto), 1 (generic), 2 (no grid), 3 (grid, one pass) or "
                                   "4 (grid, two passes in one launch)");
@@ -283,6 +300,8 @@ int hddm_b200_set_kernel(int which)
 
 int hddm_b200_set_sort(int on)
 {
+    if (!debug_knobs_enabled())
+        return fail(HDDM_ERR_ARG, "set_sort is a debug knob: set HDDM_B200_DEBUG_KNOBS=1 to enable it");
     std::lock_guard<std::mutex> lock(g_rt.mu);
     g_sort_trials = on ? 1 : 0;
     return HDDM_OK;
@@ -656,6 +675,10 @@ int hddm_sort_trials_dev(const double* d_x, int64_t n, const int64_t* d_seg, int
 {
     if (n < 0 || n_seg < 0 || (n > 0 && (!d_x || !d_sorted || !d_scratch)) || (n_seg > 0 && !d_seg) || d_x == d_sorted)
         return fail(HDDM_ERR_ARG, "sort_trials_dev: bad buffer");
+    {  // binds / checks the process's one device (kernel attributes and pool settings are per device)
+        std::lock_guard<std::mutex> lock(g_rt.mu);
+        TRY(ensure_ready());
+    }
     CUDA_TRY(sort_trials(d_x, d_sorted, n, d_seg, n_seg, d_scratch, (size_t)scratch_bytes, (cudaStream_t)stream));
     return HDDM_OK;
 }
@@ -672,6 +695,10 @@ int hddm_wiener_like_batch_dev(const double* d_x, int64_t n, const int64_t* d_se
 {
     if (n < 0 || P < 0 || (P > 0 && (!d_params || !d_logp || !d_scratch)) || (n > 0 && !d_x))
         return fail(HDDM_ERR_ARG, "batch_dev: bad buffer or size");
+    {  // binds / checks the process's one device (kernel attributes and pool settings are per device)
+        std::lock_guard<std::mutex> lock(g_rt.mu);
+        TRY(ensure_ready());
+    }
     TRY(check_numerics(n_st, n_sz, use_adaptive));
     if (P == 0) return HDDM_OK;
     const int64_t chunks = chunks_for(d_seg ? max_seg_len : n);
@@ -704,6 +731,10 @@ int hddm_pdf_array_dev(const double* d_x, int64_t n, double v, double sv, double
                        unsigned long long* d_evals, void* stream)
 {
     if (n < 0 || (n > 0 && (!d_x || !d_y))) return fail(HDDM_ERR_ARG, "pdf_array_dev: bad buffer");
+    {  // binds / checks the process's one device (kernel attributes and pool settings are per device)
+        std::lock_guard<std::mutex> lock(g_rt.mu);
+        TRY(ensure_ready());
+    }
     TRY(check_numerics(n_st, n_sz, use_adaptive));
     PdfArgs pa;
     pa.x = d_x;
@@ -722,6 +753,10 @@ int hddm_dmat_cdf_array_dev(const double* d_x, int64_t n, double v, double sv, d
                             double t, double st, double p_outlier, double w_outlier, double* d_y, void* stream)
 {
     if (n < 0 || (n > 0 && (!d_x || !d_y))) return fail(HDDM_ERR_ARG, "dmat_cdf_array_dev: bad buffer");
+    {  // binds / checks the process's one device (kernel attributes and pool settings are per device)
+        std::lock_guard<std::mutex> lock(g_rt.mu);
+        TRY(ensure_ready());
+    }
     if (out_of_support(sv, a, z, sz, t, st, p_outlier))
         return fail(HDDM_ERR_SUPPORT, "at least one of the parameters is out of the support");
     CdfArgs ca;

@@ -40,6 +40,7 @@ inline int fail(int code, const char* msg)
 struct Runtime {
     std::mutex mu;
     bool ready = false;
+    int device = -1;  // the ONE device this process uses (stream, arena, kernel attributes belong to it)
     cudaStream_t stream = nullptr;
     char* arena = nullptr;  // grow-only device scratch, carved per call
     size_t arena_bytes = 0;
@@ -48,9 +49,19 @@ struct Runtime {
 };
 extern Runtime g_rt;
 
+// One process per GPU: all library state lives on the device that was current at first use.  A call made
+// with another device current fails loudly instead of enqueueing on a stream of the wrong device.
 inline int ensure_ready()
 {
-    if (g_rt.ready) return HDDM_OK;
+    if (g_rt.ready) {
+        int cur = -1;
+        if (cudaGetDevice(&cur) != cudaSuccess || cur != g_rt.device) {
+            snprintf(g_err, sizeof(g_err), "hddm_b200 is bound to CUDA device %d but device %d is current "
+                     "(one process per GPU; see hddm_b200_init)", g_rt.device, cur);
+            return HDDM_ERR_ARG;
+        }
+        return HDDM_OK;
+    }
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0) {
@@ -58,6 +69,7 @@ inline int ensure_ready()
                  e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
         return HDDM_ERR_CUDA;
     }
+    CUDA_TRY(cudaGetDevice(&g_rt.device));
     CUDA_TRY(cudaStreamCreateWithFlags(&g_rt.stream, cudaStreamNonBlocking));
     g_rt.ready = true;
     return HDDM_OK;

@@ -38,12 +38,18 @@ def _rt_array(x):
 
 
 class DeviceTrialCache(object):
-    """Signed-RT vectors resident on the GPU, keyed by content (length + two checksums), so that the
-    thousands of logp calls an MCMC run makes on one observed node upload its data once."""
+    """Signed-RT vectors resident on the GPU, so that the thousands of logp calls an MCMC run makes on one
+    observed node upload its data once.  Read-only data (what pandas' copy-on-write `.values` returns) is
+    recognised by identity -- address, shape, strides, plus a weak reference to the owning array that drops
+    the entry when the memory is released -- so the latency path does not re-hash the vector; anything else
+    is looked up by content (length + two checksums, confirmed byte for byte on a hit).
+    Least-recently-used entries are evicted one at a time."""
 
     def __init__(self, max_entries=4096):
+        from collections import OrderedDict
         self.max_entries = max_entries
-        self._handles = {}
+        self._handles = OrderedDict()   # content key -> (Trials, host copy of the bytes)
+        self._by_id = {}                # (address, shape, strides) -> (weakref to the owning array, content key)
 
     @staticmethod
     def _key(rt):
@@ -51,25 +57,46 @@ class DeviceTrialCache(object):
         return (rt.shape[0], zlib.adler32(buf), zlib.crc32(buf))
 
     def get(self, rt):
+        import weakref
+        owner = rt  # the array that owns the memory: pandas hands out a fresh read-only view per `.values`
+        while isinstance(owner.base, np.ndarray):
+            owner = owner.base
+        layout = (rt.__array_interface__['data'][0], rt.shape, rt.strides)
+        hit = self._by_id.get(layout)
+        # identity is trusted only for read-only data (pandas copy-on-write views): nothing can change
+        # the bytes behind our back, and the weak reference drops the entry before the address is reused
+        if hit is not None and hit[0]() is owner and not rt.flags.writeable:
+            ent = self._handles.get(hit[1])
+            if ent is not None:
+                self._handles.move_to_end(hit[1])
+                return ent[0]
         key = self._key(rt)
-        h = self._handles.get(key)
-        if h is None:
-            if len(self._handles) >= self.max_entries:
-                self.clear()
-            h = self._handles[key] = wfpt.Trials(rt)
-        return h
+        ent = self._handles.get(key)
+        if ent is not None and not np.array_equal(ent[1], rt, equal_nan=True):
+            key = key + (len(self._handles),)  # checksum collision: keep both, under distinct keys
+            ent = None
+        if ent is None:
+            while len(self._handles) >= self.max_entries:
+                _, (old, _) = self._handles.popitem(last=False)
+                old.close()
+            ent = self._handles[key] = (wfpt.Trials(rt), rt.copy())
+        else:
+            self._handles.move_to_end(key)
+        if not rt.flags.writeable:
+            self._by_id[layout] = (weakref.ref(owner, lambda _, k=layout: self._by_id.pop(k, None)), key)
+        return ent[0]
 
     def clear(self):
-        for h in self._handles.values():
+        for h, _ in self._handles.values():
             h.close()
-        self._handles = {}
+        self._handles.clear()
+        self._by_id.clear()
 
     def __getstate__(self):  # never pickle device handles
         return {'max_entries': self.max_entries}
 
     def __setstate__(self, state):
-        self.max_entries = state['max_entries']
-        self._handles = {}
+        self.__init__(state['max_entries'])
 
 
 _cache = DeviceTrialCache()
@@ -323,16 +350,74 @@ def general_WienerCont(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
     return _stochastic_from_dist("Wiener Diffusion Contaminant Process", _like)
 
 
-def wiener_multi_like(value, v, sv, a, z, sz, t, st, reg_outcomes, p_outlier=0, w_outlier=0.1):
-    """hddm/models/hddm_regression.py:26-36: parameters named in reg_outcomes are per-trial vectors
-    (already aligned with value's trials)."""
-    params = {'v': v, 'sv': sv, 'a': a, 'z': z, 'sz': sz, 't': t, 'st': st}
-    for name in reg_outcomes:
-        col = params[name]
-        params[name] = np.ascontiguousarray(getattr(col, 'values', col), dtype=np.float64)
-    return wfpt.wiener_like_multi(_rt_array(value), params['v'], params['sv'], params['a'], params['z'],
-                                  params['sz'], params['t'], params['st'], 1e-4, reg_outcomes,
-                                  w_outlier=w_outlier, p_outlier=p_outlier)
+def _reg_column(col, value, n):
+    """One regression outcome aligned with the node's trials, as hddm/models/hddm_regression.py:29-30 does it:
+    a pandas Series (the regressor node's value spans the whole data set) is re-indexed by the node's own
+    trial index, `.loc[value['rt'].index].values`.  Anything without an index must already have one entry
+    per trial of the node; a longer vector is refused rather than silently truncated."""
+    rt = value['rt'] if not (isinstance(value, np.ndarray) and value.dtype.names is None) else None
+    if hasattr(col, 'loc') and rt is not None and hasattr(rt, 'index'):
+        col = col.loc[rt.index].values
+    col = np.ascontiguousarray(getattr(col, 'values', col), dtype=np.float64)
+    if col.ndim != 1 or col.shape[0] != n:
+        raise ValueError("regression outcome has %s entries for a node of %d trials" % (col.shape, n))
+    return col
+
+
+def make_wiener_multi_like(wiener_params=None):
+    """The logp closure of hddm/models/hddm_regression.py:26-36."""
+    wp = dict(DEFAULT_WIENER_PARAMS if wiener_params is None else wiener_params)
+
+    def wiener_multi_like(value, v, sv, a, z, sz, t, st, reg_outcomes, p_outlier=0.05):
+        x = _rt_array(value)
+        params = {'v': v, 'sv': sv, 'a': a, 'z': z, 'sz': sz, 't': t, 'st': st}
+        for name in reg_outcomes:
+            params[name] = _reg_column(params[name], value, x.shape[0])
+        return wfpt.wiener_like_multi(x, params['v'], params['sv'], params['a'], params['z'], params['sz'],
+                                      params['t'], params['st'], 1e-4, reg_outcomes, w_outlier=wp['w_outlier'],
+                                      p_outlier=p_outlier)
+
+    return wiener_multi_like
+
+
+def generate_wfpt_reg_stochastic_class(wiener_params=None, sampling_method='cdf', cdf_range=(-5, 5),
+                                       sampling_dt=1e-4):
+    """hddm/models/hddm_regression.py:15-60: the stochastic of HDDMRegressor.  Same closure signature and
+    defaults (p_outlier=0.05, w_outlier from wiener_params, err fixed at 1e-4, numerics left at
+    wiener_like_multi's own defaults as the reference leaves them)."""
+    wp = dict(DEFAULT_WIENER_PARAMS if wiener_params is None else wiener_params)
+    wiener_multi_like = make_wiener_multi_like(wp)
+
+    def random(self):  # :39-54: one simulated trial per row, each with its own regressed parameters
+        from . import posterior
+        parents = dict(self.parents)
+        reg = list(parents.pop('reg_outcomes'))
+        parents.pop('p_outlier', None)
+        x = _rt_array(self.value)
+        n = x.shape[0]
+        cols = np.empty((7, n))
+        for k, name in enumerate(_PARENTS):
+            cols[k] = _reg_column(parents[name], self.value, n) if name in reg else parents[name]
+        seed = np.random.randint(0, 2 ** 31 - 1)
+        if sampling_method == 'drift':  # hddm/generate.py:187-188
+            rts = posterior.simulate_drift_batch(cols, 1, sampling_dt, seed=seed)[:, 0]
+        elif sampling_method == 'cdf':
+            rts = posterior.gen_rts_from_cdf_batch(cols, 1, cdf_range[0], cdf_range[1], sampling_dt, seed=seed)[:, 0]
+        else:
+            raise TypeError("Sampling method %s not found." % sampling_method)  # hddm/generate.py:195-196
+        out = self.value.copy() if hasattr(self.value, 'copy') else np.array(self.value)
+        if isinstance(out, np.ndarray) and out.dtype.names is None:
+            return rts
+        out['rt'] = rts  # signed, as hddm.utils.flip_errors leaves them (:52)
+        return out
+
+    cls = _stochastic_from_dist('wfpt_reg', wiener_multi_like)
+    cls.random = random
+    return cls
+
+
+wfpt_reg_like = generate_wfpt_reg_stochastic_class(sampling_method='drift')  # hddm/models/hddm_regression.py:62
+wiener_multi_like = make_wiener_multi_like()
 
 
 # ---- reinforcement-learning stochastics ------------------------------------------------------------
@@ -363,13 +448,13 @@ def RL_like(x, v, alpha, pos_alpha, z=0.5, p_outlier=0):
 
 
 def wienerRL_multi_like(value, v, sv, a, z, sz, t, st, alpha, reg_outcomes, p_outlier=0):
-    """hddm/models/hddm_rl_regression.py:25-38: parameters named in reg_outcomes are per-trial vectors
-    (already aligned with value's trials)."""
+    """hddm/models/hddm_rl_regression.py:25-38: parameters named in reg_outcomes are per-trial Series,
+    re-indexed by the node's trials (:32-33) as in wiener_multi_like."""
     response, q, feedback, split_by = _rl_columns(value)
     params = {'v': v, 'sv': sv, 'a': a, 'z': z, 'sz': sz, 't': t, 'st': st, 'alpha': alpha}
+    n = response.shape[0]
     for name in reg_outcomes:
-        col = params[name]
-        params[name] = np.ascontiguousarray(getattr(col, 'values', col), dtype=np.float64)
+        params[name] = _reg_column(params[name], value, n)
     return wfpt.wiener_like_multi_rlddm(_rt_array(value), response, feedback, split_by, q, params['v'], params['sv'],
                                         params['a'], params['z'], params['sz'], params['t'], params['st'],
                                         params['alpha'], 1e-4, reg_outcomes, p_outlier=p_outlier)

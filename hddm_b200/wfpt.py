@@ -373,6 +373,8 @@ class Trials(object):
         segp = None
         if seg is not None:
             seg = np.ascontiguousarray(seg, dtype=np.int64)
+            if seg.shape != (P + 1,):  # the library reads seg[0..P]
+                raise ValueError("seg must have P+1 entries")
             segp = seg.ctypes.data_as(_lib.c_lp)
         out = np.empty(P, dtype=np.double)
         evals = C.c_ulonglong(0)

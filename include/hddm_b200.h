@@ -41,7 +41,9 @@ extern "C" {
 int hddm_b200_version(void);
 const char *hddm_b200_last_error(void);
 /* Bind the calling process to CUDA device `device` (-1: keep the current one) and create the
- * library stream.  Called lazily by every other entry point. */
+ * library stream.  Called lazily by every other entry point.  ONE PROCESS PER GPU: the stream, the
+ * device arena and the kernels' attributes belong to the device bound here; a later init with another
+ * device, or any call made while another device is current, returns HDDM_ERR_ARG. */
 int hddm_b200_init(int device);
 int hddm_b200_device_count(int *count);
 int hddm_b200_synchronize(void);
@@ -54,12 +56,13 @@ int hddm_b200_fp64_peak(int iters, double *flops, float *ms);
  * segments are longer than 512 trials, and as two launches when the sweep has thousands of 8192-trial
  * blocks), 1 = always the generic evaluator, 2 = never the grid evaluator, 3 = grid evaluator in one pass
  * only, 4 = its two passes always in one launch.  All run on the GPU; this exists for A/B parity tests
- * and profiling. */
+ * and profiling, acts on every caller in the process, and is therefore refused (HDDM_ERR_ARG) unless the
+ * environment holds HDDM_B200_DEBUG_KNOBS=1. */
 int hddm_b200_set_kernel(int which);
 /* Trial layout: 1 (default) = entry points whose result is a sum over trials with set-uniform
  * parameters (wiener_like, wiener_like_batch, the trials handle) evaluate the trials ordered by |rt|
  * (within each segment), so the lanes of a warp share the series branch; 0 = caller's order.  The sum
- * is the same up to rounding and deterministic either way. */
+ * is the same up to rounding and deterministic either way.  Debug knob: needs HDDM_B200_DEBUG_KNOBS=1. */
 int hddm_b200_set_sort(int on);
 /* The (branch, K) decision of ftt_01w (src/pdf.pxi:36-54,60) as the piecewise-constant function of
  * normalised time the kernels look up: region r = #{i < n_thr[0] : tt >= thr[i]}, code[r] = +K

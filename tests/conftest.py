@@ -3,6 +3,7 @@ import sys
 
 import pytest
 
+os.environ.setdefault("HDDM_B200_DEBUG_KNOBS", "1")  # the A/B parity tests switch evaluators (include/hddm_b200.h)
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -77,6 +77,26 @@ def test_module_surface_matches_reference_signatures():
         "(v, sv, a, z, sz, t, st, samples=1000, cdf_lb=-6, cdf_ub=6, dt=0.01")
     import hddm_b200
     assert hddm_b200.cdfdif is cdfdif_wrapper  # hddm/__init__.py:16-21
+    # the reference installs TOP-LEVEL modules `wfpt` and `cdfdif_wrapper` (setup.py:6-7, imported bare at
+    # hddm/__init__.py:11-21): the repo root carries shims of those names
+    import importlib
+    top_w, top_c = importlib.import_module("wfpt"), importlib.import_module("cdfdif_wrapper")
+    for fn in REFERENCE_SIGNATURES:
+        owner = top_c if fn.__name__ == "dmat_cdf_array" else top_w
+        assert getattr(owner, fn.__name__) is fn
+    assert top_w.gen_rts_from_cdf is wfpt.gen_rts_from_cdf and top_w.wiener_like_rlddm is wfpt.wiener_like_rlddm
+
+
+def test_debug_knobs_are_gated_by_the_environment(monkeypatch):
+    """hddm_b200_set_kernel / _set_sort act on every caller in the process: refused unless HDDM_B200_DEBUG_KNOBS=1
+    (tests/conftest.py sets it for the A/B parity tests)."""
+    L = _lib.lib()
+    monkeypatch.delenv("HDDM_B200_DEBUG_KNOBS", raising=False)
+    assert L.hddm_b200_set_kernel(0) == _lib.ERR_ARG and b"HDDM_B200_DEBUG_KNOBS" in L.hddm_b200_last_error()
+    assert L.hddm_b200_set_sort(1) == _lib.ERR_ARG
+    monkeypatch.setenv("HDDM_B200_DEBUG_KNOBS", "1")
+    assert L.hddm_b200_set_kernel(0) == _lib.OK and L.hddm_b200_set_sort(1) == _lib.OK
+    assert L.hddm_b200_set_kernel(9) == _lib.ERR_ARG
 
 
 def test_buffer_contract_errors_match_cython():
@@ -200,3 +220,70 @@ def test_sharded_batch_over_gloo_world2(P):
     for r in range(2):
         assert got[r].shape == (P,)
         assert np.array_equal(got[r], want)
+
+
+# ---- host logic of the plugin boundary that needs no GPU (the C call is replaced by a recorder) -------------
+
+def test_regression_closure_reindexes_like_the_reference(monkeypatch):
+    """hddm/models/hddm_regression.py:26-36: every regression outcome is a Series over the WHOLE data set and is
+    re-indexed by the node's own trials (`.loc[value['rt'].index].values`); p_outlier defaults to 0.05 and
+    w_outlier comes from wiener_params.  A full-length plain vector must be refused, not truncated."""
+    import pandas as pd
+    from hddm_b200 import likelihoods as L
+    seen = {}
+
+    def fake_multi(x, v, sv, a, z, sz, t, st, err, multi=None, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-3,
+                   p_outlier=0, w_outlier=0):
+        seen.update(x=x, v=v, a=a, err=err, multi=multi, p_outlier=p_outlier, w_outlier=w_outlier)
+        return -1.0
+
+    monkeypatch.setattr(L.wfpt, "wiener_like_multi", fake_multi)
+    rng = np.random.default_rng(3)
+    data = pd.DataFrame({"rt": rng.uniform(0.4, 2.0, 60) * np.where(rng.random(60) < .7, 1, -1), "subj": np.arange(60) % 3})
+    v_all = pd.Series(rng.normal(1.0, 0.3, 60), index=data.index)
+    a_all = pd.Series(rng.uniform(1.0, 2.0, 60), index=data.index)
+    node = data[data.subj == 1]                     # second subject: rows 1, 4, 7, ...
+    like = L.generate_wfpt_reg_stochastic_class(wiener_params=dict(L.DEFAULT_WIENER_PARAMS, w_outlier=0.2))
+    inst = like(value=node, v=v_all, sv=0.1, a=a_all, z=0.5, sz=0.1, t=0.3, st=0.1, reg_outcomes=["v", "a"])
+    assert inst.logp == -1.0
+    assert np.array_equal(seen["x"], node["rt"].values)
+    assert np.array_equal(seen["v"], v_all.values[1::3]) and np.array_equal(seen["a"], a_all.values[1::3])
+    assert seen["p_outlier"] == 0.05 and seen["w_outlier"] == 0.2 and seen["err"] == 1e-4
+    assert list(seen["multi"]) == ["v", "a"]
+    with pytest.raises(ValueError):                 # un-indexed full-length vector: cannot be aligned
+        L.wiener_multi_like(node, v_all.values, 0.1, 1.5, 0.5, 0.1, 0.3, 0.1, ["v"])
+    assert L.wiener_multi_like(node["rt"].values, v_all.values[1::3], 0.1, 1.5, 0.5, 0.1, 0.3, 0.1, ["v"]) == -1.0
+
+
+def test_trial_cache_identity_content_and_lru(monkeypatch):
+    import gc
+    import pandas as pd
+    from hddm_b200 import likelihoods as L
+
+    class FakeTrials(object):
+        made, closed = 0, 0
+
+        def __init__(self, x):
+            FakeTrials.made += 1
+            self.x = x.copy()
+
+        def close(self):
+            FakeTrials.closed += 1
+
+    monkeypatch.setattr(L.wfpt, "Trials", FakeTrials)
+    cache = L.DeviceTrialCache(max_entries=3)
+    df = pd.DataFrame({"rt": np.random.default_rng(1).random(100)})
+    handles = [cache.get(L._rt_array(df)) for _ in range(4)]
+    assert FakeTrials.made == 1 and all(h is handles[0] for h in handles)
+    a = np.random.default_rng(2).random(50)
+    h1 = cache.get(a)
+    a[0] = 5.0                                       # writeable data changed in place: must not hit
+    h2 = cache.get(a)
+    assert h1 is not h2 and h2.x[0] == 5.0
+    assert cache.get(a.copy()) is h2                 # same content, other array: hit by content
+    for k in range(4):
+        cache.get(np.full(7, float(k)))
+    assert len(cache._handles) == 3 and FakeTrials.closed == FakeTrials.made - 3   # evicted one at a time
+    del df, handles
+    gc.collect()
+    assert not cache._by_id                          # identity entries die with the memory they describe
