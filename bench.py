@@ -2,7 +2,7 @@
 """bench.py -- full-DDM WFPT log-density throughput (evals/s, 1 eval = one trial x parameter set).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--trials T] [--sets P] [--sweep A|B]
+                    [--trials T] [--sets P] [--sweep A|B] [--no-cpu] [--no-sub]
 
 Workload (BASELINE.json configs[3]): batched likelihood sweep, T trials x P
 parameter sets per GPU, full DDM (sv, sz, st), HDDM numerics err=1e-4 n_st=n_sz=2 adaptive
@@ -11,14 +11,27 @@ A step is one pass of the hot path over the whole T x P batch.  Weak scaling: ev
 sets (global batch = N*P sets) and the per-set log-likelihoods are all-gathered over NCCL inside
 the timed region.
 
-Prints ONE JSON line (rank 0).  `value` = device-resident throughput; `e2e` = the same through the
-public host-buffer API (hddm_b200.wfpt.wiener_like_batch: H2D of RTs+parameters and D2H of the
-log-likelihoods inside the timed region); `roofline` = algorithmic FP64 FLOP/s of the likelihood
-kernel against the FP64-FMA peak measured in this run; `cpu_baseline` = the reference's own Cython
-path (oracle/_ref) or its C restatement timed on the host cores on a bounded sample.
---impl reference times only that CPU path.
+Prints ONE JSON line (rank 0):
+  value        device-resident throughput (CUDA events, L2 flushed between steps, max over ranks)
+  e2e          the same through the public host-buffer API (hddm_b200.wfpt.wiener_like_batch: H2D of
+               RTs + parameters and D2H of the log-likelihoods inside the timed region)
+  roofline     EXECUTED work of the likelihood kernel against the FP64-FMA issue peak measured in this
+               run: frac = FP64-pipe thread-instructions per second / (peak FMA per second), <= 1.  The
+               executed instruction count per pdf_sv comes from the ncu capture of THIS kernel source
+               (profiles/ncu_fp64.json, keyed by a hash of hddm_b200/csrc); with a stale capture frac is
+               null.  The SURVEY.md 8(d) figure (the reference's operation sequence, 300 FLOP per pdf_sv)
+               is kept as achieved_reference_accounting.
+  parity       after timing: 16 random sets of the headline launch itself, at full T, against the
+               reference's own compiled code (oracle/_ref; the C port if absent) on the host
+  cpu_baseline the reference's own Cython path timed on the host cores on a bounded sample
+  strong       BASELINE config C4 as worded: P sets GLOBAL, sharded over the N GPUs (strong scaling)
+  mcmc         "MCMC it/s" of the metric: BASELINE config C2 (20 subjects x 200 trials, sv sz st), 1 and
+               16 chains, same sampler on the CUDA likelihood and on the reference's CPU likelihood
+  ppc          BASELINE config C5: posterior predictive draws/s (1e4 draws x 200 trials) over the N GPUs
+--impl reference times only the reference's CPU path (and its MCMC arm).
 """
 import argparse
+import hashlib
 import json
 import math
 import os
@@ -34,11 +47,12 @@ sys.path.insert(0, ROOT)
 
 HDDM = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
 P_OUT, W_OUT = 0.05, 0.1
-FLOP_PER_PDFSV = 300.0   # fixed accounting of the reference's operation sequence
+FLOP_PER_PDFSV = 300.0   # fixed accounting of the REFERENCE's operation sequence
 FLOP_PER_EVAL_TAIL = 28.0
 SETS_PER_CORE = 64       # CPU sample: 20000 trials x 64 sets per core ~ 8-10 s of work per core
 METRIC = "full-DDM wfpt log-density evals/sec (trial x param)"
 UNIT = "evals/s"
+PARITY_SETS = 16
 
 
 def sweep_inputs(T, P, onset, seed):
@@ -54,24 +68,49 @@ def sweep_inputs(T, P, onset, seed):
     return np.ascontiguousarray(x), np.ascontiguousarray(params)
 
 
+def csrc_sha():
+    """Hash of the kernel sources: ties an ncu capture under profiles/ to the code it measured."""
+    h = hashlib.sha1()
+    d = os.path.join(ROOT, "hddm_b200", "csrc")
+    for name in sorted(os.listdir(d)):
+        if name.endswith((".cu", ".cuh")):
+            h.update(name.encode())
+            h.update(open(os.path.join(d, name), "rb").read())
+    return h.hexdigest()[:16]
+
+
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the reference's own implementation on the host cores (oracle/_ref), else the C port.
+
+def _cpu_like(kind):
+    if kind == "reference":
+        from oracle import ref
+        W = ref.wfpt()
+    else:
+        from oracle import oracle as W
+    return lambda x, params, p: W.wiener_like(x, *params[:7, p], HDDM["err"], HDDM["n_st"], HDDM["n_sz"],
+                                              HDDM["use_adaptive"], HDDM["simps_err"], params[7, p], params[8, p])
+
 
 def _cpu_worker(job):
     kind, x, params, lo, hi = job
     sys.path.insert(0, ROOT)
-    if kind == "reference":
-        from oracle import ref
-        W = ref.wfpt()
-        fn = lambda p: W.wiener_like(x, *params[:7, p], HDDM["err"], HDDM["n_st"], HDDM["n_sz"],
-                                     HDDM["use_adaptive"], HDDM["simps_err"], params[7, p], params[8, p])
-    else:
-        from oracle import oracle as O
-        fn = lambda p: O.wiener_like(x, *params[:7, p], HDDM["err"], HDDM["n_st"], HDDM["n_sz"],
-                                     HDDM["use_adaptive"], HDDM["simps_err"], params[7, p], params[8, p])
+    fn = _cpu_like(kind)
     t0 = time.perf_counter()
-    out = [fn(p) for p in range(lo, hi)]
+    out = [fn(x, params, p) for p in range(lo, hi)]
     return time.perf_counter() - t0, out
+
+
+def _cpu_count_worker(job):
+    """pdf_sv evaluations the reference's recursion makes (counted by the C port) for sets lo..hi."""
+    x, params, lo, hi = job
+    sys.path.insert(0, ROOT)
+    from oracle import oracle as O
+    O.pdfsv_calls(reset=True)
+    for p in range(lo, hi):
+        O.wiener_like(x, *params[:7, p], HDDM["err"], HDDM["n_st"], HDDM["n_sz"], HDDM["use_adaptive"],
+                      HDDM["simps_err"], params[7, p], params[8, p])
+    return int(O.pdfsv_calls(reset=True))
 
 
 def cpu_kind():
@@ -87,6 +126,10 @@ def cpu_kind():
     return "port"
 
 
+def host_cores():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+
+
 class CpuArm(object):
     """Times wiener_like of the CPU implementation on `cores` processes over a bounded sample:
     the first t_sample trials x (sets_per_core * cores) parameter sets of the bench workload."""
@@ -94,7 +137,7 @@ class CpuArm(object):
     def __init__(self, x, params, t_sample, sets_per_core, cores=None):
         import multiprocessing as mp
         self.kind = cpu_kind()
-        self.cores = cores or (len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count())
+        self.cores = cores or host_cores()
         self.x = np.ascontiguousarray(x[:t_sample])
         self.sets = min(params.shape[1], sets_per_core * self.cores)
         self.params = np.ascontiguousarray(params[:, :self.sets])
@@ -111,9 +154,95 @@ class CpuArm(object):
         wall = time.perf_counter() - t0
         return wall, self.x.size * sets, res
 
+    def loglik_sets(self, x, params):
+        """wiener_like of every column of params against x, one set per job (the in-bench parity check)."""
+        P = params.shape[1]
+        res = self.pool.map(_cpu_worker, [(self.kind, x, params, p, p + 1) for p in range(P)])
+        return np.array([r[1][0] for r in res])
+
+    def pdfsv_counts(self, x, params):
+        return sum(self.pool.map(_cpu_count_worker, [(x, params, p, p + 1) for p in range(params.shape[1])]))
+
     def close(self):
         self.pool.close()
         self.pool.join()
+
+
+# ---------------------------------------------------------------------------------------------
+# MCMC it/s (BASELINE config C2): the same batched slice-within-Gibbs sampler on both likelihoods.
+
+MCMC_CFG = {"workload": "C2 hierarchical HDDM 20 subjects x 200 trials, include=(sv,sz,st), p_outlier=.05, HDDM "
+                        "numerics; slice-within-Gibbs, 15 stochastic families per iteration (hddm_b200/sampler.py; "
+                        "PyMC 2.3 / kabuki are not installable: reference it/s through PyMC unavailable on this box)"}
+
+
+def mcmc_data(S=20, T=200, seed=20261104, dt=1e-3):
+    """Synthetic subjects drawn from the full DDM itself by an Euler-Maruyama walk in numpy (per trial: drift
+    ~ N(v, sv), start point ~ U(z +- sz/2) a, non-decision time ~ U(t +- st/2)), so that neither the GPU nor
+    the oracle is needed to make the data and both arms see the same vectors."""
+    rng = np.random.default_rng(seed)
+    rts = []
+    for _ in range(S):
+        v, a, t = rng.normal(1.0, 0.5), rng.uniform(1.2, 2.0), rng.uniform(0.25, 0.4)
+        sv, sz, st = 0.8, 0.2, 0.15
+        drift = rng.normal(v, sv, T)
+        y = (0.5 + sz * (rng.random(T) - 0.5)) * a
+        rt = np.zeros(T)
+        alive = np.ones(T, dtype=bool)
+        k = 0
+        while alive.any() and k < 20000:
+            k += 1
+            y = np.where(alive, y + drift * dt + math.sqrt(dt) * rng.standard_normal(T), y)
+            hit = alive & ((y <= 0) | (y >= a))
+            rt[hit] = k * dt
+            alive &= ~hit
+        sign = np.where(y >= a, 1.0, -1.0)
+        rts.append(np.ascontiguousarray((rt + t + st * (rng.random(T) - 0.5)) * sign))
+    return rts
+
+
+def _mcmc_cpu_worker(job):
+    kind, rts, set_node, params, lo, hi = job
+    sys.path.insert(0, ROOT)
+    fn = _cpu_like(kind)
+    return [fn(rts[set_node[p]], params, p) for p in range(lo, hi)]
+
+
+def mcmc_cpu(pool, kind, cores, rts, chains, iters):
+    """Same sampler, reference likelihood: one wiener_like call per observed node as PyMC makes them
+    (hddm/likelihoods.py:54-55), the sets of a proposal round spread over all host cores."""
+    from hddm_b200 import sampler
+
+    def loglik(set_node, params):
+        P = params.shape[1]
+        per = int(math.ceil(P / cores))
+        out = pool.map(_mcmc_cpu_worker, [(kind, rts, set_node, params, lo, min(lo + per, P)) for lo in range(0, P, per)])
+        return np.concatenate([np.asarray(o, dtype=np.float64) for o in out])
+
+    m = sampler.HierarchicalDDM(len(rts), loglik, chains=chains, seed=1)
+    m.sample(1, trace=False)
+    _, dt = m.sample(iters, trace=False)
+    return {"chains": chains, "iters": iters, "it_per_s_per_chain": iters / dt, "chain_it_per_s": chains * iters / dt,
+            "cores": cores, "kind": kind}
+
+
+def mcmc_gpu(rts, chains, iters):
+    from hddm_b200 import likelihoods as L, sampler
+    nodes = L.BatchedNodes(rts)
+    T = rts[0].shape[0]
+    m = sampler.HierarchicalDDM(len(rts), nodes.logp, chains=chains, seed=1)
+    m.sample(5, trace=False)  # warm-up (uploads + sorts the trials once)
+    calls0, sets0 = m.loglik_calls, m.sets_evaluated
+    _, dt = m.sample(iters, trace=False)
+    return {"chains": chains, "iters": iters, "it_per_s_per_chain": iters / dt, "chain_it_per_s": chains * iters / dt,
+            "launches_per_iter": (m.loglik_calls - calls0) / iters, "evals_per_s": (m.sets_evaluated - sets0) * T / dt}
+
+
+def mcmc_reference_record(pool, kind, cores, iters=(10, 2)):
+    rts = mcmc_data()
+    return {"config": MCMC_CFG,
+            "cpu_1_chain": mcmc_cpu(pool, kind, cores, rts, 1, iters[0]),
+            "cpu_16_chains": mcmc_cpu(pool, kind, cores, rts, 16, iters[1])}
 
 
 def run_reference(args):
@@ -130,6 +259,12 @@ def run_reference(args):
         w, e, _ = arm.step()
         total_t += w
         total_e += e
+    mcmc = None
+    if not args.no_sub:
+        try:
+            mcmc = mcmc_reference_record(arm.pool, arm.kind, arm.cores)
+        except Exception as ex:
+            mcmc = {"error": repr(ex)}
     arm.close()
     value = total_e / total_t
     line = {
@@ -139,7 +274,7 @@ def run_reference(args):
         "config": workload_config(args, 1),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": arm.cores, "kind": arm.kind, "sample": arm.sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "mcmc": mcmc,
     }
     print(json.dumps(line))
     return 0
@@ -194,11 +329,67 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def split_sweep(T, P):
+    """launch_like's choice (wfpt_kernels.cu): big sweeps run the two passes as two launches."""
+    return T > 6144 and P * math.ceil(T / 8192.0) >= 2368
+
+
+def roofline_record(args, T, P, k_ms, pdfsv_per_step, peak_tflops):
+    """Executed-work roofline of the likelihood kernel (see the module docstring)."""
+    alg_flop = float(T) * P * FLOP_PER_EVAL_TAIL + pdfsv_per_step * FLOP_PER_PDFSV
+    ref_acc = alg_flop / (k_ms * 1e-3) / 1e12
+    sha = csrc_sha()
+    cap, stale = None, None
+    try:
+        caps = json.load(open(os.path.join(ROOT, "profiles", "ncu_fp64.json")))
+        cap = caps.get("%s:%dx%d" % (args.sweep, T, P))
+    except Exception:
+        caps = None
+    rec = {"bound": "fp64", "unit": "TFLOP/s", "peak": peak_tflops, "achieved": None, "frac": None, "traffic": None,
+           "peak_source": "FP64 FMA probe (k_fp64_peak, 8 independent chains per thread) measured in this run; "
+                          "MEASURED_PEAKS.json has no FP64 entry",
+           "kernel": "k_like_partial first pass + deferred-trial pass (+ k_build_tables, k_like_final)",
+           "kernel_ms": k_ms, "pdf_sv_per_eval": pdfsv_per_step / (float(T) * P),
+           "achieved_reference_accounting": ref_acc,
+           "reference_accounting": "pdf_sv evals x 300 + 28 FLOP per eval (SURVEY.md 8d: the REFERENCE's operation "
+                                   "sequence, not what the kernel executes; not a roofline fraction)",
+           "algorithmic_bytes": int(8 * T + 72 * P),
+           "scratch_bytes": int(8 * P * math.ceil(T / 2048.0) +
+                                ((2 * 1024 + 3072) * P * math.ceil(T / 8192.0) +
+                                 3072 * P * (1 + math.ceil(math.ceil(T / 8192.0) / 8.0)) if split_sweep(T, P) else 0)),
+           "csrc_sha": sha}
+    if cap:
+        stale = cap.get("csrc_sha") != sha
+        inst = float(cap["fp64_thread_inst"])                      # per step of this workload, from ncu
+        per_pdfsv = inst / float(cap["pdf_sv_evals"])
+        flop = float(cap["fp64_flop"]) / float(cap["pdf_sv_evals"])   # FMA = 2, DMUL / DADD / DSETP .. = 1
+        issue_rate = per_pdfsv * pdfsv_per_step / (k_ms * 1e-3)       # FP64-pipe thread-instructions per second
+        frac = issue_rate / (peak_tflops * 1e12 / 2.0)
+        rec.update({
+            "executed_fp64_inst_per_pdf_sv": per_pdfsv, "fused_share": cap.get("fused_share"),
+            "executed_flop_per_pdf_sv": flop,
+            "achieved_executed_flops": flop * pdfsv_per_step / (k_ms * 1e-3) / 1e12,
+            "traffic": cap.get("dram_bytes"), "capture": cap.get("source"), "capture_csrc_sha": cap.get("csrc_sha"),
+            "capture_stale": stale,
+            "fp64_pipe_active_pct_ncu": cap.get("fp64_pipe_pct"),
+            "accounting": "achieved = executed FP64-pipe thread-instructions/s x 2 (every FP64 instruction holds an "
+                          "FMA issue slot) against the FMA peak; instruction count per pdf_sv from the ncu capture "
+                          "named in `capture`, pdf_sv evals counted by the kernel in this run"})
+        if not stale:
+            rec["achieved"] = issue_rate * 2.0 / 1e12
+            rec["frac"] = frac
+        else:
+            rec["frac_from_stale_capture"] = frac
+    else:
+        rec["accounting"] = "no ncu capture of this workload under profiles/ncu_fp64.json: executed fraction unknown"
+    return rec
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
     from hddm_b200 import _lib, wfpt
-    from hddm_b200.batch import DeviceSweep, gather_loglik
+    from hddm_b200.batch import DeviceSweep, gather_loglik, shard_bounds
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the hddm_b200 path has no CPU fallback")
@@ -238,7 +429,30 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def one_step(record=None):
+    def timed(step_fn, steps, warmup):
+        """W warm-up steps, then `steps` timed ones: L2 flush + barrier outside, CUDA events on the launching
+        stream inside; returns (sum of step ms as the max over ranks, per-step kernel ms, last result)."""
+        for _ in range(warmup):
+            out = step_fn(None)
+        barrier()
+        step_ms, kern_ms = [], []
+        for _ in range(steps):
+            flush.fill_(1)  # L2 flush between timed iterations (outside the timed region)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            out = step_fn((k0, k1))
+            e1.record()
+            barrier()
+            step_ms.append(e0.elapsed_time(e1))
+            kern_ms.append(k0.elapsed_time(k1))
+        t = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), kern_ms, out
+
+    def one_step(record):
         if record is not None:
             record[0].record()
         lp = sweep.loglik(d_params, **HDDM)
@@ -246,31 +460,15 @@ def run_ours(args):
             record[1].record()
         return gather_loglik(lp, n_global)
 
-    for _ in range(max(args.warmup, 3)):
-        out = one_step()
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        one_step(None)
     barrier()
     sweep.evals.zero_()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
-
-    step_ms, kern_ms = [], []
-    total_ms = 0.0
-    for _ in range(args.steps):
-        flush.fill_(1)  # L2 flush between timed iterations (outside the timed region)
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        out = one_step((k0, k1))
-        e1.record()
-        barrier()
-        step_ms.append(e0.elapsed_time(e1))
-        kern_ms.append(k0.elapsed_time(k1))
-    t = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
+    total_ms, kern_ms, out = timed(one_step, args.steps, 0)
     pdfsv = int(sweep.evals.item())
     clocks = sampler.stop() if sampler else None
 
@@ -292,60 +490,118 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = evals_per_step * e2e_steps / float(t.item())
-    same = bool(np.array_equal(lp_host, out[rank * P:(rank + 1) * P].cpu().numpy()))
+    headline_local = out[rank * P:(rank + 1) * P].cpu().numpy()
+    same = bool(np.array_equal(lp_host, headline_local))
+
+    # ---- strong scaling of C4 as BASELINE.json words it: P sets GLOBAL, sharded over the ranks
+    strong = None
+    if not args.no_sub:
+        lo, hi = shard_bounds(P, world, rank)
+        d_block = torch.from_numpy(np.ascontiguousarray(params0[:, lo:hi])).to(dev)
+
+        def strong_step(record):
+            if record is not None:
+                record[0].record()
+            lp = sweep.loglik(d_block, **HDDM)
+            if record is not None:
+                record[1].record()
+            return gather_loglik(lp, P)
+
+        s_ms, s_kern, s_out = timed(strong_step, args.steps, 3)
+        strong = {"value": float(T) * P * args.steps / (s_ms * 1e-3), "unit": UNIT, "scaling": "strong",
+                  "global_sets": P, "sets_per_gpu": hi - lo, "ms_per_step": s_ms / args.steps,
+                  "kernel_ms_rank0": float(np.mean(s_kern)),
+                  # the sharded result is rank 0's own single-GPU vector bit for bit, sets computed on other
+                  # GPUs included (each set is summed on one GPU in a fixed order)
+                  "equals_single_gpu_result": bool(np.array_equal(s_out.cpu().numpy(), headline_local))}
+
+    # ---- C5 posterior predictive over the ranks (draws sharded, one all_gather of [D, 15])
+    ppc = None
+    if not args.no_sub:
+        from hddm_b200 import posterior
+        rng = np.random.default_rng(20261104)
+        D, S = 10000, 200
+        pp = np.stack([rng.uniform(-4, 4, D), rng.uniform(0, 2.5, D), rng.uniform(0.5, 2.0, D), rng.uniform(0.4, 0.6, D),
+                       rng.uniform(0, 0.4, D), rng.uniform(0.2, 0.5, D), rng.uniform(0, 0.35, D)])
+        posterior.post_pred_stats_sharded(pp, S, -6, 6, 1e-4, seed=1)
+        best = None
+        for _ in range(3):
+            barrier()
+            t0 = time.perf_counter()
+            table = posterior.post_pred_stats_sharded(pp, S, -6, 6, 1e-4, seed=1)
+            barrier()
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        t = torch.tensor([best], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ppc = {"value": D / float(t.item()), "unit": "draws/s", "scaling": "strong", "ms": 1e3 * float(t.item()),
+               "config": {"workload": "C5: %d posterior draws x %d trials, gen_rts_from_cdf table dt=1e-4 on [-6,6) + "
+                                      "15 gen_ppc_stats statistics per draw, host parameters in, host table out" % (D, S)},
+               "table_sha1": hashlib.sha1(np.nan_to_num(table).tobytes()).hexdigest()}
 
     line = None
     if rank == 0:
         k_ms = float(np.mean(kern_ms))
-        mean_pdfsv = pdfsv / (float(T) * P * args.steps)
-        alg_flop = float(T) * P * (mean_pdfsv * FLOP_PER_PDFSV + FLOP_PER_EVAL_TAIL)
-        achieved = alg_flop / (k_ms * 1e-3) / 1e12
-        traffic, traffic_src = None, None
-        try:  # measured DRAM bytes per launch of this exact workload, if an ncu capture of it is on file
-            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-            ent = tj.get("%s:%dx%d" % (args.sweep, T, P))
-            if ent:
-                traffic, traffic_src = ent["bytes"], ent["source"]
-        except Exception:
-            pass
-        cpu = None
+        pdfsv_per_step = pdfsv / float(args.steps)
+        cpu, parity, mcmc = None, None, None
         try:
             if args.no_cpu:
                 raise RuntimeError("skipped (--no-cpu)")
             arm = CpuArm(x, params, t_sample=min(T, 20000), sets_per_core=SETS_PER_CORE)
             arm.step(sets=arm.cores)
             w, e, res = arm.step()
-            arm.close()
             cpu = {"value": e / w, "unit": UNIT, "cores": arm.cores, "kind": arm.kind, "sample": arm.sample}
+            # ---- parity of the HEADLINE launch itself: random sets at full T against the reference's code
+            try:
+                idx = np.sort(np.random.default_rng(5).choice(P, size=min(PARITY_SETS, P), replace=False))
+                sub = np.ascontiguousarray(params[:, idx])
+                want = arm.loglik_sets(x, sub)
+                got = headline_local[idx]
+                fin = np.isfinite(want)
+                rel = float(np.max(np.abs(got[fin] - want[fin]) / np.abs(want[fin]))) if fin.any() else 0.0
+                _, ev_gpu = wfpt.wiener_like_batch(x, sub, return_evals=True, **HDDM)
+                ev_cpu = arm.pdfsv_counts(x, sub)
+                parity = {"sets": int(idx.size), "trials": T, "against": arm.kind, "max_rel_sum": rel,
+                          "tolerance": 1e-9, "ok": bool(rel <= 1e-9 and np.array_equal(got[~fin], want[~fin])),
+                          "pdf_sv_evals_gpu": int(ev_gpu), "pdf_sv_evals_oracle": int(ev_cpu),
+                          "evals_equal": bool(int(ev_gpu) == int(ev_cpu))}
+            except Exception as ex:
+                parity = {"error": repr(ex)}
+            if not args.no_sub:
+                try:
+                    rts = mcmc_data()
+                    mcmc = {"config": MCMC_CFG,
+                            "gpu_1_chain": mcmc_gpu(rts, 1, args.mcmc_iters),
+                            "gpu_16_chains": mcmc_gpu(rts, 16, max(args.mcmc_iters // 4, 10)),
+                            "cpu_1_chain": mcmc_cpu(arm.pool, arm.kind, arm.cores, rts, 1, 10),
+                            "cpu_16_chains": mcmc_cpu(arm.pool, arm.kind, arm.cores, rts, 16, 2)}
+                except Exception as ex:
+                    mcmc = {"error": repr(ex)}
+            arm.close()
         except Exception as ex:  # the CPU arm is a reported baseline; never let it sink the GPU line
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": repr(ex)}
+            if not args.no_sub and mcmc is None:
+                try:
+                    rts = mcmc_data()
+                    mcmc = {"config": MCMC_CFG, "gpu_1_chain": mcmc_gpu(rts, 1, args.mcmc_iters),
+                            "gpu_16_chains": mcmc_gpu(rts, 16, max(args.mcmc_iters // 4, 10))}
+                except Exception as ex2:
+                    mcmc = {"error": repr(ex2)}
+        launches = (4 if split_sweep(T, P) else 2) * args.steps
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(x.nbytes + params.nbytes),
                     "d2h_bytes_per_step": int(8 * P + 8), "steps": e2e_steps, "bitwise_equal_to_device_path": same},
-            # big sweeps (>= 2368 blocks of 8192 trials): per-set tables, first pass, deferred-trial pass, final sum; else 2
-            "gpu_launches": (4 if (T > 6144 and P * math.ceil(T / 8192.0) >= 2368) else 2) * args.steps,
-            "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s",
-                         "frac": achieved / peak_tflops, "traffic": traffic, "traffic_source": traffic_src,
-                         "algorithmic_bytes": int(8 * T + 72 * P + 8 * P * math.ceil(T / 2048.0) +
-                                                  # split sweep: bit map out and back, per-set tables out and
-                                                  # into every CTA of both launches
-                                                  ((2 * 1024 + 3072) * P * math.ceil(T / 8192.0) +
-                                                   3072 * P * (1 + math.ceil(math.ceil(T / 8192.0) / 8.0))
-                                                   if (T > 6144 and P * math.ceil(T / 8192.0) >= 2368) else 0)),
-                         "fp64_pipe_active_pct_ncu": 57.7,
-                         "kernel": "k_like_partial: first pass + deferred-trial pass (S-A: 97 % + 3 %) + k_build_tables, k_like_final (0.1 %)",
-                         "kernel_ms": k_ms,
-                         "pdf_sv_per_eval": mean_pdfsv,
-                         "accounting": "algorithmic FLOP = pdf_sv evals x 300 + 28 per eval (SURVEY.md 8d); "
-                                       "peak = FP64 FMA probe measured in this run (MEASURED_PEAKS.json has no FP64 entry); "
-                                       "frac > 1 because the kernel executes ~22 FP64 instructions per pdf_sv where the "
-                                       "reference's sequence costs 300 FLOP; fp64_pipe_active_pct_ncu (profiles/r1_v9_summary.md) "
-                                       "is the executed-work utilisation"},
+            # big sweeps: per-set tables, first pass, deferred-trial pass, final sum; else 2
+            "gpu_launches": launches,
+            "roofline": roofline_record(args, T, P, k_ms, pdfsv_per_step, peak_tflops),
+            "parity": parity,
             "cpu_baseline": cpu,
+            "strong": strong, "mcmc": mcmc, "ppc": ppc,
             "clocks": clocks,
         }
         sys.stdout.flush()
@@ -368,7 +624,9 @@ def main():
     ap.add_argument("--trials", type=int, default=100000)
     ap.add_argument("--sets", type=int, default=10000)
     ap.add_argument("--sweep", default="A", choices=["A", "B"])
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--mcmc-iters", type=int, default=100)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity / CPU-MCMC legs (profiling runs)")
+    ap.add_argument("--no-sub", action="store_true", help="skip the strong / mcmc / ppc sub-records")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

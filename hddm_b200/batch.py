@@ -101,6 +101,10 @@ def gather_loglik(local_logp, n_sets, group=None):
     world = dist.get_world_size(group)
     sizes = shard_sizes(n_sets, world)
     width = max(sizes)
+    if min(sizes) == width:  # equal shards: one pre-sized all-gather straight into the result, no pad, no cat
+        gathered = local_logp.new_empty(n_sets)
+        dist.all_gather_into_tensor(gathered, local_logp.contiguous(), group=group)
+        return gathered
     padded = local_logp.new_zeros(width)
     padded[:local_logp.numel()] = local_logp
     gathered = local_logp.new_empty(world * width)
@@ -118,6 +122,10 @@ def gather_rows(local, n_rows, group=None):
     world = dist.get_world_size(group)
     sizes = shard_sizes(n_rows, world)
     width, cols = max(sizes), int(local.shape[1])
+    if min(sizes) == width:
+        gathered = local.new_empty((n_rows, cols))
+        dist.all_gather_into_tensor(gathered, local.contiguous(), group=group)
+        return gathered
     padded = local.new_zeros((width, cols))
     padded[:local.shape[0]] = local
     gathered = local.new_empty((world * width, cols))

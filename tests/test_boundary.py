@@ -199,7 +199,7 @@ def _gloo_worker(rank, world, port, P, q):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("P", [7, 1])
+@pytest.mark.parametrize("P", [7, 1, 8])  # ragged shards, an empty shard, equal shards (the no-pad path)
 def test_sharded_batch_over_gloo_world2(P):
     """N>1 host path: sets split over 2 ranks, all_gather, every rank sees the single-process vector
     bit for bit (each per-set sum is computed on one rank only)."""

@@ -15,6 +15,12 @@ from tests.util import (ATOL_LOG, RTOL_SUM, RTOL_TRIAL, assert_parity, cdf_noise
 pytestmark = pytest.mark.gpu
 
 HDDM = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
+# dmat_cdf_array with sz or st < 1e-3: the reference differences two series 1e-10 apart (src/cdfdif.c:135-148), so
+# its own output moves by `band` under a ONE-ulp nudge of a parameter (tests/util.py:cdf_noise_band); the kernel
+# may differ from the fixture by this many bands there.  Measured need per fixture case: see CDF_BAND_USED below
+# (printed by the test); the factor is twice the largest observed.
+CDF_BAND_FACTOR = 64
+CDF_BAND_USED = {}
 
 
 @pytest.fixture(scope="module")
@@ -104,8 +110,12 @@ def test_cdf_fixtures(W, O, gpu, golden_dir):
         # under a 1-ulp parameter change, see cdf_noise_band): sz/st -> 1e-10 epsilon configurations.
         band = cdf_noise_band(O, x, p[:7], p[7], p[8])
         err = np.abs(got - want)
-        lim = RTOL_TRIAL * np.abs(want) + 1e-14 + 64 * band
+        lim = RTOL_TRIAL * np.abs(want) + 1e-14 + CDF_BAND_FACTOR * band
         assert (err <= lim).all(), "dmat_cdf_array[%d]: err %r lim %r" % (k, err[err > lim], lim[err > lim])
+        over = np.maximum(err - (RTOL_TRIAL * np.abs(want) + 1e-14), 0.0)
+        used = float(np.max(np.where(band > 0, over / np.where(band > 0, band, 1.0), 0.0)))
+        CDF_BAND_USED[k] = max(CDF_BAND_USED.get(k, 0.0), used)
+        print("cdf case %d: %.2f of the reference noise band used (limit %g)" % (k, used, CDF_BAND_FACTOR))
         if p[4] >= 1e-2 and p[6] >= 1e-2:   # full DDM: the plain 1e-10 bar must hold by itself
             assert_parity(got, want, RTOL_TRIAL, atol=1e-14, what="dmat_cdf_array[%d]" % k)
         print("cdf case %d (sz=%.3g st=%.3g): max rel err %.2e, reference noise band %.2e" % (
@@ -160,6 +170,43 @@ def test_per_trial_vs_oracle(W, O, quadrant):
         got = W.pdf_array(x, *args, **HDDM)
         worst = max(worst, assert_parity(got, want, RTOL_TRIAL, what="density quadrant %d set %d" % (quadrant, p)))
     print("quadrant %d: max rel err %.2e" % (quadrant, worst))
+
+
+_ORACLE_1E6 = {}
+
+
+def _oracle_logpdf_job(job):
+    import sys
+    sys.path.insert(0, job[0])
+    from oracle import oracle as Oj
+    _, x, cols = job
+    return [Oj.pdf_array(x, *c, logp=1, p_outlier=0.05, w_outlier=0.1, **HDDM) for c in cols]
+
+
+@pytest.mark.parametrize("quadrant", range(8))
+def test_per_trial_1e6_pairs_per_quadrant(W, O, quadrant):
+    """SURVEY.md 8(d) parity protocol at its stated size: >= 1e6 (trial, set) pairs per quadrant (sv/sz/st
+    on/off), both boundaries, onset-mixed RTs, per-trial log-density <= 1e-10 relative with exact 0 / NaN
+    classes.  The CPU oracle runs over a process pool, once per quadrant (shared by the evaluator variants)."""
+    import multiprocessing as mp
+    import os
+    rng = np.random.default_rng(9500 + quadrant)
+    T, P = 8000, 128
+    par = draw_params(rng, P, quadrant & 1, quadrant & 2, quadrant & 4)
+    x = draw_rts(rng, T, 0.30)
+    if quadrant not in _ORACLE_1E6:
+        root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        cores = max(1, min(len(os.sched_getaffinity(0)), 32))
+        jobs = [(root, x, [list(par[:, p]) for p in range(lo, min(lo + 4, P))]) for lo in range(0, P, 4)]
+        with mp.get_context("spawn").Pool(cores) as pool:
+            _ORACLE_1E6[quadrant] = np.concatenate([np.stack(r) for r in pool.map(_oracle_logpdf_job, jobs)])
+    want = _ORACLE_1E6[quadrant]
+    assert want.shape == (P, T) and want.size >= 1000000
+    worst = 0.0
+    for p in range(P):
+        got = W.pdf_array(x, *list(par[:, p]), logp=1, p_outlier=0.05, w_outlier=0.1, **HDDM)
+        worst = max(worst, assert_parity(got, want[p], RTOL_TRIAL, atol=ATOL_LOG, what="quadrant %d set %d" % (quadrant, p)))
+    print("quadrant %d: %d pairs, max rel err %.2e" % (quadrant, want.size, worst))
 
 
 @pytest.mark.parametrize("numerics", [dict(err=1e-4, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-3),

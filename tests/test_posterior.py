@@ -253,7 +253,7 @@ def _ppc_standin(block, first_draw):
     return np.stack(rows)
 
 
-@pytest.mark.parametrize("D", [9, 1])
+@pytest.mark.parametrize("D", [9, 1, 6])
 def test_sharded_post_pred_stats_over_gloo_world2(D):
     """N>1 host path of the posterior-predictive batch: draws split over 2 ranks, one all_gather of the
     [D, 15] statistics, every rank sees the single-process table bit for bit."""
