@@ -1,4 +1,4 @@
-// sort_kernels.cu -- one-time layout step for the likelihood sweep: trials ordered by |rt|.
+// sort_kernels.cu -- one-time layout step for the likelihood sweep: trials ordered by boundary, then |rt|.
 //
 // The series branch and term count of every decision-time node are monotone in |rt| for a given
 // parameter set (src/pdf.pxi:36-60 through tt = (|rt| - t') / a^2), so when the 32 lanes of a warp
@@ -20,7 +20,13 @@ __global__ void k_abs_keys(const double* __restrict__ x, unsigned long long* __r
 {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-        keys[i] = (unsigned long long)__double_as_longlong(x[i]) & 0x7fffffffffffffffULL;  // NaNs sort last
+    {
+        // boundary-major, then |rt|: lower-boundary trials (x <= 0) first, each group ascending in |x| (NaNs last
+        // in their group), so that a warp's lanes share the boundary as well as the series branch
+        const double v = x[i];
+        keys[i] = ((unsigned long long)__double_as_longlong(v) & 0x7fffffffffffffffULL) |
+                  (v > 0 ? 0x8000000000000000ULL : 0ULL);
+    }
 }
 
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -38,7 +44,7 @@ size_t sort_trials_scratch_bytes(int64_t n, int64_t n_seg)
         const int64_t* off = nullptr;
         cub::DeviceSegmentedSort::StableSortPairs(nullptr, tmp, k, k, v, v, (int)n, (int)n_seg, off, off + 1);
     } else {
-        cub::DeviceRadixSort::SortPairs(nullptr, tmp, k, k, v, v, n, 0, 63);
+        cub::DeviceRadixSort::SortPairs(nullptr, tmp, k, k, v, v, n, 0, 64);
     }
     return 2 * align256((size_t)n * sizeof(unsigned long long)) + align256(tmp) + 256;
 }
@@ -66,7 +72,7 @@ cudaError_t sort_trials(const double* d_x, double* d_sorted, int64_t n, const in
         return cub::DeviceSegmentedSort::StableSortPairs(tmp, tmp_bytes, keys_in, keys_out, d_x, d_sorted, (int)n,
                                                          (int)n_seg, d_seg, d_seg + 1, stream);
     }
-    return cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, d_x, d_sorted, n, 0, 63, stream);
+    return cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, d_x, d_sorted, n, 0, 64, stream);
 }
 
 }  // namespace hddm

@@ -94,6 +94,23 @@ __device__ __forceinline__ double rcp_fast(double y)
     return fma(fma(e, e, e), s, s);
 }
 
+// Per-set constants of the lean first level (wfpt_lean.cuh); part of GridSet so that it is built once per set
+// and copied with it.
+struct alignas(16) LeanSet {
+    double ks[2][4][6];   // k sin(k pi w_i), k = 1..4, at the five first-level start points (padded)
+    double c0h[2], dc0h[2], d2ch[2];  // halves of c(w_0), c(w_1) - c(w_0) and the second difference (GridSet::sw0..d2c)
+    double xhi;           // largest decision time the lean level takes: exponent arguments stay inside [-128, 128]
+    double v2h;           // v^2 / 2
+    double k1;            // pi / (144 a^2)
+    double thr_in, thr_out;  // 15 simps_err / 12 and 15 simps_err
+    // bit patterns of decision-time break points: a node is large-time and inside the comfortable range of
+    // its boundary iff xt >= x_small[b] (compared as SIGNED integers: a negative xt fails); it has >= k terms iff
+    // xt < x_k[k - 2] (k = 2, 3, 4)
+    long long x_small[2];
+    unsigned long long x_k[3];
+    int ok, pad;
+};
+
 template <int KMAX>
 struct alignas(16) GridSet {
     double s5[2][KMAX][6];  // sin(k pi w_i) at the five first-level start points (table nodes 4 i), padded
@@ -125,6 +142,7 @@ struct alignas(16) GridSet {
     double zw, zw6, zw12;  // ub_z - lb_z, and that / 6, / 12 (src/integrate.pxi:99-100,137)
     double tw, tw6, tw12;  // ub_t - lb_t, / 6, / 12
     double raw[7];         // the set's v, sv, a, z, sz, t, st as given (for the out-of-range fallback)
+    LeanSet lean;          // lean.ok == 0 unless the builder was asked for it (first pass of long segments)
 };
 
 // Smallest double X with fl(X / a_sq) >= thr (thr and thr * a_sq normal and positive).

@@ -13,6 +13,11 @@
 #include "wfpt_device.cuh"
 #include "wfpt_fast.cuh"
 #include "wfpt_grid.cuh"
+#include "wfpt_lean.cuh"
+
+#include <cmath>
+#include <mutex>
+#include <vector>
 
 namespace hddm {
 
@@ -55,6 +60,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
     k_like_partial(const __grid_constant__ LikeArgs a)
 {
     constexpr bool TWO_PASS = PASSES != kOnePass;
+    constexpr bool LEAN = GRID && KMAX == 4 && (PASSES == kTwoPass || PASSES == kSplitFirst);
     constexpr int KT = KMAX > 0 ? KMAX : 1;
     __shared__ GridSet<KT> gs;
     WTable<KT>* wt = gs.wt;
@@ -115,11 +121,22 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         uint4* dst = reinterpret_cast<uint4*>(&gs);
         for (int k = threadIdx.x; k < (int)(sizeof(GridSet<KT>) / sizeof(uint4)); k += kLikeThreads) dst[k] = __ldg(src + k);
         __syncthreads();
-    } else if (GRID)
+    } else if (GRID) {
         build_gridset<KT>(gs, par, a.tab,
                           (a.mode != kModeContaminant && p_out >= 0 && p_out <= 1) ? w_out * p_out : 0.0);
-    else if (KMAX > 0)
+        if (LEAN) {  // (k_build_tables does the same for the shared tables)
+            if (threadIdx.x == 0) build_leanset(gs, gs.lean, par[0], a.nm, !per_trial && !multi);
+            __syncthreads();
+        }
+    } else if (KMAX > 0)
         build_wtables<KT>(wt, par[3], par[4]);
+    // Lean first level (wfpt_lean.cuh): the set qualifies (CTA-uniform) -> stage the 2^(i/2048) table
+    __shared__ double ebig[LEAN ? kExpBig : 1];
+    const bool lean_ok = LEAN && gs.lean.ok != 0 && !per_trial && !multi;
+    if (lean_ok) {
+        for (int k = threadIdx.x; k < kExpBig; k += kLikeThreads) ebig[k] = g_exp2_big[k];
+        __syncthreads();
+    }
 
     // Stages of the two-pass flavours (GRID): 0 = first pass, the first 5 x 5 level only (*need: the trial goes
     // to stage 1); 1 = the complete grid evaluator (*need: out of its range, goes to stage 2); 2 = the v2
@@ -185,6 +202,36 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         }
         return need;
     };
+    // Lean first level for one warp round: returns true when the warp took it (then *need is set per lane).
+    auto lean_round = [&](int64_t i, bool in_range, bool* need) {
+        const LeanSet& L = gs.lean;
+        const bool valid = in_range && !(a.cont && a.cont[i] != 0);
+        const double x = valid ? __ldg(a.x + i) : 1.0;
+        const int b = x > 0 ? 1 : 0;
+        const double ax = fabs(x);
+        const double xt0 = ax - gs.tn[0], xt4 = ax - gs.tn[4];
+        // every node large-time and inside the comfortable range (x_small: signed compare, a negative or -NaN
+        // decision time fails; +NaN fails the second test)
+        const bool fit = (__double_as_longlong(xt4) >= L.x_small[b]) & (xt0 <= L.xhi);
+        if (!__all_sync(0xffffffffu, fit | !valid)) return false;
+        const int K = 1 + (int)below(xt4, L.x_k[0]) + (int)below(xt4, L.x_k[1]) + (int)below(xt4, L.x_k[2]);
+        const int wK = __reduce_max_sync(0xffffffffu, valid ? K : 1);
+        bool nd = false;
+        double d;
+        if (wK == 1) d = lean_trial<KT, 1>(gs, L, ebig, b, ax, xt0, xt4, &nd);
+        else if (wK == 2) d = lean_trial<KT, 2>(gs, L, ebig, b, ax, xt0, xt4, &nd);
+        else if (wK == 3) d = lean_trial<KT, 3>(gs, L, ebig, b, ax, xt0, xt4, &nd);
+        else d = lean_trial<KT, 4>(gs, L, ebig, b, ax, xt0, xt4, &nd);
+        nd &= valid;
+        if (valid & !nd) {
+            evals += 25;  // 5 decision times x 5 start points, src/integrate.pxi:131-133,187-198
+            d = d * (1 - p_out) + w_out * p_out;
+            hit_zero |= (d == 0);
+            add_log(d);
+        }
+        *need = nd;
+        return true;
+    };
     if (GRID && TWO_PASS) {
         // Pass 1 evaluates the first 5 x 5 level, which settles almost every trial; the few that need more are
         // queued per warp (ballot order: deterministic) and pass 2 runs them through the complete evaluator with
@@ -241,12 +288,15 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
             const int rounds = (int)((end - begin + kLikeThreads - 1) / kLikeThreads);
             unsigned int* const bits = PASSES == kSplitFirst
                                            ? a.defer_bits + (p * a.chunks + chunk) * words_per_block : nullptr;
+            unsigned int* const my_bits = bits ? bits + warp : nullptr;
             for (int r = 0; r < rounds; ++r) {
                 const int off = r * kLikeThreads + threadIdx.x;
-                const bool need = (begin + off < end) ? score(begin + off, 0) : false;
+                bool need = false;
+                if (!(LEAN && lean_ok && lean_round(begin + off, begin + off < end, &need)))
+                    need = (begin + off < end) ? score(begin + off, 0) : false;
                 const unsigned int votes = __ballot_sync(0xffffffffu, need);
                 if (PASSES == kSplitFirst) {
-                    if (lane == 0) bits[r * (kLikeThreads / 32) + warp] = votes;
+                    if (lane == 0) my_bits[r * (kLikeThreads / 32)] = votes;
                 } else {
                     if (need) queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] = (unsigned short)off;
                     queued += __popc(votes);
@@ -291,6 +341,12 @@ __global__ void __launch_bounds__(kLikeThreads) k_build_tables(const __grid_cons
     const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
     build_gridset<KMAX>(gs, par, a.tab,
                         (a.mode != kModeContaminant && p_out >= 0 && p_out <= 1) ? w_out * p_out : 0.0);
+    if (threadIdx.x == 0) {
+        bool uniform = a.mode != kModeMulti && a.mode != kModeMultiRL;
+        for (int k = 0; k < 7; ++k) uniform &= a.trial_stride[k] == 0;
+        if (KMAX == 4) build_leanset(gs, gs.lean, par[0], a.nm, uniform);
+        else gs.lean.ok = 0;
+    }
     __syncthreads();
     const uint4* src = reinterpret_cast<const uint4*>(&gs);
     uint4* dst = reinterpret_cast<uint4*>(out) + p * (sizeof(GridSet<KMAX>) / sizeof(uint4));
@@ -341,9 +397,27 @@ static void keep_pool_memory()
     done = true;
 }
 
+// 2^(i/2048) for exp_lean, correctly rounded (long-double exp2l, then one rounding), uploaded once per process
+// (one process per GPU: hddm_b200_init).
+static cudaError_t ensure_exp_table()
+{
+    static std::once_flag once;
+    static cudaError_t status = cudaSuccess;
+    std::call_once(once, [] {
+        std::vector<double> t(kExpBig);
+        for (int i = 0; i < kExpBig; ++i) t[i] = (double)exp2l((long double)i / (long double)kExpBig);
+        status = cudaMemcpyToSymbol(g_exp2_big, t.data(), sizeof(double) * kExpBig);
+    });
+    return status;
+}
+
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
 {
     if (a.n_sets <= 0) return cudaSuccess;
+    {
+        const cudaError_t e = ensure_exp_table();
+        if (e != cudaSuccess) return e;
+    }
     LikeArgs b = a;
     b.tab = series_table_for(a.nm.err);
     b.trials_per_block = kTrialsPerBlock;

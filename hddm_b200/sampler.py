@@ -115,6 +115,115 @@ def slice_step(x0, logp, width, rng, left=None, maxiter=MAXITER):
     return x1.reshape(shape), lp1.reshape(shape), calls
 
 
+def slice_step_batched(x0, lp0, logp_many, width, rng, left=None, maxiter=MAXITER, m_out=3, m_shrink=6):
+    """The same slice update as `slice_step` -- same random numbers consumed in the same order, same
+    stepping-out and shrinkage decisions, hence the same result for the same generator state -- with the
+    target evaluated in a few LARGE batches instead of once per probe (one launch per phase instead of one
+    per probe: what makes a single chain fast on a GPU).
+
+    Why speculation is exact: the points a slice step probes do not depend on the values it finds, only on
+    how many probes it takes.  Stepping out visits L - k width and R + k width (k = 0, 1, ...) until the
+    target drops below the level; shrinkage visits a candidate drawn from the current interval, and a
+    REJECTED candidate narrows the interval towards x0 whatever its value was -- so, given the uniforms,
+    the whole sequence of candidates is known in advance and the accepted one is the first above the level.
+
+    `lp0`: the target at x0 (the caller keeps it from the previous update; None: evaluated here).
+    `logp_many(X)`: X is [K, *x0.shape]; returns the target at every row, shape [K, *x0.shape].
+    Returns (x1, lp1, n_batches, picks) with picks = (batch_id[n], row[n]): which batch and row of the
+    shrinkage phase each unit's accepted point came from (row -1: kept x0), batch ids counting the calls of
+    logp_many made here from 0."""
+    x0 = np.asarray(x0, dtype=np.float64)
+    shape = x0.shape
+    x0 = x0.ravel()
+    n = x0.size
+    batches = 0
+
+    def many(rows):  # rows: list of [n] vectors -> [K, n]
+        X = np.stack(rows).reshape((len(rows),) + shape)
+        return np.asarray(logp_many(X), dtype=np.float64).reshape(len(rows), n)
+
+    if lp0 is None:
+        lp0 = many([x0])[0]
+        batches += 1
+    else:
+        lp0 = np.asarray(lp0, dtype=np.float64).ravel()
+    y = lp0 + np.log(rng.random(n))
+    L = x0 - width * rng.random(n)
+    R = L + width
+    if left is not None:
+        L = np.maximum(L, left)
+    grow_l = np.ones(n, dtype=bool) if left is None else (L > left)
+    grow_r = np.ones(n, dtype=bool)
+    it = 0
+    while (grow_l.any() or grow_r.any()) and it < maxiter:
+        # the next m_out rounds of both ends, as slice_step would probe them if every unit kept growing
+        rows = []
+        Lk, Rk, gl = L.copy(), R.copy(), grow_l.copy()
+        for _ in range(m_out):
+            rows.append(np.where(gl, Lk, x0)); rows.append(np.where(grow_r, Rk, x0))
+            Lk = np.where(gl, Lk - width, Lk)
+            if left is not None:
+                hit = Lk <= left
+                Lk = np.where(hit, left, Lk)
+                gl = gl & ~hit
+            Rk = np.where(grow_r, Rk + width, Rk)
+        vals = many(rows)
+        batches += 1
+        for k in range(m_out):  # replay slice_step's loop on the table
+            if not ((grow_l.any() or grow_r.any()) and it < maxiter):
+                break
+            lpl, lpr = vals[2 * k], vals[2 * k + 1]
+            grow_l &= lpl > y
+            grow_r &= lpr > y
+            L = np.where(grow_l, L - width, L)
+            if left is not None:
+                hit = L <= left
+                L = np.where(hit, left, L)
+                grow_l &= ~hit
+            R = np.where(grow_r, R + width, R)
+            it += 1
+    # shrinkage
+    x1 = x0.copy()
+    lp1 = lp0.copy()
+    todo = np.ones(n, dtype=bool)
+    pick_batch = np.full(n, -1, dtype=np.int64)
+    pick_row = np.full(n, -1, dtype=np.int64)
+    it = 0
+    while todo.any() and it < maxiter:
+        state = rng.bit_generator.state
+        U = rng.random((m_shrink, n))  # row r = the draw of round r (the generator fills in C order)
+        cands = []
+        Lk, Rk = L.copy(), R.copy()
+        for r in range(m_shrink):  # candidates of the next rounds if every pending unit keeps being rejected
+            cand = np.where(todo, Lk + (Rk - Lk) * U[r], x1)
+            cands.append(cand)
+            Lk = np.where(todo & (cand < x0), cand, Lk)
+            Rk = np.where(todo & (cand >= x0), cand, Rk)
+        vals = many(cands)
+        used = 0
+        for r in range(m_shrink):
+            if not (todo.any() and it < maxiter):
+                break
+            cand, lpc = cands[r], vals[r]
+            ok = todo & (lpc > y)
+            x1 = np.where(ok, cand, x1)
+            lp1 = np.where(ok, lpc, lp1)
+            pick_batch[ok] = batches
+            pick_row[ok] = r
+            rej = todo & ~ok
+            L = np.where(rej & (cand < x0), cand, L)
+            R = np.where(rej & (cand >= x0), cand, R)
+            todo = rej
+            it += 1
+            used += 1
+        batches += 1
+        if used < m_shrink:  # give back the draws slice_step would not have made
+            rng.bit_generator.state = state
+            if used:
+                rng.random((used, n))
+    return x1.reshape(shape), lp1.reshape(shape), batches, (pick_batch, pick_row)
+
+
 class HierarchicalDDM(object):
     """State + one-sweep update of the hierarchical full DDM, `chains` independent chains at once.
 
