@@ -65,6 +65,8 @@ SIGNATURES = {
     "hddm_trials_wiener_like_batch": (_i, [_v, c_lp, c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_wiener_like_nodes": (_i, [c_dp, _l, c_lp, _l, c_lp, c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_trials_wiener_like_nodes": (_i, [_v, c_lp, _l, c_lp, c_dp, _l] + _NUM + [c_dp, c_up]),
+    "hddm_hier_ddm_sample": (_i, [_v, c_lp, _l, _l, c_dp, c_dp, _d, _d, _d] + _NUM +
+                             [C.POINTER(C.c_uint64), _l, c_dp, c_dp, c_lp]),
     "hddm_wiener_like_batch_scratch": (_l, [_l, _l]),
     "hddm_wiener_like_batch_dev": (_i, [_v, _l, _v, _l, _v, _l] + _NUM + [_v, _v, _v, _v]),
     "hddm_pdf_array_dev": (_i, [_v, _l] + [_d] * 7 + [_d, _i, _i, _i, _i, _d, _d, _d, _v, _v, _v]),

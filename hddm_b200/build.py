@@ -16,8 +16,8 @@ ROOT = os.path.dirname(HERE)
 # HDDM_B200_LIB: load (and build) another file name -- kernel variants built with HDDM_B200_NVCC_EXTRA
 # (space-separated extra nvcc flags, e.g. -DHDDM_LIKE_THREADS=128) can be measured side by side on the GPU box.
 LIB = os.environ.get("HDDM_B200_LIB") or os.path.join(HERE, "libhddm_b200.so")
-SOURCES = ["abi.cu", "abi_rl.cu", "abi_ppc.cu", "rl_kernels.cu", "ppc_kernels.cu", "sim_kernels.cu", "wfpt_kernels.cu", "cdfdif_kernels.cu", "gen_kernels.cu", "series_table.cu", "sort_kernels.cu"]
-HEADERS = ["kernels.cuh", "abi_runtime.cuh", "wfpt_device.cuh", "wfpt_fast.cuh", "wfpt_grid.cuh", os.path.join(ROOT, "include", "hddm_b200.h")]
+SOURCES = ["abi.cu", "abi_rl.cu", "abi_ppc.cu", "abi_mcmc.cu", "rl_kernels.cu", "ppc_kernels.cu", "sim_kernels.cu", "wfpt_kernels.cu", "cdfdif_kernels.cu", "gen_kernels.cu", "series_table.cu", "sort_kernels.cu"]
+HEADERS = ["kernels.cuh", "abi_runtime.cuh", "wfpt_device.cuh", "wfpt_fast.cuh", "wfpt_grid.cuh", "wfpt_lean.cuh", os.path.join(ROOT, "include", "hddm_b200.h")]
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-shared", "-cudart", "static", "--threads", "0"]

@@ -108,7 +108,22 @@ struct alignas(16) LeanSet {
     // xt < x_k[k - 2] (k = 2, 3, 4)
     long long x_small[2];
     unsigned long long x_k[3];
-    int ok, pad;
+    int ok, ok_small;
+    // Small-time nodes (src/pdf.pxi:51-57) with 3 or 4 terms: exp(-(w_i + 2k)^2 / (2 tt)) = A_i R_{k,i} (see grid_node);
+    // every exponent is a per-set constant times 1 / xt.  g_* = a^2 / 2 times w_0^2, w_1^2 - w_0^2, the second
+    // difference of w_i^2; g4_* = 2 a^2 times h_w, 1, 1 - w_4, w_0 + 1.
+    double g_w0sq[2], g_dw1[2], g_d2w[2], g4_hw, g4_one, g4_omw4[2], g4_w0p1[2];
+    double k1s;            // 1 / (144 a^2 sqrt(2 pi))
+    // a node is small-time iff xt < x_edge (the bit pattern behind x_small); it has 4 terms (k = -1..2) iff
+    // xt >= x_s4, else 3 (k = -1..1); the lean small-time node takes xt >= x_lo_small[b] (signed compare)
+    unsigned long long x_edge, x_s4;
+    long long x_lo_small[2];
+    // decision-time nodes of the outer recursion down to its third level (n_st = 2: lb + m st / 16, m = 0..16, by the
+    // reference's midpoint rule, src/integrate.pxi:153-155): the deferred-trial tree of wfpt_lean.cuh
+    double tn17[17];
+    double v;              // the set's drift (boundary flip applied per trial)
+    double xz[2];          // decision times in (0, xz[b]) are negligible nodes (GridSet::xt_zero; 0: none are)
+    double pad17;
 };
 
 template <int KMAX>

@@ -55,12 +55,17 @@ enum : int { kOnePass = 0, kTwoPass = 1, kSplitFirst = 2, kSplitSecond = 3 };
 #ifndef HDDM_SECOND_MIN_BLOCKS
 #define HDDM_SECOND_MIN_BLOCKS 2
 #endif
+#ifndef HDDM_FIRST_MIN_BLOCKS
+#define HDDM_FIRST_MIN_BLOCKS 2
+#endif
 template <int KMAX, bool GRID, int PASSES = kOnePass>
-__global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSecond ? HDDM_SECOND_MIN_BLOCKS : 2) : 1)
+__global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSecond ? HDDM_SECOND_MIN_BLOCKS
+                                                             : (PASSES == kSplitFirst ? HDDM_FIRST_MIN_BLOCKS : 2)) : 1)
     k_like_partial(const __grid_constant__ LikeArgs a)
 {
     constexpr bool TWO_PASS = PASSES != kOnePass;
     constexpr bool LEAN = GRID && KMAX == 4 && (PASSES == kTwoPass || PASSES == kSplitFirst);
+    constexpr bool TREE = GRID && KMAX == 4 && (PASSES == kTwoPass || PASSES == kSplitSecond);  // deferred trials: lean_tree
     constexpr int KT = KMAX > 0 ? KMAX : 1;
     __shared__ GridSet<KT> gs;
     WTable<KT>* wt = gs.wt;
@@ -131,8 +136,9 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
     } else if (KMAX > 0)
         build_wtables<KT>(wt, par[3], par[4]);
     // Lean first level (wfpt_lean.cuh): the set qualifies (CTA-uniform) -> stage the 2^(i/2048) table
-    __shared__ double ebig[LEAN ? kExpBig : 1];
-    const bool lean_ok = LEAN && gs.lean.ok != 0 && !per_trial && !multi;
+    __shared__ double ebig[(LEAN || TREE) ? kExpBig : 1];
+    const bool lean_ok = (LEAN || TREE) && gs.lean.ok != 0 && !per_trial && !multi;
+    const bool tree_ok = TREE && lean_ok && a.nm.n_st == 2;
     if (lean_ok) {
         for (int k = threadIdx.x; k < kExpBig; k += kLikeThreads) ebig[k] = g_exp2_big[k];
         __syncthreads();
@@ -212,16 +218,21 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         const double xt0 = ax - gs.tn[0], xt4 = ax - gs.tn[4];
         // every node large-time and inside the comfortable range (x_small: signed compare, a negative or -NaN
         // decision time fails; +NaN fails the second test)
-        const bool fit = (__double_as_longlong(xt4) >= L.x_small[b]) & (xt0 <= L.xhi);
-        if (!__all_sync(0xffffffffu, fit | !valid)) return false;
-        const int K = 1 + (int)below(xt4, L.x_k[0]) + (int)below(xt4, L.x_k[1]) + (int)below(xt4, L.x_k[2]);
-        const int wK = __reduce_max_sync(0xffffffffu, valid ? K : 1);
+        const long long bits4 = __double_as_longlong(xt4);
+        const bool large = (bits4 >= L.x_small[b]) & (xt0 <= L.xhi);
         bool nd = false;
         double d;
-        if (wK == 1) d = lean_trial<KT, 1>(gs, L, ebig, b, ax, xt0, xt4, &nd);
-        else if (wK == 2) d = lean_trial<KT, 2>(gs, L, ebig, b, ax, xt0, xt4, &nd);
-        else if (wK == 3) d = lean_trial<KT, 3>(gs, L, ebig, b, ax, xt0, xt4, &nd);
-        else d = lean_trial<KT, 4>(gs, L, ebig, b, ax, xt0, xt4, &nd);
+        if (__all_sync(0xffffffffu, large | !valid)) {
+            const int K = 1 + (int)below(xt4, L.x_k[0]) + (int)below(xt4, L.x_k[1]) + (int)below(xt4, L.x_k[2]);
+            const int wK = __reduce_max_sync(0xffffffffu, valid ? K : 1);
+            d = lean_trial_large<KT>(gs, L, ebig, b, ax, xt0, xt4, wK, &nd);
+        } else {
+            // every node small-time (xt0 below the edge) and not too early for the lean small-time node
+            const bool small = (bits4 >= L.x_lo_small[b]) & below(xt0, L.x_edge) & (L.ok_small != 0);
+            if (!__all_sync(0xffffffffu, small | !valid)) return false;
+            const bool any_four = __any_sync(0xffffffffu, valid & !below(xt0, L.x_s4));
+            d = lean_trial_small<KT>(gs, L, ebig, b, ax, xt0, xt4, any_four, &nd);
+        }
         nd &= valid;
         if (valid & !nd) {
             evals += 25;  // 5 decision times x 5 start points, src/integrate.pxi:131-133,187-198
@@ -246,6 +257,33 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         // part of the queue already consumed (ballot order again) and run last.  Returns the new fill (0).
         auto run_queue = [&](int n_queued) {
             __syncwarp();
+            if (TREE && tree_ok) {
+                // Stage "tree" first: the whole outer recursion with lean nodes, lanes in step (wfpt_lean.cuh); what it
+                // cannot settle is compacted, as below, for the complete evaluator
+                int n_left = 0;
+                for (int k0 = 0; k0 < n_queued; k0 += 32) {
+                    const int k = k0 + lane;
+                    const bool live = k < n_queued;
+                    const unsigned short off = live ? queue[warp][k] : 0;
+                    const bool on = live && !(a.cont && a.cont[begin + off] != 0);
+                    const double x = on ? __ldg(a.x + begin + off) : 1.0;
+                    bool fail = false;
+                    int made = 0;
+                    double d = lean_tree<KT>(gs, gs.lean, ebig, x, on, &fail, &made);
+                    fail &= on;
+                    if (on & !fail) {
+                        evals += made;
+                        d = d * (1 - p_out) + w_out * p_out;
+                        hit_zero |= (d == 0);
+                        add_log(d);
+                    }
+                    const unsigned int votes = __ballot_sync(0xffffffffu, fail);
+                    if (fail) queue[warp][n_left + __popc(votes & ((1u << lane) - 1u))] = off;
+                    n_left += __popc(votes);
+                    __syncwarp();
+                }
+                n_queued = n_left;
+            }
             int n_fallback = 0;
             for (int k0 = 0; k0 < n_queued; k0 += 32) {
                 const int k = k0 + lane;
@@ -605,6 +643,19 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters)
     }
     out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
 }
+
+#ifdef HDDM_DEBUG_TREE
+extern "C" int hddm_debug_counters(unsigned long long* out, int reset)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_dbg, sizeof(g_dbg));
+    if (reset) {
+        unsigned long long z[16] = {0};
+        cudaMemcpyToSymbol(g_dbg, z, sizeof(z));
+    }
+    return 0;
+}
+#endif
 
 // Returns achieved FP64 FLOP/s (2 per FMA) of the probe; *ms_out = kernel time.
 double fp64_peak_probe(int iters, float* ms_out, cudaStream_t stream)

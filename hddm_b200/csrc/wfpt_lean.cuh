@@ -25,14 +25,27 @@
 
 namespace hddm {
 
+#ifndef HDDM_LEAN_UNROLL
+#define HDDM_LEAN_UNROLL 5
+#endif
+constexpr int kLeanUnroll = HDDM_LEAN_UNROLL;  // the five decision-time nodes of a lean trial: unrolled (5) or looped (1)
 constexpr int kExpBigBits = 11;
 constexpr int kExpBig = 1 << kExpBigBits;
 // 2^(i/2048), filled once per process by the host (launch_like -> ensure_exp_table) with correctly rounded values.
 __device__ double g_exp2_big[kExpBig];
+#ifdef HDDM_DEBUG_TREE
+__device__ unsigned long long g_dbg[16];
+#define DBG(i, c) do { if (c) atomicAdd(&g_dbg[i], 1ULL); } while (0)
+#else
+#define DBG(i, c) do { } while (0)
+#endif
 
 // exp(x), |x| <= 128 (callers guarantee it): x = n ln2/2048 + r, |r| <= ln2/4096 = 1.7e-4;
 // exp(x) = 2^(n >> 11) T[n & 2047] (1 + r + r^2/2 + r^3/6), truncation r^4/24 < 4e-17, argument reduction
 // with the single constant ln2/2048 (its rounding error times |n| <= 3.8e5 stays below 1.5e-14 |x| / 128).
+// CLAMP: any x <= 128 down to -7e5; results below 2^-1021 come out as exactly 0 (used where such a term is added to
+// one larger by hundreds of orders of magnitude, or multiplies a node that is negligible as a whole).
+template <bool CLAMP = false>
 __device__ __forceinline__ double exp_lean(double x, const double* __restrict__ T)
 {
     const double magic = 6755399441055744.0;  // 1.5 * 2^52
@@ -44,7 +57,10 @@ __device__ __forceinline__ double exp_lean(double x, const double* __restrict__ 
     const double p = fma(r * r, c, r);
     const double tv = T[n & (kExpBig - 1)];
     const double m = fma(tv, p, tv);
-    return __hiloint2double(__double2hiint(m) + ((n >> kExpBigBits) << 20), __double2loint(m));
+    const int e = n >> kExpBigBits;
+    int hi = __double2hiint(m) + (e << 20), lo = __double2loint(m);
+    if (CLAMP && e < -1021) hi = lo = 0;
+    return __hiloint2double(hi, lo);
 }
 
 // Fills L from the GridSet it belongs to; one thread (tid == 0) after build_gridset's final barrier.
@@ -61,6 +77,7 @@ __device__ __noinline__ void build_leanset(GS& G, LeanSet& L, double v, const Nu
         L.d2ch[b] = 0.5 * G.d2c[b];
     }
     L.v2h = 0.5 * (v * v);
+    L.v = v;
     L.k1 = kPi / (144.0 * G.a_sq);
     L.thr_out = 15.0 * nm.simps_err;
     L.thr_in = L.thr_out / 12.0;
@@ -96,9 +113,39 @@ __device__ __noinline__ void build_leanset(GS& G, LeanSet& L, double v, const Nu
     if (v != 0.0 && room / (v * v) < xhi) xhi = room / (v * v);
     if (G.xt_hi < xhi) xhi = G.xt_hi;
     L.xhi = xhi;
+    // small-time side of the window: 3 terms, then 4 terms (err = 1e-4: 3 below tt = 0.0555, 4 up to 0.154)
+    bool small_ok = s >= 1;
+    int first4 = s;  // first small-time region with 4 terms
+    for (int m = 0; m < s && small_ok; ++m) {
+        const int c = G.code[G.region0 + m];
+        small_ok = (c == 3 && first4 == s) || c == 4;
+        if (c == 4 && first4 == s) first4 = m;
+    }
+    L.x_edge = edge;
+    L.x_s4 = first4 == s ? edge : (first4 == 0 ? 0ULL : G.xwin[first4 - 1]);
+    for (int b = 0; b < 2; ++b) {
+        // down to the comfortable range's lower end (the k = 0 term stays above e^-650 there; the others may
+        // underflow: exp_lean<true>)
+        L.x_lo_small[b] = __double_as_longlong(G.xt_lo[b]);
+        L.xz[b] = nm.simps_err >= 1e-200 ? G.xt_zero[b] : 0.0;
+        small_ok = small_ok && G.chain_ok[b] && (unsigned long long)L.x_lo_small[b] < edge;
+        L.g_w0sq[b] = (0.5 * G.a_sq) * G.w0sq[b];
+        L.g_dw1[b] = (0.5 * G.a_sq) * G.dw1[b];
+        L.g_d2w[b] = (0.5 * G.a_sq) * G.d2w[b];
+        L.g4_omw4[b] = (2.0 * G.a_sq) * G.omw4[b];
+        L.g4_w0p1[b] = (2.0 * G.a_sq) * G.w0p1[b];
+    }
+    L.g4_hw = (2.0 * G.a_sq) * G.hw;
+    L.g4_one = 2.0 * G.a_sq;
+    L.k1s = 1.0 / ((144.0 * G.a_sq) * sqrt(2.0 * kPi));
     L.ok = G.ok && G.support && drift_uniform && mono && G.sz != 0 && G.st != 0 && nm.n_sz > 0 && nm.n_st > 0 &&
            nm.simps_err >= 0.0 && asw * asw <= 50.0 && xhi > 0.0 && isfinite(v) && isfinite(L.k1) && L.k1 > 0.0 ? 1 : 0;
-    L.pad = 0;
+    L.ok_small = L.ok && small_ok && isfinite(L.k1s) ? 1 : 0;
+    L.tn17[0] = G.tn[0];
+    L.tn17[16] = G.tn[4];
+    for (int step = 8; step >= 1; step >>= 1)  // (lb + ub) / 2. recursively: tn17[4 j] == tn[j] bit for bit
+        for (int m = step; m < 16; m += 2 * step) L.tn17[m] = (L.tn17[m - step] + L.tn17[m + step]) / 2.;
+    L.pad17 = 0.0;
 }
 
 __device__ __forceinline__ bool below(double xt, unsigned long long edge)
@@ -106,76 +153,377 @@ __device__ __forceinline__ bool below(double xt, unsigned long long edge)
     return (unsigned long long)__double_as_longlong(xt) < edge;
 }
 
-// One trial, all five decision times, at most WK large-time terms per node (WK is the warp's maximum).
-// b: boundary (0 lower / 1 upper); ax = |rt|; xt0 = ax - tn[0] and xt4 = ax - tn[4] have passed the range checks.
-// Returns full_pdf; *need is set when a stop test fails or a series value is negative (the trial is then
-// re-evaluated by the complete evaluator, and the return value is ignored).
-template <int KMAX, int WK>
-__device__ __forceinline__ double lean_trial(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
-                                             int b, double ax, double xt0, double xt4, bool* need)
+// Per-trial constants of the lean evaluators (boundary-dependent table entries, read once per trial).
+struct LeanTrial {
+    int b;
+    double c0h, dc0h, d2ch;
+};
+
+// sv marginal of one decision time (src/pdf.pxi:102) times `scale`, at the five start points:
+// exp(c(w_i) d - v^2 xt d), d = r^2 / 2 -- the numerator is quadratic in i, so the five exponentials are a
+// second-order geometric chain from three.  `shift0/1/2` are added to the three exponents (the small-time node
+// merges its own quadratic chain exp(-w_i^2 / (2 tt)) here).
+template <bool CLAMP>
+__device__ __forceinline__ void lean_chain(const LeanSet& L, const LeanTrial& c, const double* __restrict__ T, double xt,
+                                           double dd, double scale, double shift0, double shift1, double shift2,
+                                           double E[5])
 {
+    E[0] = exp_lean<CLAMP>(fma(fma(-L.v2h, xt, c.c0h), dd, shift0), T) * scale;
+    const double g0 = exp_lean<CLAMP>(fma(c.dc0h, dd, shift1), T);
+    const double r2 = exp_lean<CLAMP>(fma(c.d2ch, dd, shift2), T);
+    E[1] = E[0] * g0;
+    const double g1 = g0 * r2;
+    E[2] = E[1] * g1;
+    const double g2 = g1 * r2;
+    E[3] = E[2] * g2;
+    E[4] = E[3] * (g2 * r2);
+}
+
+// Inner Simpson level over the five start points (src/integrate.pxi:114-141, :99-106) of values p_i E_i.
+__device__ __forceinline__ double lean_inner(const LeanSet& L, const double p[5], const double E[5], bool& bad)
+{
+    const double s04 = fma(p[4], E[4], p[0] * E[0]);
+    const double s13 = fma(p[3], E[3], p[1] * E[1]);
+    const double f2 = p[2] * E[2];
+    const double S = fma(2.0, f2, fma(4.0, s13, s04));
+    const double D = fma(-6.0, f2, fma(4.0, s13, -s04));
+    bad |= !(fabs(D) <= L.thr_in);
+    return fma(D, 1.0 / 15.0, S);
+}
+
+// The same, reporting the stop test instead of folding it into `bad`, and handing out the five values.
+__device__ __forceinline__ double lean_inner_f(const LeanSet& L, const double p[5], const double E[5], bool* pass,
+                                               double f[5])
+{
+#pragma unroll
+    for (int i = 0; i < 5; ++i) f[i] = p[i] * E[i];
+    const double s04 = f[0] + f[4], s13 = f[1] + f[3];
+    const double S = fma(2.0, f[2], fma(4.0, s13, s04));
+    const double D = fma(-6.0, f[2], fma(4.0, s13, -s04));
+    *pass = fabs(D) <= L.thr_in;
+    return fma(D, 1.0 / 15.0, S);
+}
+
+// One LARGE-TIME decision time xt (src/pdf.pxi:59-63) with q = exp(-pi^2 tt / 2): the inner integral I''.
+// wK (warp-uniform): the largest term count among the warp's nodes; a node with fewer terms gets zero coefficients.
+template <int KMAX>
+__device__ __forceinline__ double lean_node_large(const GridSet<KMAX>& G, const LeanSet& L, const LeanTrial& c,
+                                                  const double* __restrict__ T, double xt, double q, int wK, int& neg,
+                                                  bool& bad)
+{
+    // series / q: sin(pi w_i) + sum_{k>=2} q^(k^2-1) k sin(k pi w_i), ascending k (src/pdf.pxi:60-62)
+    double p[5], s[5];
+    load5(L.ks[c.b][0], p);
+    if (wK >= 2) {
+        const double q2 = q * q, q3 = q2 * q;
+        const double e2 = below(xt, L.x_k[0]) ? q3 : 0.0;
+        load5(L.ks[c.b][1], s);
+#pragma unroll
+        for (int i = 0; i < 5; ++i) p[i] = fma(e2, s[i], p[i]);
+        if (wK >= 3) {
+            const double q4 = q2 * q2, q8 = q4 * q4;
+            const double e3 = below(xt, L.x_k[1]) ? q8 : 0.0;
+            load5(L.ks[c.b][2], s);
+#pragma unroll
+            for (int i = 0; i < 5; ++i) p[i] = fma(e3, s[i], p[i]);
+            if (wK >= 4) {
+                const double e4 = below(xt, L.x_k[2]) ? (q8 * q4) * q3 : 0.0;
+                load5(L.ks[c.b][3], s);
+#pragma unroll
+                for (int i = 0; i < 5; ++i) p[i] = fma(e4, s[i], p[i]);
+            }
+        }
+    }
+    neg |= (__double2hiint(p[0]) | __double2hiint(p[1])) | (__double2hiint(p[2]) | __double2hiint(p[3])) |
+           __double2hiint(p[4]);
+    const double r = rsqrt_fast(fma(G.sv_sq, xt, 1.0));
+    double E[5];
+    lean_chain<false>(L, c, T, xt, r * r, (r * q) * L.k1, 0.0, 0.0, 0.0, E);
+    return lean_inner(L, p, E, bad);
+}
+
+// One SMALL-TIME decision time xt (src/pdf.pxi:51-57) with 3 terms (k = -1, 0, 1) or, where `four`, 4 (k = 2 too).
+// p_i = sum_k (w_i + 2k) exp(-(w_i + 2k)^2 g), g = 1 / (2 tt) = a^2 / (2 xt): exp(-(w_i + 2k)^2 g) = A_i R_{k,i} with
+// A_i = exp(-g w_i^2) (quadratic in i: merged into the sv-marginal chain) and R_{k,i} = exp(-4 g k (w_i + k)),
+// geometric in i with ratio eta = exp(-4 g h_w); R_{2,i} = R_{1,i}^2 exp(-8 g).
+template <int KMAX>
+__device__ __forceinline__ double lean_node_small(const GridSet<KMAX>& G, const LeanSet& L, const LeanTrial& c,
+                                                  const double* __restrict__ T, double xt, bool any_four, int& neg,
+                                                  bool& bad, bool* inner_pass = nullptr, double* f5 = nullptr)
+{
+    const int b = c.b;
+    const double rc = rcp_fast(xt);
+    double w[5];
+    load5(G.w5[b], w);
+    const double g4 = L.g4_one * rc;
+    const double eta = exp_lean<true>(-L.g4_hw * rc, T);
+    double Rn = exp_lean<true>(-L.g4_omw4[b] * rc, T);   // k = -1 at i = 4, then down
+    double Rp = exp_lean<true>(-L.g4_w0p1[b] * rc, T);   // k = +1 at i = 0, then up
+    double C2 = 0.0;
+    if (any_four) {  // warp-uniform
+        const double C = exp_lean<true>(-g4, T);
+        C2 = below(xt, L.x_s4) ? 0.0 : C * C;
+    }
+    double t[5];
+#pragma unroll
+    for (int i = 4; i >= 0; --i) {  // the reference adds k ascending: k = -1 first
+        t[i] = fma(w[i] - 2.0, Rn, w[i]);
+        if (i > 0) Rn *= eta;
+    }
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        t[i] = fma(w[i] + 2.0, Rp, t[i]);
+        if (any_four) t[i] = fma(w[i] + 4.0, (Rp * Rp) * C2, t[i]);
+        if (i < 4) Rp *= eta;
+    }
+    neg |= (__double2hiint(t[0]) | __double2hiint(t[1])) | (__double2hiint(t[2]) | __double2hiint(t[3])) |
+           __double2hiint(t[4]);
+    const double r = rsqrt_fast(fma(G.sv_sq, xt, 1.0));
+    // 1 / sqrt(2 pi tt^3) = u sqrt(u) / sqrt(2 pi), u = 1 / tt = a^2 / xt
+    const double u = G.a_sq * rc;
+    const double post = (u * u) * rsqrt_fast(u);
+    double E[5];
+    lean_chain<true>(L, c, T, xt, r * r, (post * r) * L.k1s, -L.g_w0sq[b] * rc, -L.g_dw1[b] * rc, -L.g_d2w[b] * rc, E);
+    if (f5) return lean_inner_f(L, t, E, inner_pass, f5);
+    return lean_inner(L, t, E, bad);
+}
+
+// pdf_sv'' at ONE start point w of a small-time decision time (the deeper levels of the inner recursion,
+// src/integrate.pxi:99-112): the same terms as lean_node_small without the chains.
+template <int KMAX>
+__device__ __forceinline__ double lean_point_small(const GridSet<KMAX>& G, const LeanSet& L, const LeanTrial& c,
+                                                   const double* __restrict__ T, double xt, double w, double rc,
+                                                   double dd, double scale, double C2, int& neg)
+{
+    const double g4 = L.g4_one * rc, g = 0.25 * g4;
+    const double Rn = exp_lean<true>(-g4 * (1.0 - w), T), Rp = exp_lean<true>(-g4 * (w + 1.0), T);
+    double t = fma(w - 2.0, Rn, w);
+    t = fma(w + 2.0, Rp, t);
+    t = fma(w + 4.0, (Rp * Rp) * C2, t);
+    neg |= __double2hiint(t);
+    const double vb = c.b ? -L.v : L.v;
+    const double asw = (G.a * G.sv) * w;
+    const double ch = 0.5 * fma(asw, asw, -((2.0 * G.a) * vb) * w);
+    return (t * scale) * exp_lean<true>(fma(fma(-L.v2h, xt, ch), dd, -(g * w) * w), T);
+}
+
+// The inner recursion below its first level for a small-time decision time whose stop test failed: f5 = the five
+// first-level values (table nodes 0, 4, 8, 12, 16).  Same tree as the outer one (n_sz == 2).  *extra += pdf_sv made.
+template <int KMAX>
+__device__ __noinline__ double lean_refine_small(const GridSet<KMAX>& G, const LeanSet& L, const LeanTrial& c,
+                                                 const double* __restrict__ T, double xt, const double f5[5], int& neg,
+                                                 int* extra)
+{
+    const double rc = rcp_fast(xt);
+    const double r = rsqrt_fast(fma(G.sv_sq, xt, 1.0));
+    const double u = G.a_sq * rc;
+    const double scale = (((u * u) * rsqrt_fast(u)) * r) * L.k1s, dd = r * r;
+    double C2 = 0.0;
+    if (!below(xt, L.x_s4)) {
+        const double C = exp_lean<true>(-L.g4_one * rc, T);
+        C2 = C * C;
+    }
+    const double* wn = G.wt[c.b].w;
+    auto pt = [&](int m) { return lean_point_small<KMAX>(G, L, c, T, xt, wn[m], rc, dd, scale, C2, neg); };
+    auto simpson = [&](double y0, double y1, double y2, double y3, double y4, bool* pass) {
+        const double s04 = y0 + y4, s13 = y1 + y3;
+        const double S = fma(2.0, y2, fma(4.0, s13, s04));
+        const double D = fma(-6.0, y2, fma(4.0, s13, -s04));
+        *pass = fabs(D) <= L.thr_in;
+        return fma(D, 1.0 / 15.0, S);
+    };
+    double Z[17];
+    Z[0] = f5[0]; Z[4] = f5[1]; Z[8] = f5[2]; Z[12] = f5[3]; Z[16] = f5[4];
+#pragma unroll 1
+    for (int m = 2; m < 16; m += 4) Z[m] = pt(m);
+    int made = 4;
+    bool lok, rok, dummy;
+    double left = 0.5 * simpson(Z[0], Z[2], Z[4], Z[6], Z[8], &lok);
+    double right = 0.5 * simpson(Z[8], Z[10], Z[12], Z[14], Z[16], &rok);
+#pragma unroll 1
+    for (int m = 1; m < 16; m += 2) {
+        if (m < 8 ? lok : rok) continue;
+        Z[m] = pt(m);
+        ++made;
+    }
+    if (!lok) left = 0.25 * simpson(Z[0], Z[1], Z[2], Z[3], Z[4], &dummy) + 0.25 * simpson(Z[4], Z[5], Z[6], Z[7], Z[8], &dummy);
+    if (!rok) right = 0.25 * simpson(Z[8], Z[9], Z[10], Z[11], Z[12], &dummy) + 0.25 * simpson(Z[12], Z[13], Z[14], Z[15], Z[16], &dummy);
+    *extra += made;
+    return left + right;
+}
+
+// Outer Simpson level over the five decision times (src/integrate.pxi:143-178).
+__device__ __forceinline__ double lean_outer(const LeanSet& L, const double I[5], bool& bad)
+{
+    const double s04 = I[0] + I[4], s13 = I[1] + I[3];
+    const double S = fma(2.0, I[2], fma(4.0, s13, s04));
+    const double D = fma(-6.0, I[2], fma(4.0, s13, -s04));
+    bad |= !(fabs(D) <= L.thr_out);
+    return fma(D, 1.0 / 15.0, S);
+}
+
+__device__ __forceinline__ LeanTrial lean_begin(const LeanSet& L, int b)
+{
+    LeanTrial c;
+    c.b = b;
+    c.c0h = L.c0h[b];
+    c.dc0h = L.dc0h[b];
+    c.d2ch = L.d2ch[b];
+    return c;
+}
+
+// One trial, all five decision times large-time with at most wK terms (warp-uniform).  b: boundary (0 lower /
+// 1 upper); ax = |rt|; xt0 = ax - tn[0] and xt4 = ax - tn[4] have passed the range checks.  Returns full_pdf; *need
+// is set when a stop test fails or a series value is negative (the trial is then re-evaluated by the complete
+// evaluator and the return value ignored).
+template <int KMAX>
+__device__ __forceinline__ double lean_trial_large(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
+                                                   int b, double ax, double xt0, double xt4, int wK, bool* need)
+{
+    const LeanTrial c = lean_begin(L, b);
     const double q0 = exp_lean(G.qk * xt0, T);
-    const double c0h = L.c0h[b], dc0h = L.dc0h[b], d2ch = L.d2ch[b];
+    int neg = 0;
+    bool bad = false;
+    double out;
+    if (kLeanUnroll == 5) {
+        double I[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const double xt = j == 0 ? xt0 : (j == 4 ? xt4 : ax - G.tn[j]);
+            const double q = j == 0 ? q0 : q0 * G.rho[j];
+            I[j] = lean_node_large<KMAX>(G, L, c, T, xt, q, wK, neg, bad);
+        }
+        out = lean_outer(L, I, bad);
+    } else {  // looped: S'' and D'' of the outer level accumulate with the Simpson weights 1 4 2 4 1 / -1 4 -6 4 -1
+        double S = 0.0, D = 0.0;
+#pragma unroll 1
+        for (int j = 0; j < 5; ++j) {
+            const double xt = ax - G.tn[j];
+            const double v = lean_node_large<KMAX>(G, L, c, T, xt, q0 * G.rho[j], wK, neg, bad);
+            const double ws = (j & 1) ? 4.0 : (j == 2 ? 2.0 : 1.0), wd = (j & 1) ? 4.0 : (j == 2 ? -6.0 : -1.0);
+            S = fma(ws, v, S);
+            D = fma(wd, v, D);
+        }
+        bad |= !(fabs(D) <= L.thr_out);
+        out = fma(D, 1.0 / 15.0, S);
+    }
+    *need = bad | (neg < 0);
+    return out;
+}
+
+// The same with all five decision times small-time.
+template <int KMAX>
+__device__ __forceinline__ double lean_trial_small(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
+                                                   int b, double ax, double xt0, double xt4, bool any_four, bool* need)
+{
+    const LeanTrial c = lean_begin(L, b);
     double I[5];
     int neg = 0;
     bool bad = false;
 #pragma unroll
     for (int j = 0; j < 5; ++j) {
         const double xt = j == 0 ? xt0 : (j == 4 ? xt4 : ax - G.tn[j]);
-        const double q = j == 0 ? q0 : q0 * G.rho[j];
-        // series / q: sin(pi w_i) + sum_{k>=2} q^(k^2-1) k sin(k pi w_i), ascending k (src/pdf.pxi:60-62)
-        double p[5], s[5];
-        load5(L.ks[b][0], p);
-        if (WK >= 2) {
-            const double q2 = q * q, q3 = q2 * q;
-            const double e2 = below(xt, L.x_k[0]) ? q3 : 0.0;
-            load5(L.ks[b][1], s);
-#pragma unroll
-            for (int i = 0; i < 5; ++i) p[i] = fma(e2, s[i], p[i]);
-            if (WK >= 3) {
-                const double q4 = q2 * q2, q8 = q4 * q4;
-                const double e3 = below(xt, L.x_k[1]) ? q8 : 0.0;
-                load5(L.ks[b][2], s);
-#pragma unroll
-                for (int i = 0; i < 5; ++i) p[i] = fma(e3, s[i], p[i]);
-                if (WK >= 4) {
-                    const double q15 = (q8 * q4) * q3;
-                    const double e4 = below(xt, L.x_k[2]) ? q15 : 0.0;
-                    load5(L.ks[b][3], s);
-#pragma unroll
-                    for (int i = 0; i < 5; ++i) p[i] = fma(e4, s[i], p[i]);
-                }
-            }
-        }
-        neg |= (__double2hiint(p[0]) | __double2hiint(p[1])) | (__double2hiint(p[2]) | __double2hiint(p[3])) |
-               __double2hiint(p[4]);
-        // sv marginal (src/pdf.pxi:102): exp(c(w_i) d - v^2 xt d) r / a^2, d = 1 / (2 (sv^2 xt + 1)) = r^2 / 2; the
-        // numerator is quadratic in i, so the five exponentials are a second-order geometric chain from three
-        const double r = rsqrt_fast(fma(G.sv_sq, xt, 1.0));
-        const double dd = r * r;
-        const double E0 = exp_lean(fma(-L.v2h, xt, c0h) * dd, T) * ((r * q) * L.k1);
-        const double g0 = exp_lean(dc0h * dd, T);
-        const double r2 = exp_lean(d2ch * dd, T);
-        const double E1 = E0 * g0, g1 = g0 * r2;
-        const double E2 = E1 * g1, g2 = g1 * r2;
-        const double E3 = E2 * g2, g3 = g2 * r2;
-        const double E4 = E3 * g3;
-        // inner Simpson level over the five start points (src/integrate.pxi:114-141, :99-106)
-        const double s04 = fma(p[4], E4, p[0] * E0);
-        const double s13 = fma(p[3], E3, p[1] * E1);
-        const double f2 = p[2] * E2;
-        const double S = fma(2.0, f2, fma(4.0, s13, s04));
-        const double D = fma(-6.0, f2, fma(4.0, s13, -s04));
-        bad |= !(fabs(D) <= L.thr_in);
-        I[j] = fma(D, 1.0 / 15.0, S);
+        I[j] = lean_node_small<KMAX>(G, L, c, T, xt, any_four, neg, bad);
     }
-    // outer Simpson level over the five decision times (src/integrate.pxi:143-178)
-    const double s04 = I[0] + I[4], s13 = I[1] + I[3];
-    const double S = fma(2.0, I[2], fma(4.0, s13, s04));
-    const double D = fma(-6.0, I[2], fma(4.0, s13, -s04));
-    bad |= !(fabs(D) <= L.thr_out);
+    const double out = lean_outer(L, I, bad);
     *need = bad | (neg < 0);
-    return fma(D, 1.0 / 15.0, S);
+    return out;
+}
+
+// Deferred trials, HDDM numerics (n_st == 2): the whole outer recursion of src/integrate.pxi:143-178 for one trial,
+// lane-synchronous.  Its decision-time nodes are per-set constants (tn17); a lane evaluates a node only if the
+// reference's recursion reaches it (first level m = 0,4,8,12,16; the halves add m = 2,6 / 10,14 when the top stop
+// test fails; their quarters add the odd m when a half's test -- same threshold on D'', the tolerance halves with the
+// interval, :107-112 -- fails; the quarters return without a test, bottom == 0).  A node is 0 when its decision time
+// is not positive (src/pdf.pxi:92-93), else a lean small- or large-time node.  Anything else (a node below the
+// comfortable range, an inner stop test that fails, a negative series value, NaN) sets *fail: the trial goes on to
+// the complete evaluator.  *n_evals = pdf_sv evaluations made (5 per node + those of inner refinements).
+template <int KMAX>
+__device__ __noinline__ double lean_tree(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
+                                         double x, bool active, bool* fail, int* n_evals)
+{
+    const int b = x > 0 ? 1 : 0;
+    const double ax = fabs(x);
+    const LeanTrial c = lean_begin(L, b);
+    bool bad = !(ax == ax) || !(ax - G.t_onset >= 0);  // NaN; before the onset (full_pdf returns 0 without a node)
+    DBG(0, active); DBG(2, active & bad);
+    int neg = 0, count = 0, extra = 0;
+    bool saw_tiny = false;
+    // value of node m for the lanes in `want` (others keep 0); warp-convergent
+    auto node = [&](int m, bool want) {
+        const double xt = ax - L.tn17[m];
+        const bool pos = xt > 0.0;
+        const long long bits = __double_as_longlong(xt);
+        // a decision time in (0, xz): the node is negligible (GridSet::xt_zero) and taken as 0; checked at the end
+        const bool tiny = want & pos & (xt < L.xz[b]);
+        saw_tiny |= tiny;
+        const bool small = want & pos & !tiny & (bits < (long long)L.x_edge);
+        const bool large = want & pos & !tiny & !small;
+        DBG(3, small & !bad & !((bits >= L.x_lo_small[b]) & (L.ok_small != 0)));
+        DBG(4, large & !bad & !(xt <= L.xhi));
+        bad |= small & !((bits >= L.x_lo_small[b]) & (L.ok_small != 0));
+        bad |= large & !(xt <= L.xhi);
+        const bool do_small = small & !bad, do_large = large & !bad;
+        const bool bad_before = bad;
+        const int K = 1 + (int)below(xt, L.x_k[0]) + (int)below(xt, L.x_k[1]) + (int)below(xt, L.x_k[2]);
+        const int wK = __reduce_max_sync(0xffffffffu, do_large ? K : 1);
+        const bool any_four = __any_sync(0xffffffffu, do_small & !below(xt, L.x_s4));
+        double val = 0.0;
+        if (do_large) val = lean_node_large<KMAX>(G, L, c, T, xt, exp_lean(G.qk * xt, T), wK, neg, bad);
+        if (do_small) {
+            bool pass = true;
+            double f5[5];
+            val = lean_node_small<KMAX>(G, L, c, T, xt, any_four, neg, bad, &pass, f5);
+            if (!pass) val = lean_refine_small<KMAX>(G, L, c, T, xt, f5, neg, &extra);  // (NaN values fail every test)
+        }
+        DBG(5, do_large & bad & !bad_before); DBG(6, do_small & bad & !bad_before); DBG(7, want);
+        count += want ? 1 : 0;
+        return val;
+    };
+    // Simpson on five equally spaced values: S'' + D'' / 15 and whether the stop test passes
+    auto simpson = [&](double y0, double y1, double y2, double y3, double y4, bool* pass) {
+        const double s04 = y0 + y4, s13 = y1 + y3;
+        const double S = fma(2.0, y2, fma(4.0, s13, s04));
+        const double D = fma(-6.0, y2, fma(4.0, s13, -s04));
+        *pass = fabs(D) <= L.thr_out;
+        return fma(D, 1.0 / 15.0, S);
+    };
+    double I[17];  // (indexed in loops: lives in local memory -- 17 words against ~100 instructions per node)
+#pragma unroll
+    for (int m = 0; m < 17; ++m) I[m] = 0.0;
+    active &= !bad;
+#pragma unroll 1
+    for (int m = 0; m < 17; m += 4) I[m] = node(m, active);
+    bool top_ok;
+    double out = simpson(I[0], I[4], I[8], I[12], I[16], &top_ok);
+    const bool refine = active & !top_ok & !bad;  // (a NaN D fails the test, as in the reference)
+    if (__any_sync(0xffffffffu, refine)) {
+#pragma unroll 1
+        for (int m = 2; m < 16; m += 4) I[m] = node(m, refine);
+        bool left_ok, right_ok;
+        double left = 0.5 * simpson(I[0], I[2], I[4], I[6], I[8], &left_ok);
+        double right = 0.5 * simpson(I[8], I[10], I[12], I[14], I[16], &right_ok);
+        const bool ql = refine & !left_ok & !bad, qr = refine & !right_ok & !bad;
+#pragma unroll 1
+        for (int m = 1; m < 16; m += 2) {
+            const bool want = m < 8 ? ql : qr;
+            if (!__any_sync(0xffffffffu, want)) continue;
+            I[m] = node(m, want);
+        }
+        bool dummy;
+        if (ql) left = 0.25 * simpson(I[0], I[1], I[2], I[3], I[4], &dummy) +
+                       0.25 * simpson(I[4], I[5], I[6], I[7], I[8], &dummy);
+        if (qr) right = 0.25 * simpson(I[8], I[9], I[10], I[11], I[12], &dummy) +
+                        0.25 * simpson(I[12], I[13], I[14], I[15], I[16], &dummy);
+        if (refine) out = left + right;
+    }
+    // negligible nodes were taken as 0: fine unless the whole result is that small too and no outlier term swamps it
+    if (saw_tiny && !(fabs(out) > 1e-150) && !(fabs(out) <= 1e-150 && G.mix_floor > 1e-120)) bad = true;
+    if (!(out == out)) bad = true;  // NaN: let the complete evaluator reproduce the reference's NaN semantics
+    DBG(1, active & (bad | (neg < 0))); DBG(8, active & (neg < 0)); DBG(9, refine);
+    *fail = bad | (neg < 0);
+    *n_evals = 5 * count + extra;
+    return out;
 }
 
 }  // namespace hddm

@@ -229,9 +229,14 @@ class HierarchicalDDM(object):
 
     loglik(set_node, params) evaluates P = chains * subjects sets in one call."""
 
-    def __init__(self, n_subjects, loglik, chains=1, z=0.5, p_outlier=0.05, w_outlier=0.1, seed=0):
+    def __init__(self, n_subjects, loglik, chains=1, z=0.5, p_outlier=0.05, w_outlier=0.1, seed=0, batched=True):
+        """batched=True: every slice step evaluates its probes speculatively in a few large launches
+        (slice_step_batched) and the node likelihoods of the current state are carried from update to update;
+        batched=False: one launch per probe (slice_step).  Both give the same chain for the same seed."""
         self.S, self.C = int(n_subjects), int(chains)
         self.loglik = loglik
+        self.batched = bool(batched)
+        self.node_ll = None  # [C, S] log-likelihood of every observed node at the current state (batched mode)
         self.z, self.p_outlier, self.w_outlier = z, p_outlier, w_outlier
         self.rng = np.random.default_rng(seed)
         C, S = self.C, self.S
@@ -257,6 +262,26 @@ class HierarchicalDDM(object):
         self.sets_evaluated += C * S
         return np.asarray(self.loglik(self.set_node, params), dtype=np.float64).reshape(C, S)
 
+    # -- the same for K candidate values of ONE parameter at once: X is [K, C, S] (subject-level) or [K, C]
+    #    (group-only, shared by the chain's subjects); one launch of K * C * S sets -> [K, C, S]
+    def _node_loglik_many(self, name, X):
+        C, S = self.C, self.S
+        K = X.shape[0]
+        base = np.empty((9, C * S))
+        bc = lambda a: np.broadcast_to(np.asarray(a, dtype=np.float64).reshape(C, -1), (C, S)).ravel()
+        cur = lambda n: self.subj[n] if n in self.subj else self.g[n]
+        base[0] = bc(cur('v')); base[1] = bc(cur('sv')); base[2] = bc(cur('a')); base[3] = self.z
+        base[4] = bc(cur('sz')); base[5] = bc(cur('t')); base[6] = bc(cur('st'))
+        base[7] = self.p_outlier; base[8] = self.w_outlier
+        params = np.empty((9, K, C * S))
+        params[:] = base[:, None, :]
+        row = {'v': 0, 'sv': 1, 'a': 2, 'sz': 4, 't': 5, 'st': 6}[name]
+        params[row] = np.broadcast_to(X.reshape(K, C, -1), (K, C, S)).reshape(K, C * S)
+        self.loglik_calls += 1
+        self.sets_evaluated += K * C * S
+        out = self.loglik(np.tile(self.set_node, K), params.reshape(9, K * C * S))
+        return np.asarray(out, dtype=np.float64).reshape(K, C, S)
+
     def _subj_prior(self, name, x, g=None, std=None):
         g = self.g[name][:, None] if g is None else g
         std = self.g[name + '_std'][:, None] if std is None else std
@@ -266,6 +291,8 @@ class HierarchicalDDM(object):
 
     def sweep(self):
         """One MCMC iteration: every stochastic of the model is updated once."""
+        if self.batched:
+            return self._sweep_batched()
         rng = self.rng
         # subject-level parameters: chains x subjects targets in lock-step
         for name in ('v', 'a', 't'):
@@ -289,6 +316,62 @@ class HierarchicalDDM(object):
                                               _halfnorm_logpdf(s, std_sd[name]))
             self.g[name + '_std'], _, _ = slice_step(self.g[name + '_std'], ts, SLICE_WIDTHS[name + '_std'], rng,
                                                      left=0.0)
+
+    def _sweep_batched(self):
+        """The same iteration as sweep() with batched=False -- same update order, same random numbers, same
+        decisions -- in about two launches per likelihood-bearing stochastic family instead of one per probe."""
+        rng = self.rng
+        C, S = self.C, self.S
+        if self.node_ll is None:
+            self.node_ll = np.ascontiguousarray(self._node_loglik())
+
+        def take(payloads, picks, per_chain):
+            """Carry the node likelihoods of the accepted points into the cache."""
+            pb, pr = picks
+            if per_chain:  # unit = chain: the whole row of subjects moves
+                for c in np.nonzero(pr >= 0)[0]:
+                    self.node_ll[c] = payloads[pb[c]][pr[c], c]
+            else:          # unit = (chain, subject)
+                pb, pr = pb.reshape(C, S), pr.reshape(C, S)
+                cs, ss = np.nonzero(pr >= 0)
+                for c, s_ in zip(cs, ss):
+                    self.node_ll[c, s_] = payloads[pb[c, s_]][pr[c, s_], c, s_]
+
+        for name in ('v', 'a', 't'):
+            payloads = []
+
+            def many(X, name=name, payloads=payloads):  # X: [K, C, S]
+                ll = self._node_loglik_many(name, X)
+                payloads.append(ll)
+                return ll + self._subj_prior(name, X)
+
+            lp0 = self.node_ll + self._subj_prior(name, self.subj[name])
+            self.subj[name], _, _, picks = slice_step_batched(self.subj[name], lp0, many, SUBJ_WIDTHS[name], rng)
+            take(payloads, picks, per_chain=False)
+        priors = {'sv': lambda x: _halfnorm_logpdf(x, 2.0), 'sz': lambda x: _beta_logpdf(x, 1.0, 3.0),
+                  'st': lambda x: _halfnorm_logpdf(x, 0.3)}
+        for name in ('sv', 'sz', 'st'):
+            payloads = []
+
+            def many(X, name=name, payloads=payloads):  # X: [K, C]
+                ll = self._node_loglik_many(name, X)
+                payloads.append(ll)
+                return ll.sum(axis=2) + priors[name](X)
+
+            lp0 = self.node_ll.sum(axis=1) + priors[name](self.g[name])
+            self.g[name], _, _, picks = slice_step_batched(self.g[name], lp0, many, SLICE_WIDTHS[name], rng, left=0.0)
+            take(payloads, picks, per_chain=True)
+        hyper = {'v': lambda x: _norm_logpdf(x, 2.0, 3.0), 'a': lambda x: _gamma_from_mean_std(x, 1.5, 0.75),
+                 't': lambda x: _gamma_from_mean_std(x, 0.4, 0.2)}
+        std_sd = {'v': 2.0, 'a': 2.0, 't': 1.0}
+        for name in ('v', 'a', 't'):  # no likelihood below: numpy only, still fewer and larger evaluations
+            xs = self.subj[name]
+            tg = lambda G, name=name, xs=xs: self._subj_prior(name, xs, g=G[..., None]).sum(axis=-1) + hyper[name](G)
+            self.g[name], _, _, _ = slice_step_batched(self.g[name], None, tg, SLICE_WIDTHS[name], rng)
+            ts = lambda Sd, name=name, xs=xs: (self._subj_prior(name, xs, std=Sd[..., None]).sum(axis=-1) +
+                                               _halfnorm_logpdf(Sd, std_sd[name]))
+            self.g[name + '_std'], _, _, _ = slice_step_batched(self.g[name + '_std'], None, ts,
+                                                                SLICE_WIDTHS[name + '_std'], rng, left=0.0)
 
     def sample(self, n_iter, trace=True):
         """Run n_iter sweeps; returns (trace dict name -> [n_iter, chains(, subjects)], seconds)."""

@@ -265,6 +265,20 @@ int hddm_trials_wiener_like_nodes(const hddm_trials *h, const int64_t *node_off,
                                   int n_st, int n_sz, int use_adaptive, double simps_err, double *logp,
                                   unsigned long long *evals);
 
+/* NEW: native slice-within-Gibbs driver for the hierarchical full DDM of BASELINE config 2 (S subjects, one observed
+ * node each, include = sv sz st; priors, slice widths and maxiter of hddm/models/hddm_info.py:103-175,
+ * hddm/models/base.py:578-681), C chains in lock-step, no Python between the launches of a sweep.  `trials` holds all
+ * subjects' signed RTs, subject s = [node_off[s], node_off[s+1]).  g is float64 [9][C] (rows v, v_std, a, a_std, t,
+ * t_std, sv, sz, st) and subj float64 [3][C][S] (rows v, a, t): the chains' state, in and out.  rng_state = numpy
+ * PCG64 {state hi, state lo, inc hi, inc lo}, in and out: the chain drawn equals the one hddm_b200/sampler.py
+ * (HierarchicalDDM, the readable specification) draws from the same generator state.  trace_g [n_iter][9][C] and
+ * trace_subj [n_iter][3][C][S] may be NULL.  n_launches (may be NULL) counts likelihood launches. */
+int hddm_hier_ddm_sample(const hddm_trials *trials, const int64_t *node_off, int64_t S, int64_t C, double *g,
+                         double *subj, double z, double p_outlier, double w_outlier, double err, int n_st, int n_sz,
+                         int use_adaptive, double simps_err, uint64_t *rng_state, int64_t n_iter, double *trace_g,
+                         double *trace_subj, int64_t *n_launches);
+
+
 /* ---- device-pointer entry points (enqueue only; used under torch.distributed sharding) ----- */
 
 /* One-time layout step for a device-resident trial vector that many launches will reuse: d_sorted =

@@ -26,7 +26,14 @@ FP64_OPS = ("DFMA", "DMUL", "DADD", "DSETP", "DMNMX")   # what the FP64 pipe exe
 def pages(rep):
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = [r for r in csv.reader(io.StringIO(raw)) if len(r) > 20]
-    metrics = dict(zip(rows[0], rows[2]))
+    scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12,      # -> bytes
+             "ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1.0, "msecond": 1.0, "s": 1e3, "second": 1e3}  # -> ms
+    metrics = {}
+    for name, unit, val in zip(rows[0], rows[1], rows[2]):
+        try:
+            metrics[name] = repr(float(val.replace(",", "")) * scale.get(unit, 1.0)) if unit in scale else val
+        except ValueError:
+            metrics[name] = val
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(src)))
     hdr, data = rows[1], rows[2:]
@@ -68,7 +75,7 @@ def main():
         tot_t.update(t)
         launches.append({
             "report": os.path.basename(rep), "kernel": m.get("Kernel Name"),
-            "duration_ms": (num(m, "gpu__time_duration.sum") or 0) / 1e6,
+            "duration_ms": num(m, "gpu__time_duration.sum"),
             "fp64_pipe_pct": num(m, "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),
             "issue_active_pct": num(m, "sm__issue_active.avg.pct_of_peak_sustained_elapsed"),
             "warps_eligible": num(m, "smsp__warps_eligible.avg.per_cycle_active"),

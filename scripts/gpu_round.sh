@@ -47,7 +47,6 @@ if [ -f $O/${TAG}_like.ncu-rep ] && [ -f $O/${TAG}_like_second.ncu-rep ]; then
     python profiles/ncu_digest.py $O/${TAG}_$r.ncu-rep > $O/${TAG}_ncu_digest_$r.txt 2>&1
   done
   ncu -i $O/${TAG}_like.ncu-rep --page source --csv 2>/dev/null | gzip > $O/${TAG}_ncu_source_like.csv.gz
-  rm -f $O/${TAG}_like_second.ncu-rep
 fi
 timeout 300 $SMALL --sweep B > $O/${TAG}_plain_B.json 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_like_partial -s 2 -c 1 -o $O/${TAG}_like_B -f $SMALL --sweep B > $O/${TAG}_ncu_fB.log 2>&1
