@@ -226,16 +226,19 @@ def mcmc_cpu(pool, kind, cores, rts, chains, iters):
             "cores": cores, "kind": kind}
 
 
-def mcmc_gpu(rts, chains, iters):
+def mcmc_gpu(rts, chains, iters, native=True):
+    """native: the C++ driver (csrc/abi_mcmc.cu) -- the same chain as the Python sampler draws, without Python
+    between the launches; else hddm_b200/sampler.py with speculative batches."""
     from hddm_b200 import likelihoods as L, sampler
     nodes = L.BatchedNodes(rts)
     T = rts[0].shape[0]
     m = sampler.HierarchicalDDM(len(rts), nodes.logp, chains=chains, seed=1)
-    m.sample(5, trace=False)  # warm-up (uploads + sorts the trials once)
-    calls0, sets0 = m.loglik_calls, m.sets_evaluated
-    _, dt = m.sample(iters, trace=False)
+    run = (lambda n: m.sample_native(nodes, n, trace=False)) if native else (lambda n: m.sample(n, trace=False))
+    run(5)  # warm-up (uploads + sorts the trials once)
+    calls0 = m.loglik_calls
+    _, dt = run(iters)
     return {"chains": chains, "iters": iters, "it_per_s_per_chain": iters / dt, "chain_it_per_s": chains * iters / dt,
-            "launches_per_iter": (m.loglik_calls - calls0) / iters, "evals_per_s": (m.sets_evaluated - sets0) * T / dt}
+            "launches_per_iter": (m.loglik_calls - calls0) / iters, "driver": "native" if native else "python"}
 
 
 def mcmc_reference_record(pool, kind, cores, iters=(10, 2)):
@@ -572,8 +575,9 @@ def run_ours(args):
                 try:
                     rts = mcmc_data()
                     mcmc = {"config": MCMC_CFG,
-                            "gpu_1_chain": mcmc_gpu(rts, 1, args.mcmc_iters),
-                            "gpu_16_chains": mcmc_gpu(rts, 16, max(args.mcmc_iters // 4, 10)),
+                            "gpu_1_chain": mcmc_gpu(rts, 1, 4 * args.mcmc_iters),
+                            "gpu_16_chains": mcmc_gpu(rts, 16, args.mcmc_iters),
+                            "gpu_1_chain_python_driver": mcmc_gpu(rts, 1, args.mcmc_iters, native=False),
                             "cpu_1_chain": mcmc_cpu(arm.pool, arm.kind, arm.cores, rts, 1, 10),
                             "cpu_16_chains": mcmc_cpu(arm.pool, arm.kind, arm.cores, rts, 16, 2)}
                 except Exception as ex:
@@ -584,8 +588,8 @@ def run_ours(args):
             if not args.no_sub and mcmc is None:
                 try:
                     rts = mcmc_data()
-                    mcmc = {"config": MCMC_CFG, "gpu_1_chain": mcmc_gpu(rts, 1, args.mcmc_iters),
-                            "gpu_16_chains": mcmc_gpu(rts, 16, max(args.mcmc_iters // 4, 10))}
+                    mcmc = {"config": MCMC_CFG, "gpu_1_chain": mcmc_gpu(rts, 1, 4 * args.mcmc_iters),
+                            "gpu_16_chains": mcmc_gpu(rts, 16, args.mcmc_iters)}
                 except Exception as ex2:
                     mcmc = {"error": repr(ex2)}
         launches = (4 if split_sweep(T, P) else 2) * args.steps

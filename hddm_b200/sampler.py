@@ -373,6 +373,52 @@ class HierarchicalDDM(object):
             self.g[name + '_std'], _, _, _ = slice_step_batched(self.g[name + '_std'], None, ts,
                                                                 SLICE_WIDTHS[name + '_std'], rng, left=0.0)
 
+    def sample_native(self, nodes, n_iter, trace=True):
+        """n_iter sweeps in the native driver (hddm_hier_ddm_sample, csrc/abi_mcmc.cu): the same chain as
+        sample() draws from the same generator state -- same model, update order and random numbers -- with no
+        Python between the launches.  `nodes`: the likelihoods.BatchedNodes holding the subjects' trials (its
+        numerics and w_outlier are used; self.loglik is not called).  Returns (trace, seconds) like sample()."""
+        import ctypes as C
+        from . import _lib
+        st = self.rng.bit_generator.state
+        if st.get('bit_generator') != 'PCG64':
+            raise ValueError("sample_native replays numpy's PCG64 stream; the model's generator is %r" % st.get('bit_generator'))
+        mask = (1 << 64) - 1
+        words = (C.c_uint64 * 4)(st['state']['state'] >> 64, st['state']['state'] & mask,
+                                 st['state']['inc'] >> 64, st['state']['inc'] & mask)
+        Cn, S = self.C, self.S
+        gnames = ('v', 'v_std', 'a', 'a_std', 't', 't_std', 'sv', 'sz', 'st')
+        g = np.ascontiguousarray(np.stack([self.g[k] for k in gnames]), dtype=np.float64)
+        subj = np.ascontiguousarray(np.stack([self.subj[k] for k in ('v', 'a', 't')]), dtype=np.float64)
+        tg = np.empty((n_iter, 9, Cn)) if trace else None
+        ts = np.empty((n_iter, 3, Cn, S)) if trace else None
+        launches = C.c_int64(0)
+        nm = nodes.numerics
+        node_off = np.ascontiguousarray(nodes.node_off, dtype=np.int64)
+        if node_off.shape[0] != S + 1:
+            raise ValueError("nodes holds %d observed nodes, the model %d subjects" % (node_off.shape[0] - 1, S))
+        t0 = time.perf_counter()
+        _lib.check(_lib.lib().hddm_hier_ddm_sample(
+            nodes._handle()._h, node_off.ctypes.data_as(_lib.c_lp), S, Cn, _lib.dptr(g), _lib.dptr(subj),
+            float(self.z), float(self.p_outlier), float(nodes.w_outlier), nm['err'], nm['n_st'], nm['n_sz'],
+            int(bool(nm['use_adaptive'])), nm['simps_err'], words, int(n_iter),
+            _lib.dptr(tg) if trace else None, _lib.dptr(ts) if trace else None, C.byref(launches)))
+        dt = time.perf_counter() - t0
+        for k, name in enumerate(gnames):
+            self.g[name] = g[k].copy()
+        for k, name in enumerate(('v', 'a', 't')):
+            self.subj[name] = subj[k].copy()
+        st['state']['state'] = (int(words[0]) << 64) | int(words[1])
+        st['has_uint32'], st['uinteger'] = 0, 0
+        self.rng.bit_generator.state = st
+        self.node_ll = None
+        self.loglik_calls += int(launches.value)
+        tr = None
+        if trace:
+            tr = {name: tg[:, k] for k, name in enumerate(gnames)}
+            tr.update({name + '_subj': ts[:, k] for k, name in enumerate(('v', 'a', 't'))})
+        return tr, dt
+
     def sample(self, n_iter, trace=True):
         """Run n_iter sweeps; returns (trace dict name -> [n_iter, chains(, subjects)], seconds)."""
         names = list(self.g) + [k + '_subj' for k in self.subj]

