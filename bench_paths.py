@@ -126,6 +126,47 @@ def main():
              ms=dt * 1e3, h2d_bytes=int(design.nbytes + x.nbytes + params.nbytes + coef.nbytes),
              algorithmic_GBps=16.0 * T * P / dt / 1e9)
 
+    if on("regression_resident"):
+        # C3 as an MCMC over coefficients sees it: trials + design resident (wfpt.Regression), one call per batch of
+        # proposals; outcome v (lean evaluators with a drift per trial) and outcome a (table-driven walk)
+        T, P, K = 100000, 512, 3
+        x = rts(rng, T)
+        params = np.concatenate([draw(rng, P), np.full((1, P), 0.05), np.full((1, P), 0.1)])
+        design = np.concatenate([np.ones((1, T)), rng.standard_normal((K - 1, T))])
+        nm = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
+        for outcome, centre, spread in (("v", params[0], 0.5), ("a", params[2], 0.05)):
+            coef = np.concatenate([centre[None, :], rng.uniform(-spread, spread, (K - 1, P))])
+            reg = wfpt.Regression(x, {outcome: design})
+            dt, lp = best_of(lambda: reg.like_batch({outcome: coef}, params, **nm), args.reps)
+            cols = np.ascontiguousarray((design[:, :5000].T @ coef[:, :4]).T)
+            t0 = time.perf_counter()
+            for p in range(4):
+                a7 = [cols[p] if n == outcome else params[k, p] for k, n in enumerate(("v", "sv", "a", "z", "sz", "t", "st"))]
+                W.wiener_like_multi(x[:5000], *a7, 1e-4, [outcome], 2, 2, 1, 1e-3, 0.05, 0.1)
+            cdt = time.perf_counter() - t0
+            emit("regression %s ~ 1 + x1 + x2, data resident: %d trials x %d coefficient proposals" % (outcome, T, P),
+                 T * P / dt, "evals/s", 5000 * 4 / cdt, kind, "first 5000 trials x first 4 proposals", ms=dt * 1e3,
+                 h2d_bytes=int(params.nbytes + coef.nbytes), design_read_GBps=8.0 * (K + 1) * T * P / dt / 1e9)
+            reg.close()
+
+    if on("nodes"):
+        # C2-shaped node batches: 20 observed nodes x 200 trials, P proposals per launch (what the sampler issues)
+        from hddm_b200 import likelihoods as L
+        S, Tn = 20, 200
+        nodes = L.BatchedNodes([rts(rng, Tn, 0.45) for _ in range(S)])
+        for per_node in (1, 16, 205):
+            P = S * per_node
+            params = np.concatenate([draw(rng, P), np.full((1, P), 0.05), np.full((1, P), 0.1)])
+            set_node = np.tile(np.arange(S, dtype=np.int64), per_node)
+            dt, lp = best_of(lambda: nodes.logp(set_node, params), max(args.reps, 5))
+            emit("node batch: %d nodes x %d trials x %d proposals each (%d sets)" % (S, Tn, per_node, P), Tn * P / dt,
+                 "evals/s", None, kind, "-", ms=dt * 1e3)
+        for T2, P2 in ((1000, 10000),):
+            x = rts(rng, T2)
+            params = np.concatenate([draw(rng, P2), np.full((1, P2), 0.05), np.full((1, P2), 0.1)])
+            dt, lp = best_of(lambda: wfpt.wiener_like_batch(x, params, **HDDM), args.reps)
+            emit("short segments: %d trials x %d sets" % (T2, P2), T2 * P2 / dt, "evals/s", None, kind, "-", ms=dt * 1e3)
+
     if on("ppc"):
         D, S = 10000, 200
         params = draw(rng, D)

@@ -51,6 +51,9 @@ SIGNATURES = {
     "hddm_ppc_stats": (_i, [c_dp, _l, _l, c_dp]),
     "hddm_dmat_cdf_batch": (_i, [c_dp, _l, c_dp, _l, c_dp, c_ip]),
     "hddm_wiener_like_regression_batch": (_i, [c_dp, _l, c_dp, _l, c_dp, c_dp, _l] + _NUM + [c_dp, c_up]),
+    "hddm_regdata_upload": (_i, [c_dp, _l, _i, c_lp, C.POINTER(c_dp), C.POINTER(_v)]),
+    "hddm_regdata_free": (_i, [_v]),
+    "hddm_regdata_like_batch": (_i, [_v, C.POINTER(_i), C.POINTER(_i), C.POINTER(c_dp), c_dp, _l] + _NUM + [c_dp, c_up]),
     "hddm_simulate_drift_batch": (_i, [c_dp, _l, _l, _d, _d, C.c_ulonglong, c_dp, c_dp, _l, c_dp]),
     "hddm_simulate_drift_switch_batch": (_i, [c_dp, c_dp, _l, _l, _d, _d, C.c_ulonglong, c_dp, c_dp, _l, c_dp]),
     "hddm_wiener_like_rlddm": (_i, [c_dp, c_lp, c_dp, c_lp, _l] + [_d] * 10 + _NUM + [_d, _d, c_dp]),

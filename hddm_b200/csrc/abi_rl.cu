@@ -6,6 +6,8 @@
 // ordering of the trials by condition; everything numerical runs on the GPU (rl_kernels.cu for the
 // Q recursion, the ordinary likelihood kernel for the densities).
 #include <algorithm>
+#include <new>
+#include <mutex>
 #include <numeric>
 #include <vector>
 
@@ -244,59 +246,177 @@ int hddm_wiener_like_rl_batch(const int64_t* response, const double* feedback, c
     return rl_choice_impl(response, feedback, split_by, n, params, P, logp);
 }
 
-int hddm_wiener_like_regression_batch(const double* x, int64_t n, const double* design, int64_t K,
-                                      const double* coef, const double* params, int64_t P, double err, int n_st,
-                                      int n_sz, int use_adaptive, double simps_err, double* logp,
-                                      unsigned long long* evals)
+// ---- regression likelihood (HDDMRegressor): trials + design matrices resident on the device ---------------------
+
+}  // extern "C"
+
+struct hddm_regdata {
+    int64_t n = 0;
+    int n_terms = 0;
+    int64_t K[kMaxRegTerms] = {0, 0, 0, 0};
+    double* d_x = nullptr;                       // trials ordered boundary-major, then |rt| (one-time layout)
+    double* d_design[kMaxRegTerms] = {nullptr, nullptr, nullptr, nullptr};  // [K][n] each, rows in the same order
+    double* d_block = nullptr;                   // one allocation behind all of the above
+    double* d_scratch = nullptr;                 // partial sums / logp / params / coefficients, grown on demand
+    size_t scratch_bytes = 0;
+};
+
+extern "C" {
+
+int hddm_regdata_upload(const double* x, int64_t n, int n_terms, const int64_t* K, const double* const* design,
+                        hddm_regdata** out)
 {
     std::lock_guard<std::mutex> lock(g_rt.mu);
-    if (n < 0 || K < 1 || P < 0 || (n > 0 && (!x || !design)) || (P > 0 && (!coef || !params || !logp)))
-        return fail(HDDM_ERR_ARG, "regression_batch: bad buffer or size");
-    if (P > 65535) return fail(HDDM_ERR_ARG, "regression_batch: more than 65535 coefficient sets per call");
+    if (!out || n < 0 || n_terms < 0 || n_terms > kMaxRegTerms || (n > 0 && !x) || (n_terms > 0 && (!K || !design)))
+        return fail(HDDM_ERR_ARG, "regdata_upload: bad argument (at most 4 regression terms)");
+    for (int r = 0; r < n_terms; ++r)
+        if (K[r] < 1 || K[r] > kMaxRegK || !design[r])
+            return fail(HDDM_ERR_ARG, "regdata_upload: a design matrix needs 1..16 columns");
+    TRY(ensure_ready());
+    // One-time layout on the host: lower-boundary trials first, each group ascending in |rt| (what sort_trials does for
+    // the uniform-parameter entry points), so that the lanes of a warp share boundary, series branch and term count;
+    // the design rows follow the same permutation.
+    std::vector<int64_t> order((size_t)n);
+    std::iota(order.begin(), order.end(), (int64_t)0);
+    auto key = [&](int64_t i) {
+        uint64_t bits;
+        const double v = x[i];
+        memcpy(&bits, &v, sizeof(bits));
+        return (bits & 0x7fffffffffffffffULL) | (v > 0 ? 0x8000000000000000ULL : 0ULL);
+    };
+    std::stable_sort(order.begin(), order.end(), [&](int64_t l, int64_t r) { return key(l) < key(r); });
+    size_t doubles = (size_t)(n > 0 ? n : 1);
+    for (int r = 0; r < n_terms; ++r) doubles += (size_t)K[r] * (size_t)(n > 0 ? n : 1);
+    std::vector<double> host(doubles);
+    for (int64_t j = 0; j < n; ++j) host[(size_t)j] = x[order[(size_t)j]];
+    size_t off = (size_t)(n > 0 ? n : 1);
+    hddm_regdata* h = new (std::nothrow) hddm_regdata();
+    if (!h) return fail(HDDM_ERR_ARG, "regdata_upload: out of host memory");
+    h->n = n;
+    h->n_terms = n_terms;
+    if (cudaMalloc(&h->d_block, doubles * sizeof(double)) != cudaSuccess) {
+        delete h;
+        (void)cudaGetLastError();
+        return fail(HDDM_ERR_CUDA, "regdata_upload: out of device memory");
+    }
+    h->d_x = h->d_block;
+    for (int r = 0; r < n_terms; ++r) {
+        h->K[r] = K[r];
+        h->d_design[r] = h->d_block + off;
+        for (int64_t k = 0; k < K[r]; ++k)
+            for (int64_t j = 0; j < n; ++j) host[off + (size_t)k * n + j] = design[r][(size_t)k * n + order[(size_t)j]];
+        off += (size_t)K[r] * (size_t)(n > 0 ? n : 1);
+    }
+    const cudaError_t e = cudaMemcpy(h->d_block, host.data(), doubles * sizeof(double), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(h->d_block);
+        delete h;
+        CUDA_TRY(e);
+    }
+    *out = h;
+    return HDDM_OK;
+}
+
+int hddm_regdata_free(hddm_regdata* h)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!h) return HDDM_OK;
+    if (g_rt.ready) cudaStreamSynchronize(g_rt.stream);
+    cudaFree(h->d_block);
+    cudaFree(h->d_scratch);
+    delete h;
+    return HDDM_OK;
+}
+
+int hddm_regdata_like_batch(hddm_regdata* h, const int* outcome, const int* link, const double* const* coef,
+                            const double* params, int64_t P, double err, int n_st, int n_sz, int use_adaptive,
+                            double simps_err, double* logp, unsigned long long* evals)
+{
+    std::lock_guard<std::mutex> lock(g_rt.mu);
+    if (!h || P < 0 || (P > 0 && (!params || !logp)) || (h->n_terms > 0 && (!outcome || !link || !coef)))
+        return fail(HDDM_ERR_ARG, "regdata_like_batch: bad argument");
+    for (int r = 0; r < h->n_terms; ++r) {
+        if (outcome[r] < 0 || outcome[r] > 6 || link[r] < 0 || link[r] > kLinkExp || !coef[r])
+            return fail(HDDM_ERR_ARG, "regdata_like_batch: outcome must be 0..6 (v sv a z sz t st), link 0..2");
+        for (int q = 0; q < r; ++q)
+            if (outcome[q] == outcome[r]) return fail(HDDM_ERR_ARG, "regdata_like_batch: an outcome is regressed twice");
+    }
     const Numerics nm = make_numerics(err, n_st, n_sz, use_adaptive, simps_err);
     TRY(check_numerics(n_st, n_sz, use_adaptive));
     TRY(ensure_ready());
     if (P == 0) return HDDM_OK;
-    const int64_t chunks = chunks_for(n);
+    const int64_t n = h->n, chunks = chunks_for(n);
     if (chunks > 65535) return fail(HDDM_ERR_ARG, "more than 65535*2048 trials per parameter set");
-    if ((double)P * (double)n * 8.0 > 64e9) return fail(HDDM_ERR_ARG, "regression_batch: P x n drift table above 64 GB");
-    Stager S;
-    const int s_x = S.add(x, (size_t)n * sizeof(double));
-    const int s_design = S.add(design, (size_t)K * n * sizeof(double));
-    const int s_coef = S.add(coef, (size_t)K * P * sizeof(double));
-    const int s_par = S.add(params, (size_t)P * kNumPar * sizeof(double));
-    const int s_drift = S.scratch((size_t)P * (size_t)(n > 0 ? n : 1) * sizeof(double));
-    const int s_partial = S.scratch((size_t)P * chunks * sizeof(double));
-    const int s_logp = S.scratch((size_t)P * sizeof(double));
-    const int s_evals = S.scratch(sizeof(unsigned long long));
+    // per-call device scratch: params [9][P] | coef per term [K][P] | partial [P][2 chunks] | logp [P] | evals
+    size_t coef_doubles = 0;
+    for (int r = 0; r < h->n_terms; ++r) coef_doubles += (size_t)h->K[r] * P;
+    const size_t need = ((size_t)kNumPar * P + coef_doubles + (size_t)2 * P * chunks + (size_t)P + 2) * sizeof(double);
     cudaStream_t s = g_rt.stream;
-    TRY(S.commit(s));
-    CUDA_TRY(cudaMemsetAsync(S.dev<char>(s_evals), 0, sizeof(unsigned long long), s));
-    CUDA_TRY(launch_design_drift(S.dev<double>(s_design), S.dev<double>(s_coef), n, K, P, S.dev<double>(s_drift), s));
-    const double* d_par = S.dev<double>(s_par);
+    if (need > h->scratch_bytes) {
+        CUDA_TRY(cudaStreamSynchronize(s));
+        cudaFree(h->d_scratch);
+        h->d_scratch = nullptr;
+        h->scratch_bytes = 0;
+        CUDA_TRY(cudaMalloc(&h->d_scratch, need + need / 4));
+        h->scratch_bytes = need + need / 4;
+    }
+    double* d_par = h->d_scratch;
+    double* d_coef = d_par + (size_t)kNumPar * P;
+    double* d_partial = d_coef + coef_doubles;
+    double* d_logp = d_partial + (size_t)2 * P * chunks;
+    unsigned long long* d_evals = reinterpret_cast<unsigned long long*>(d_logp + P);
+    CUDA_TRY(cudaMemcpyAsync(d_par, params, (size_t)kNumPar * P * sizeof(double), cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemsetAsync(d_evals, 0, sizeof(unsigned long long), s));
     LikeArgs a;
     memset(&a, 0, sizeof(a));
-    a.x = S.dev<double>(s_x);
+    a.x = h->d_x;
     for (int k = 0; k < kNumPar; ++k) {
-        a.par[k] = d_par + k * P;
+        a.par[k] = d_par + (size_t)k * P;
         a.set_stride[k] = 1;
     }
-    a.par[0] = S.dev<double>(s_drift);
-    a.set_stride[0] = n;
-    a.trial_stride[0] = 1;
+    a.n_reg = h->n_terms;
+    size_t off = 0;
+    for (int r = 0; r < h->n_terms; ++r) {
+        CUDA_TRY(cudaMemcpyAsync(d_coef + off, coef[r], (size_t)h->K[r] * P * sizeof(double), cudaMemcpyHostToDevice, s));
+        a.reg[r].design = h->d_design[r];
+        a.reg[r].coef = d_coef + off;
+        a.reg[r].K = (int)h->K[r];
+        a.reg[r].outcome = outcome[r];
+        a.reg[r].link = link[r];
+        off += (size_t)h->K[r] * P;
+    }
     a.n = n;
     a.n_sets = P;
     a.chunks = (int)chunks;
     a.mode = kModeMulti;  // wiener_like_multi semantics per set (src/wfpt.pyx:244-274)
     a.nm = nm;
-    a.partial = S.dev<double>(s_partial);
-    a.logp = S.dev<double>(s_logp);
-    a.evals = S.dev<unsigned long long>(s_evals);
+    a.partial = d_partial;
+    a.logp = d_logp;
+    a.evals = d_evals;
     CUDA_TRY(launch_like(a, s));
-    CUDA_TRY(cudaMemcpyAsync(logp, a.logp, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, s));
-    if (evals) CUDA_TRY(cudaMemcpyAsync(evals, a.evals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(logp, d_logp, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (evals) CUDA_TRY(cudaMemcpyAsync(evals, d_evals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));
     return HDDM_OK;
+}
+
+// One-shot form of the above for a regression on the drift with the identity link (kept from round 1).
+int hddm_wiener_like_regression_batch(const double* x, int64_t n, const double* design, int64_t K,
+                                      const double* coef, const double* params, int64_t P, double err, int n_st,
+                                      int n_sz, int use_adaptive, double simps_err, double* logp,
+                                      unsigned long long* evals)
+{
+    if (n < 0 || K < 1 || P < 0 || (n > 0 && (!x || !design)) || (P > 0 && (!coef || !params || !logp))) {
+        std::lock_guard<std::mutex> lock(g_rt.mu);
+        return fail(HDDM_ERR_ARG, "regression_batch: bad buffer or size");
+    }
+    hddm_regdata* h = nullptr;
+    TRY(hddm_regdata_upload(x, n, 1, &K, &design, &h));
+    const int outcome = 0, link = kLinkIdentity;
+    const int rc = hddm_regdata_like_batch(h, &outcome, &link, &coef, params, P, err, n_st, n_sz, use_adaptive, simps_err,
+                                           logp, evals);
+    hddm_regdata_free(h);
+    return rc;
 }
 
 int hddm_wiener_like_multi_rlddm(const double* x, const int64_t* response, const double* feedback,

@@ -68,6 +68,18 @@ enum LikeMode : int {
 //   regression (per trial)    -> trial_stride 1 (set_stride = n for a batch of regressions)
 // Set p sees trials [seg[s], seg[s+1]) of x with s = set_node ? set_node[p] : p, or all n trials when
 // seg == nullptr.
+// Regression term (HDDMRegressor: hddm/models/hddm_regression.py:26-36 regresses any of v, sv, a, z, sz, t, st): the
+// per-trial value of parameter `outcome` is link(sum_k design[k][i] * coef[k][p]), k ascending, fused multiply-adds,
+// evaluated inside the likelihood kernel (K numbers of the design row per trial instead of a [P][n] table).
+constexpr int kMaxRegTerms = 4;
+constexpr int kMaxRegK = 16;
+enum RegLink : int { kLinkIdentity = 0, kLinkInvLogit = 1, kLinkExp = 2 };
+struct RegTerm {
+    const double* design;  // [K][n], rows in the order of the trials of x
+    const double* coef;    // [K][n_sets]
+    int K, outcome, link, pad;
+};
+
 struct LikeArgs {
     const double* x;
     const int64_t* seg;
@@ -94,6 +106,8 @@ struct LikeArgs {
     double* partial2 = nullptr;          // [n_sets * chunks2]
     int chunks2 = 0;                     // ceil(chunks / kBlocksPerDeferredCta)
     const void* set_tables = nullptr;    // [n_sets] GridSet tables built once per set by k_build_tables (else per CTA)
+    int n_reg = 0;                       // regression terms (0: none); the outcomes' par[] entries are then ignored
+    RegTerm reg[kMaxRegTerms] = {};
 };
 
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream);

@@ -122,6 +122,7 @@ struct alignas(16) LeanSet {
     // reference's midpoint rule, src/integrate.pxi:153-155): the deferred-trial tree of wfpt_lean.cuh
     double tn17[17];
     double v;              // the set's drift (boundary flip applied per trial)
+    int uniform, pad_u;    // the drift-dependent constants above belong to the set (else: per trial, lean_begin_v)
     double xz[2];          // decision times in (0, xz[b]) are negligible nodes (GridSet::xt_zero; 0: none are)
     double pad17;
 };

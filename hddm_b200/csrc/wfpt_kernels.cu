@@ -119,6 +119,25 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         par[k] = load_par(a, k, p, 0);
         per_trial |= a.trial_stride[k] != 0;
     }
+    // regression terms: this set's coefficients, once per CTA
+    __shared__ double s_coef[kMaxRegTerms][kMaxRegK];
+    const bool reg_v_only = a.n_reg == 1 && a.reg[0].outcome == 0 && !per_trial;  // the lean evaluators take it
+    if (a.n_reg > 0) {
+        for (int k = threadIdx.x; k < a.n_reg * kMaxRegK; k += kLikeThreads) {
+            const RegTerm& t = a.reg[k / kMaxRegK];
+            s_coef[k / kMaxRegK][k % kMaxRegK] = (k % kMaxRegK) < t.K ? __ldg(t.coef + (int64_t)(k % kMaxRegK) * a.n_sets + p) : 0.0;
+        }
+        per_trial = true;
+        __syncthreads();
+    }
+    auto reg_value = [&](int r, int64_t i) {
+        const RegTerm& t = a.reg[r];
+        double acc = 0.0;
+        for (int k = 0; k < t.K; ++k) acc = fma(__ldg(t.design + (int64_t)k * a.n + i), s_coef[r][k], acc);
+        if (t.link == kLinkInvLogit) acc = 1.0 / (1.0 + exp(-acc));
+        else if (t.link == kLinkExp) acc = exp(acc);
+        return acc;
+    };
 
     if (GRID && a.set_tables) {  // split sweep: the set's tables were built once, by k_build_tables
         static_assert(sizeof(GridSet<KT>) % sizeof(uint4) == 0, "tables are copied 16 bytes at a time");
@@ -130,14 +149,16 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         build_gridset<KT>(gs, par, a.tab,
                           (a.mode != kModeContaminant && p_out >= 0 && p_out <= 1) ? w_out * p_out : 0.0);
         if (LEAN) {  // (k_build_tables does the same for the shared tables)
-            if (threadIdx.x == 0) build_leanset(gs, gs.lean, par[0], a.nm, !per_trial && !multi);
+            if (threadIdx.x == 0) build_leanset(gs, gs.lean, par[0], a.nm, !per_trial);
             __syncthreads();
         }
     } else if (KMAX > 0)
         build_wtables<KT>(wt, par[3], par[4]);
     // Lean first level (wfpt_lean.cuh): the set qualifies (CTA-uniform) -> stage the 2^(i/2048) table
     __shared__ double ebig[(LEAN || TREE) ? kExpBig : 1];
-    const bool lean_ok = (LEAN || TREE) && gs.lean.ok != 0 && !per_trial && !multi;
+    // (uniform drift, or a drift regressed per trial; wiener_like / contaminant / wiener_like_multi semantics)
+    const bool lean_ok = (LEAN || TREE) && gs.lean.ok != 0 && a.mode != kModeMultiRL &&
+                         (reg_v_only ? gs.lean.uniform == 0 : (!per_trial && gs.lean.uniform != 0));
     const bool tree_ok = TREE && lean_ok && a.nm.n_st == 2;
     if (lean_ok) {
         for (int k = threadIdx.x; k < kExpBig; k += kLikeThreads) ebig[k] = g_exp2_big[k];
@@ -184,6 +205,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
 #pragma unroll
             for (int k = 0; k < (GRID ? 1 : 7); ++k)  // GRID: only the drift can vary per trial
                 if (a.trial_stride[k] != 0) par[k] = load_par(a, k, p, i);
+            for (int r = 0; r < a.n_reg; ++r) par[GRID ? 0 : a.reg[r].outcome] = reg_value(r, i);
         }
         bool need = false;
         double d;
@@ -208,7 +230,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         }
         return need;
     };
-    // Lean first level for one warp round: returns true when the warp took it (then *need is set per lane).
+    // Lean first level for one warp round (lean_ok sets): *need is set per lane; always returns true.
     auto lean_round = [&](int64_t i, bool in_range, bool* need) {
         const LeanSet& L = gs.lean;
         const bool valid = in_range && !(a.cont && a.cont[i] != 0);
@@ -219,23 +241,42 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         // every node large-time and inside the comfortable range (x_small: signed compare, a negative or -NaN
         // decision time fails; +NaN fails the second test)
         const long long bits4 = __double_as_longlong(xt4);
-        const bool large = (bits4 >= L.x_small[b]) & (xt0 <= L.xhi);
-        bool nd = false;
-        double d;
-        if (__all_sync(0xffffffffu, large | !valid)) {
+        bool v_fits = true;
+        const LeanTrial c = reg_v_only ? lean_begin_v<KT>(gs, L, b, reg_value(0, valid ? i : begin), xt0, &v_fits)
+                                       : lean_begin(L, b);
+        const bool large = valid & v_fits & (bits4 >= L.x_small[b]) & (xt0 <= L.xhi);
+        // every node small-time (xt0 below the edge) and inside the comfortable range
+        const bool small = valid & v_fits & !large & (bits4 >= L.x_lo_small[b]) & below(xt0, L.x_edge) & (L.ok_small != 0);
+        // Lean or deferred: a lane in neither class (a node at or before the onset, a trial straddling the
+        // small-/large-time edge, ...) goes to the second pass, whose tree evaluates exactly what the reference's
+        // recursion reaches; the first pass then holds no other code for these sets (it was instruction-fetch bound
+        // on onset-mixed data: profiles/r2_v7_ncu_digest_like_B.txt).  A warp with both classes runs both evaluators.
+        // (a trial before the onset has density exactly 0 and costs the reference no pdf_sv: src/pdf.pxi:111-113)
+        const bool before = valid & ((ax - gs.t_onset) < 0);
+        bool nd = valid & !(large | small | before);
+        double d = 0.0;
+        if (__any_sync(0xffffffffu, large)) {
             const int K = 1 + (int)below(xt4, L.x_k[0]) + (int)below(xt4, L.x_k[1]) + (int)below(xt4, L.x_k[2]);
-            const int wK = __reduce_max_sync(0xffffffffu, valid ? K : 1);
-            d = lean_trial_large<KT>(gs, L, ebig, b, ax, xt0, xt4, wK, &nd);
-        } else {
-            // every node small-time (xt0 below the edge) and not too early for the lean small-time node
-            const bool small = (bits4 >= L.x_lo_small[b]) & below(xt0, L.x_edge) & (L.ok_small != 0);
-            if (!__all_sync(0xffffffffu, small | !valid)) return false;
-            const bool any_four = __any_sync(0xffffffffu, valid & !below(xt0, L.x_s4));
-            d = lean_trial_small<KT>(gs, L, ebig, b, ax, xt0, xt4, any_four, &nd);
+            const int wK = __reduce_max_sync(0xffffffffu, large ? K : 1);
+            bool n1 = false;
+            const double dl = lean_trial_large<KT>(gs, L, ebig, c, ax, xt0, xt4, wK, &n1);
+            if (large) {
+                d = dl;
+                nd = n1;
+            }
+        }
+        if (__any_sync(0xffffffffu, small)) {
+            const bool any_four = __any_sync(0xffffffffu, small & !below(xt0, L.x_s4));
+            bool n2 = false;
+            const double ds = lean_trial_small<KT>(gs, L, ebig, c, ax, xt0, xt4, any_four, &n2);
+            if (small) {
+                d = ds;
+                nd = n2;
+            }
         }
         nd &= valid;
         if (valid & !nd) {
-            evals += 25;  // 5 decision times x 5 start points, src/integrate.pxi:131-133,187-198
+            evals += before ? 0 : 25;  // 5 decision times x 5 start points, src/integrate.pxi:131-133,187-198
             d = d * (1 - p_out) + w_out * p_out;
             hit_zero |= (d == 0);
             add_log(d);
@@ -267,10 +308,14 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
                     const unsigned short off = live ? queue[warp][k] : 0;
                     const bool on = live && !(a.cont && a.cont[begin + off] != 0);
                     const double x = on ? __ldg(a.x + begin + off) : 1.0;
-                    bool fail = false;
+                    bool fail = false, v_fits = true;
                     int made = 0;
-                    double d = lean_tree<KT>(gs, gs.lean, ebig, x, on, &fail, &made);
-                    fail &= on;
+                    const int bb = x > 0 ? 1 : 0;
+                    const LeanTrial c = reg_v_only ? lean_begin_v<KT>(gs, gs.lean, bb, reg_value(0, begin + (on ? off : 0)),
+                                                                      fabs(x) - gs.tn[0], &v_fits)
+                                                   : lean_begin(gs.lean, bb);
+                    double d = lean_tree<KT>(gs, gs.lean, ebig, x, c, on & v_fits, &fail, &made);
+                    fail = (fail | !v_fits) & on;
                     if (on & !fail) {
                         evals += made;
                         d = d * (1 - p_out) + w_out * p_out;
@@ -380,7 +425,7 @@ __global__ void __launch_bounds__(kLikeThreads) k_build_tables(const __grid_cons
     build_gridset<KMAX>(gs, par, a.tab,
                         (a.mode != kModeContaminant && p_out >= 0 && p_out <= 1) ? w_out * p_out : 0.0);
     if (threadIdx.x == 0) {
-        bool uniform = a.mode != kModeMulti && a.mode != kModeMultiRL;
+        bool uniform = a.n_reg == 0;
         for (int k = 0; k < 7; ++k) uniform &= a.trial_stride[k] == 0;
         if (KMAX == 4) build_leanset(gs, gs.lean, par[0], a.nm, uniform);
         else gs.lean.ok = 0;
@@ -473,10 +518,13 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     }
     dim3 grid((unsigned)b.n_sets, (unsigned)b.chunks);
     // z (3) and sz (4) must be uniform per set for the shared start-point tables
+    bool varies[7];  // per-trial columns and regression outcomes
+    for (int k = 0; k < 7; ++k) varies[k] = a.trial_stride[k] != 0;
+    for (int r = 0; r < a.n_reg; ++r) varies[a.reg[r].outcome] = true;
     const bool fast = g_kernel_choice != 1 && a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 &&
-                      b.tab.max_large_k <= 8 && a.trial_stride[3] == 0 && a.trial_stride[4] == 0;
+                      b.tab.max_large_k <= 8 && !varies[3] && !varies[4];
     bool uniform = true;  // everything but the drift is uniform per set
-    for (int k = 1; k < 7; ++k) uniform &= a.trial_stride[k] == 0;
+    for (int k = 1; k < 7; ++k) uniform &= !varies[k];
     const bool gridk = fast && uniform && g_kernel_choice != 2;
     // two passes when threads own several trials each (segments longer than two rounds of the CTA)
     const int64_t longest = a.max_seg_len > 0 ? a.max_seg_len : a.n;

@@ -110,7 +110,7 @@ __device__ __noinline__ void build_leanset(GS& G, LeanSet& L, double v, const Nu
     const double asw = (G.a * G.sv) * wmax;
     double xhi = 25.0 * G.a_sq;
     const double room = 200.0 - (2.0 * G.a) * fabs(v);
-    if (v != 0.0 && room / (v * v) < xhi) xhi = room / (v * v);
+    if (drift_uniform && v != 0.0 && room / (v * v) < xhi) xhi = room / (v * v);  // (per-trial drift: lean_begin_v)
     if (G.xt_hi < xhi) xhi = G.xt_hi;
     L.xhi = xhi;
     // small-time side of the window: 3 terms, then 4 terms (err = 1e-4: 3 below tt = 0.0555, 4 up to 0.154)
@@ -138,8 +138,10 @@ __device__ __noinline__ void build_leanset(GS& G, LeanSet& L, double v, const Nu
     L.g4_hw = (2.0 * G.a_sq) * G.hw;
     L.g4_one = 2.0 * G.a_sq;
     L.k1s = 1.0 / ((144.0 * G.a_sq) * sqrt(2.0 * kPi));
-    L.ok = G.ok && G.support && drift_uniform && mono && G.sz != 0 && G.st != 0 && nm.n_sz > 0 && nm.n_st > 0 &&
-           nm.simps_err >= 0.0 && asw * asw <= 50.0 && xhi > 0.0 && isfinite(v) && isfinite(L.k1) && L.k1 > 0.0 ? 1 : 0;
+    L.uniform = drift_uniform ? 1 : 0;
+    L.ok = G.ok && G.support && mono && G.sz != 0 && G.st != 0 && nm.n_sz > 0 && nm.n_st > 0 &&
+           nm.simps_err >= 0.0 && asw * asw <= 50.0 && xhi > 0.0 && (!drift_uniform || isfinite(v)) && isfinite(L.k1) &&
+           L.k1 > 0.0 ? 1 : 0;
     L.ok_small = L.ok && small_ok && isfinite(L.k1s) ? 1 : 0;
     L.tn17[0] = G.tn[0];
     L.tn17[16] = G.tn[4];
@@ -157,6 +159,7 @@ __device__ __forceinline__ bool below(double xt, unsigned long long edge)
 struct LeanTrial {
     int b;
     double c0h, dc0h, d2ch;
+    double v2h, vb;  // v^2 / 2 and the drift after the boundary flip (src/pdf.pxi:116-118)
 };
 
 // sv marginal of one decision time (src/pdf.pxi:102) times `scale`, at the five start points:
@@ -168,7 +171,7 @@ __device__ __forceinline__ void lean_chain(const LeanSet& L, const LeanTrial& c,
                                            double dd, double scale, double shift0, double shift1, double shift2,
                                            double E[5])
 {
-    E[0] = exp_lean<CLAMP>(fma(fma(-L.v2h, xt, c.c0h), dd, shift0), T) * scale;
+    E[0] = exp_lean<CLAMP>(fma(fma(-c.v2h, xt, c.c0h), dd, shift0), T) * scale;
     const double g0 = exp_lean<CLAMP>(fma(c.dc0h, dd, shift1), T);
     const double r2 = exp_lean<CLAMP>(fma(c.d2ch, dd, shift2), T);
     E[1] = E[0] * g0;
@@ -301,10 +304,9 @@ __device__ __forceinline__ double lean_point_small(const GridSet<KMAX>& G, const
     t = fma(w + 2.0, Rp, t);
     t = fma(w + 4.0, (Rp * Rp) * C2, t);
     neg |= __double2hiint(t);
-    const double vb = c.b ? -L.v : L.v;
     const double asw = (G.a * G.sv) * w;
-    const double ch = 0.5 * fma(asw, asw, -((2.0 * G.a) * vb) * w);
-    return (t * scale) * exp_lean<true>(fma(fma(-L.v2h, xt, ch), dd, -(g * w) * w), T);
+    const double ch = 0.5 * fma(asw, asw, -((2.0 * G.a) * c.vb) * w);
+    return (t * scale) * exp_lean<true>(fma(fma(-c.v2h, xt, ch), dd, -(g * w) * w), T);
 }
 
 // The inner recursion below its first level for a small-time decision time whose stop test failed: f5 = the five
@@ -369,6 +371,25 @@ __device__ __forceinline__ LeanTrial lean_begin(const LeanSet& L, int b)
     c.c0h = L.c0h[b];
     c.dc0h = L.dc0h[b];
     c.d2ch = L.d2ch[b];
+    c.v2h = L.v2h;
+    c.vb = b ? -L.v : L.v;
+    return c;
+}
+
+// The same for a drift that differs from trial to trial (regression on v): the two drift-dependent chain constants
+// are two FMAs per trial.  *fits: the exponent bound the per-set range check makes for a uniform drift.
+template <int KMAX>
+__device__ __forceinline__ LeanTrial lean_begin_v(const GridSet<KMAX>& G, const LeanSet& L, int b, double v, double xt0,
+                                                  bool* fits)
+{
+    LeanTrial c;
+    c.b = b;
+    c.vb = b ? -v : v;
+    c.c0h = 0.5 * fma(-G.aw0[b], c.vb, G.sw0[b]);
+    c.dc0h = 0.5 * fma(-G.daw[b], c.vb, G.dsw[b]);
+    c.d2ch = L.d2ch[b];
+    c.v2h = 0.5 * (v * v);
+    *fits = fma(v * v, xt0, (2.0 * G.a) * fabs(v)) <= 200.0;  // (NaN drift: false)
     return c;
 }
 
@@ -378,9 +399,9 @@ __device__ __forceinline__ LeanTrial lean_begin(const LeanSet& L, int b)
 // evaluator and the return value ignored).
 template <int KMAX>
 __device__ __forceinline__ double lean_trial_large(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
-                                                   int b, double ax, double xt0, double xt4, int wK, bool* need)
+                                                   const LeanTrial& c, double ax, double xt0, double xt4, int wK,
+                                                   bool* need)
 {
-    const LeanTrial c = lean_begin(L, b);
     const double q0 = exp_lean(G.qk * xt0, T);
     int neg = 0;
     bool bad = false;
@@ -414,9 +435,9 @@ __device__ __forceinline__ double lean_trial_large(const GridSet<KMAX>& G, const
 // The same with all five decision times small-time.
 template <int KMAX>
 __device__ __forceinline__ double lean_trial_small(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
-                                                   int b, double ax, double xt0, double xt4, bool any_four, bool* need)
+                                                   const LeanTrial& c, double ax, double xt0, double xt4, bool any_four,
+                                                   bool* need)
 {
-    const LeanTrial c = lean_begin(L, b);
     double I[5];
     int neg = 0;
     bool bad = false;
@@ -440,11 +461,10 @@ __device__ __forceinline__ double lean_trial_small(const GridSet<KMAX>& G, const
 // the complete evaluator.  *n_evals = pdf_sv evaluations made (5 per node + those of inner refinements).
 template <int KMAX>
 __device__ __noinline__ double lean_tree(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
-                                         double x, bool active, bool* fail, int* n_evals)
+                                         double x, const LeanTrial& c, bool active, bool* fail, int* n_evals)
 {
-    const int b = x > 0 ? 1 : 0;
+    const int b = c.b;
     const double ax = fabs(x);
-    const LeanTrial c = lean_begin(L, b);
     bool bad = !(ax == ax) || !(ax - G.t_onset >= 0);  // NaN; before the onset (full_pdf returns 0 without a node)
     DBG(0, active); DBG(2, active & bad);
     int neg = 0, count = 0, extra = 0;
@@ -488,28 +508,37 @@ __device__ __noinline__ double lean_tree(const GridSet<KMAX>& G, const LeanSet& 
         *pass = fabs(D) <= L.thr_out;
         return fma(D, 1.0 / 15.0, S);
     };
-    double I[17];  // (indexed in loops: lives in local memory -- 17 words against ~100 instructions per node)
+    double I[17];  // (indexed in a loop: lives in local memory -- 17 words against ~100 instructions per node)
 #pragma unroll
     for (int m = 0; m < 17; ++m) I[m] = 0.0;
     active &= !bad;
+    // ONE loop over the 17 nodes in level order, so that the node evaluator is inlined once (the deferred-trial
+    // pass is instruction-fetch bound: profiles/r2_v7_ncu_digest_like_B_second.txt)
+    bool refine = false, ql = false, qr = false;
+    double out = 0.0, left = 0.0, right = 0.0;
 #pragma unroll 1
-    for (int m = 0; m < 17; m += 4) I[m] = node(m, active);
-    bool top_ok;
-    double out = simpson(I[0], I[4], I[8], I[12], I[16], &top_ok);
-    const bool refine = active & !top_ok & !bad;  // (a NaN D fails the test, as in the reference)
-    if (__any_sync(0xffffffffu, refine)) {
-#pragma unroll 1
-        for (int m = 2; m < 16; m += 4) I[m] = node(m, refine);
-        bool left_ok, right_ok;
-        double left = 0.5 * simpson(I[0], I[2], I[4], I[6], I[8], &left_ok);
-        double right = 0.5 * simpson(I[8], I[10], I[12], I[14], I[16], &right_ok);
-        const bool ql = refine & !left_ok & !bad, qr = refine & !right_ok & !bad;
-#pragma unroll 1
-        for (int m = 1; m < 16; m += 2) {
-            const bool want = m < 8 ? ql : qr;
-            if (!__any_sync(0xffffffffu, want)) continue;
-            I[m] = node(m, want);
+    for (int s = 0; s < 17; ++s) {
+        if (s == 5) {  // first level done: the top stop test
+            bool top_ok;
+            out = simpson(I[0], I[4], I[8], I[12], I[16], &top_ok);
+            refine = active & !top_ok & !bad;  // (a NaN D fails the test, as in the reference)
+            if (!__any_sync(0xffffffffu, refine)) break;
         }
+        if (s == 9) {  // halves done: their stop tests (same threshold on D'': the tolerance halves with the interval)
+            bool left_ok, right_ok;
+            left = 0.5 * simpson(I[0], I[2], I[4], I[6], I[8], &left_ok);
+            right = 0.5 * simpson(I[8], I[10], I[12], I[14], I[16], &right_ok);
+            ql = refine & !left_ok & !bad;
+            qr = refine & !right_ok & !bad;
+            if (!__any_sync(0xffffffffu, ql | qr)) break;
+        }
+        // level order: 0 4 8 12 16 | 2 6 10 14 | 1 3 5 7 9 11 13 15
+        const int m = s < 5 ? 4 * s : (s < 9 ? 4 * (s - 5) + 2 : 2 * (s - 9) + 1);
+        const bool want = s < 5 ? active : (s < 9 ? refine : (m < 8 ? ql : qr));
+        if (!__any_sync(0xffffffffu, want)) continue;
+        I[m] = node(m, want);
+    }
+    {
         bool dummy;
         if (ql) left = 0.25 * simpson(I[0], I[1], I[2], I[3], I[4], &dummy) +
                        0.25 * simpson(I[4], I[5], I[6], I[7], I[8], &dummy);

@@ -13,7 +13,7 @@ import numpy as np
 from . import _lib
 from ._lib import as_rt_buffer, check, dptr, lib
 
-__all__ = ["full_pdf", "pdf_array", "wiener_like", "wiener_like_multi", "wiener_like_contaminant",
+__all__ = ["Regression", "full_pdf", "pdf_array", "wiener_like", "wiener_like_multi", "wiener_like_contaminant",
            "wiener_like_rlddm", "wiener_like_rl", "wiener_like_multi_rlddm", "wiener_like_rlddm_batch",
            "wiener_like_rl_batch",
            "gen_cdf_using_pdf", "gen_rts_from_cdf", "split_cdf", "wiener_like_batch",
@@ -299,12 +299,78 @@ def wiener_like_multi_batch(x, v_trial, params, err=1e-4, n_st=10, n_sz=10, use_
     return (out, evals.value) if return_evals else out
 
 
+_OUTCOMES = {"v": 0, "sv": 1, "a": 2, "z": 3, "sz": 4, "t": 5, "st": 6}
+_LINKS = {"identity": 0, None: 0, "invlogit": 1, "logistic": 1, "exp": 2}
+
+
+class Regression(object):
+    """Trials and design matrices of an HDDMRegressor node resident on the GPU (hddm_regdata_*): the reference
+    regresses any of v, sv, a, z, sz, t, st (hddm/models/hddm_regression.py:26-36) and calls wiener_like_multi with one
+    per-trial column per outcome; here every coefficient proposal is scored in one launch and the linear predictors
+    are evaluated inside the kernel.
+
+        reg = Regression(x, {"v": design_v, "a": design_a})        # design_*: float64 [K, n], intercept included
+        logp = reg.like_batch({"v": coef_v, "a": coef_a}, params)   # coef_*: [K, P]; params [9, P]
+    `links`: outcome -> "identity" (default) | "invlogit" | "exp", applied to the linear predictor."""
+
+    def __init__(self, x, designs, links=None):
+        x = as_rt_buffer(x)
+        self.n = x.shape[0]
+        self.names = list(designs)
+        if len(self.names) > 4:
+            raise ValueError("at most 4 regressed outcomes")
+        links = links or {}
+        self.outcome = (C.c_int * len(self.names))(*[_OUTCOMES[k] for k in self.names])
+        self.link = (C.c_int * len(self.names))(*[_LINKS[links.get(k)] for k in self.names])
+        mats = []
+        for k in self.names:
+            d = np.ascontiguousarray(designs[k], dtype=np.float64)
+            if d.ndim != 2 or d.shape[1] != self.n or not 1 <= d.shape[0] <= 16:
+                raise ValueError("design of %r must be float64 [K, n] with 1 <= K <= 16" % k)
+            mats.append(d)
+        self.K = [d.shape[0] for d in mats]
+        Ks = (C.c_int64 * len(mats))(*self.K)
+        ptrs = (_lib.c_dp * len(mats))(*[dptr(d) for d in mats])
+        self._h = C.c_void_p()
+        check(lib().hddm_regdata_upload(dptr(x), self.n, len(mats), Ks, ptrs, C.byref(self._h)))
+
+    def like_batch(self, coefs, params, err=1e-4, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-3, return_evals=False):
+        """wiener_like_multi (src/wfpt.pyx:244-274) per coefficient proposal; numerics default to
+        wiener_like_multi's own, as hddm/models/hddm_regression.py:31-36 leaves them."""
+        params = _pack_params(params)
+        P = params.shape[1]
+        mats = []
+        for k, K in zip(self.names, self.K):
+            c = np.ascontiguousarray(coefs[k], dtype=np.float64)
+            if c.shape != (K, P):
+                raise ValueError("coefficients of %r must be [K, P] = %r" % (k, (K, P)))
+            mats.append(c)
+        ptrs = (_lib.c_dp * len(mats))(*[dptr(c) for c in mats])
+        out = np.empty(P, dtype=np.double)
+        evals = C.c_ulonglong(0)
+        check(lib().hddm_regdata_like_batch(self._h, self.outcome, self.link, ptrs, dptr(params), P, err, n_st, n_sz,
+                                            int(bool(use_adaptive)), simps_err, dptr(out),
+                                            C.byref(evals) if return_evals else None))
+        return (out, evals.value) if return_evals else out
+
+    def close(self):
+        if self._h:
+            lib().hddm_regdata_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def wiener_like_regression_batch(x, design, coef, params, err=1e-4, n_st=10, n_sz=10, use_adaptive=1,
                                  simps_err=1e-3, return_evals=False):
-    """Regression layout with the drift built on the GPU: design float64 [K, n] (rows = columns of the design
-    matrix of `v ~ ...`, intercept included), coef float64 [K, P] (columns = coefficient proposals), params
-    [9, P] (row 0 ignored).  Equivalent to wiener_like_multi_batch(x, (design.T @ coef).T, params) without
-    uploading the [P, n] drift table."""
+    """Regression on the drift with the identity link, one shot: design float64 [K, n] (rows = columns of the
+    design matrix of `v ~ ...`, intercept included), coef float64 [K, P] (columns = coefficient proposals), params
+    [9, P] (row 0 ignored).  Equivalent to wiener_like_multi_batch(x, (design.T @ coef).T, params) without ever
+    forming the [P, n] drift table.  (Regression keeps the data on the GPU across calls and takes other outcomes.)"""
     x = as_rt_buffer(x)
     params = _pack_params(params)
     P = params.shape[1]

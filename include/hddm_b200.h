@@ -231,14 +231,28 @@ int hddm_wiener_like_multi_rlddm(const double *x, const int64_t *response, const
                                  const int64_t stride[8], double err, int n_st, int n_sz, int use_adaptive,
                                  double simps_err, double p_outlier, double w_outlier, double *logp);
 
-/* NEW: regression layout with the drift built on the device.  design is float64 [K][n] (one row per
- * column of the patsy design matrix of `v ~ ...`, intercept included), coef float64 [K][P] (one column per
- * coefficient proposal): the drift of trial i under proposal p is sum_k design[k][i] * coef[k][p].  The other
- * eight parameters per proposal in params [9][P] (row 0 ignored).  wiener_like_multi semantics per set
- * (hddm/models/hddm_regression.py:26-36 -> src/wfpt.pyx:244-274).  Only K (n + P) numbers are uploaded. */
+/* NEW: regression likelihood for many coefficient proposals (HDDMRegressor; hddm/models/hddm_regression.py:26-36 ->
+ * wiener_like_multi, src/wfpt.pyx:244-274).  The reference regresses any of v, sv, a, z, sz, t, st and hands the
+ * likelihood one per-trial column per outcome; here the linear predictors are evaluated INSIDE the likelihood
+ * kernel: for regression term r, the value of parameter outcome[r] (0..6 = v sv a z sz t st) of trial i under
+ * proposal p is link[r](sum_k design_r[k][i] * coef_r[k][p]), k ascending, with link 0 = identity, 1 = inverse
+ * logit 1 / (1 + exp(-x)), 2 = exp.  No [P][n] table exists anywhere: no limit on P, K_r (n + P) numbers cross the
+ * host-device link.  hddm_regdata_upload keeps the trials and the design matrices (design[r] is float64 [K[r]][n],
+ * 1 <= K[r] <= 16, at most 4 terms) resident, laid out once by boundary and |rt|; hddm_regdata_like_batch then takes
+ * the coefficients (coef[r] float64 [K[r]][P]) and the remaining parameters (params [9][P]; rows of regressed outcomes
+ * are ignored) and returns wiener_like_multi's value per proposal (+-999 sentinels and all).  A regression on v alone
+ * runs in the lean / grid evaluators; other outcomes in the table-driven or generic ones. */
+typedef struct hddm_regdata hddm_regdata; /* opaque */
+int hddm_regdata_upload(const double *x, int64_t n, int n_terms, const int64_t *K, const double *const *design,
+                        hddm_regdata **out);
+int hddm_regdata_free(hddm_regdata *h);
+int hddm_regdata_like_batch(hddm_regdata *h, const int *outcome, const int *link, const double *const *coef,
+                            const double *params, int64_t P, double err, int n_st, int n_sz, int use_adaptive,
+                            double simps_err, double *logp, unsigned long long *evals);
+/* One-shot form for a regression on v with the identity link: design float64 [K][n], coef float64 [K][P]. */
 int hddm_wiener_like_regression_batch(const double *x, int64_t n, const double *design, int64_t K,
-                                      const double *coef, const double *params, int64_t P, double err,
-                                      int n_st, int n_sz, int use_adaptive, double simps_err, double *logp,
+                                      const double *coef, const double *params, int64_t P, double err, int n_st,
+                                      int n_sz, int use_adaptive, double simps_err, double *logp,
                                       unsigned long long *evals);
 
 /* ---- device-resident trials (one upload per observed node, reused every MCMC step) --------- */

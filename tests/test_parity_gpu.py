@@ -423,6 +423,67 @@ def test_split_sweep_equals_one_launch(W, O, evaluator, onset):
         assert_parity(got["auto"][0][p], want, RTOL_SUM, what="split sweep, set %d" % p)
 
 
+@pytest.mark.parametrize("outcomes", [("v",), ("a",), ("t",), ("v", "a"), ("z", "v"), ("sv", "st"), ("sz",)])
+def test_regression_on_any_outcome(W, O, outcomes):
+    """HDDMRegressor regresses any of v, sv, a, z, sz, t, st (hddm/models/hddm_regression.py:26-36; its own slow
+    tutorial case is a ~ theta:C(conf)): linear predictors evaluated inside the kernel from resident design
+    matrices, links included, against the oracle's wiener_like_multi on the numpy columns.  HDDM numerics."""
+    rng = np.random.default_rng(9460 + len(outcomes) * 7 + sum(map(ord, outcomes[0])))
+    T, P, K = 2500, 7, 3
+    x = draw_rts(rng, T, 0.55)
+    x[::197] = 999.0
+    x[5::233] = -999.0
+    par = draw_params(rng, P)
+    par[6] = np.minimum(par[6], 0.2)      # keep t - st/2 > 0 under a regressed t / st
+    params = np.concatenate([par, np.full((1, P), 0.05), np.full((1, P), 0.1)])
+    names = ("v", "sv", "a", "z", "sz", "t", "st")
+    centre = {"v": (0.0, 2.0, "identity"), "a": (0.4, 0.12, "exp"), "t": (0.45, 0.04, "identity"),
+              "z": (0.0, 0.3, "invlogit"), "sv": (0.0, 0.2, "exp"), "st": (0.12, 0.03, "identity"),
+              "sz": (-2.5, 0.2, "invlogit")}
+    designs, coefs, links, cols = {}, {}, {}, {}
+    for name in outcomes:
+        mu, spread, link = centre[name]
+        designs[name] = np.concatenate([np.ones((1, T)), rng.standard_normal((K - 1, T))])
+        coefs[name] = np.concatenate([mu + spread * rng.uniform(-1, 1, (1, P)), 0.3 * spread * rng.uniform(-1, 1, (K - 1, P))])
+        links[name] = link
+        eta = (designs[name].T @ coefs[name]).T
+        cols[name] = {"identity": eta, "exp": np.exp(eta), "invlogit": 1.0 / (1.0 + np.exp(-eta))}[link]
+    reg = W.Regression(x, designs, links)
+    got = reg.like_batch(coefs, params, n_st=2, n_sz=2)
+    want = []
+    for p in range(P):
+        args = [np.ascontiguousarray(cols[n][p]) if n in outcomes else par[k, p] for k, n in enumerate(names)]
+        want.append(O.wiener_like_multi(x, *args, 1e-4, multi=list(outcomes), n_st=2, n_sz=2, p_outlier=0.05, w_outlier=0.1))
+    assert np.isfinite(want).all()
+    assert_parity(got, np.array(want), RTOL_SUM, what="regression on %s" % (outcomes,))
+    again = reg.like_batch(coefs, params, n_st=2, n_sz=2)
+    assert np.array_equal(got, again)           # resident data, deterministic reduction
+    reg.close()
+
+
+def test_regression_many_proposals_long_segment(W, O):
+    """The C3 bench shape in small: 40000 trials x 300 proposals of v ~ 1 + x1 + x2 (split sweep, lean evaluators with
+    a drift per trial, deferred-trial tree), three proposals against the oracle + pdf_sv counts of the whole launch
+    against the uploaded-table entry point."""
+    rng = np.random.default_rng(9470)
+    T, P, K = 40000, 300, 3
+    x = draw_rts(rng, T, 0.45)
+    par = draw_params(rng, P)
+    params = np.concatenate([par, np.full((1, P), 0.05), np.full((1, P), 0.1)])
+    design = np.concatenate([np.ones((1, T)), rng.standard_normal((K - 1, T))])
+    coef = np.concatenate([par[0][None, :], rng.uniform(-0.4, 0.4, (K - 1, P))])
+    reg = W.Regression(x, {"v": design})
+    got, evals = reg.like_batch({"v": coef}, params, n_st=2, n_sz=2, return_evals=True)
+    for p in (0, 137, 299):
+        v = np.ascontiguousarray(design.T @ coef[:, p])
+        O.pdfsv_calls(reset=True)
+        want = O.wiener_like_multi(x, v, *par[1:, p], 1e-4, multi=["v"], n_st=2, n_sz=2, p_outlier=0.05, w_outlier=0.1)
+        assert_parity(got[p], want, RTOL_SUM, what="regression proposal %d" % p)
+        one, ev_one = reg.like_batch({"v": coef[:, p:p + 1].copy()}, params[:, p:p + 1].copy(), n_st=2, n_sz=2, return_evals=True)
+        assert ev_one == O.pdfsv_calls(reset=True)
+        assert_parity(one[0], want, RTOL_SUM, what="single proposal %d" % p)
+
+
 def test_split_sweep_with_per_trial_drift(W, O, evaluator):
     """The two-launch flavour with a drift per trial (regression sweep built on the device, wiener_like_multi
     semantics: no zero guard) equals the one-launch flavour; oracle parity on one coefficient set."""
