@@ -32,27 +32,47 @@ struct WTable {
     double s[KMAX][kWNodes];  // s[k-1][m] = sin((k*pi) * w[m])   (src/pdf.pxi:62)
 };
 
-// Block-cooperative build of the two tables (index 0: lower boundary, start point z; index 1:
+// A cooperating group of threads for the table builders: the whole CTA (barrier = __syncthreads) or one warp
+// (barrier = __syncwarp, so that several sets are built side by side in one CTA).
+struct BlockGroup {
+    __device__ __forceinline__ int tid() const { return threadIdx.x; }
+    __device__ __forceinline__ int size() const { return blockDim.x; }
+    __device__ __forceinline__ void sync() const { __syncthreads(); }
+};
+struct WarpGroup {
+    __device__ __forceinline__ int tid() const { return threadIdx.x & 31; }
+    __device__ __forceinline__ int size() const { return 32; }
+    __device__ __forceinline__ void sync() const { __syncwarp(); }
+};
+// Virtual thread ids of a lane: a CTA thread has one (its own); lane l of a warp takes (l - 5 j) mod 32 + 32 j for
+// j = 0..7, a rotation per group of 32 so that the few heavy ids of build_gridset (64; 80, 81; 0..4 and 32..39 of the
+// last phase) land on different lanes.
+__device__ __forceinline__ int virtual_tid(const BlockGroup&, int tid, int) { return tid; }
+__device__ __forceinline__ int virtual_tid(const WarpGroup&, int lane, int j) { return ((lane - 5 * j) & 31) + 32 * j; }
+__device__ __forceinline__ int virtual_rounds(const BlockGroup&) { return 1; }
+__device__ __forceinline__ int virtual_rounds(const WarpGroup&) { return 8; }
+
+// Cooperative build of the two tables (index 0: lower boundary, start point z; index 1:
 // upper boundary, start point 1 - z, src/pdf.pxi:116-118) for one parameter set.
-template <int KMAX>
-__device__ __forceinline__ void build_wtables(WTable<KMAX>* T, double z, double sz_raw)
+template <int KMAX, class Group = BlockGroup>
+__device__ __forceinline__ void build_wtables(WTable<KMAX>* T, double z, double sz_raw, Group grp = Group())
 {
-    if (threadIdx.x < 2) {
-        double* w = T[threadIdx.x].w;
-        const double zz = threadIdx.x ? 1. - z : z;
+    if (grp.tid() < 2) {
+        double* w = T[grp.tid()].w;
+        const double zz = grp.tid() ? 1. - z : z;
         const double sz = sz_raw < 1e-3 ? 0.0 : sz_raw;  // src/pdf.pxi:124-125
         w[0] = zz - sz / 2.;
         w[16] = zz + sz / 2.;
         for (int step = 8; step >= 1; step >>= 1)  // src/integrate.pxi:83-85: (lb+ub)/2. recursively
             for (int m = step; m < 16; m += 2 * step) w[m] = (w[m - step] + w[m + step]) / 2.;
     }
-    __syncthreads();
-    for (int item = threadIdx.x; item < 2 * KMAX * kWNodes; item += blockDim.x) {
+    grp.sync();
+    for (int item = grp.tid(); item < 2 * KMAX * kWNodes; item += grp.size()) {
         const int b = item / (KMAX * kWNodes), r = item % (KMAX * kWNodes);
         const int k = r / kWNodes + 1, m = r % kWNodes;
         T[b].s[k - 1][m] = sin(((double)k * kPi) * T[b].w[m]);
     }
-    __syncthreads();
+    grp.sync();
 }
 
 // Per-trial constants after the boundary flip.

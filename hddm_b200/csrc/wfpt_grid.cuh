@@ -170,13 +170,16 @@ __device__ __forceinline__ double xt_threshold(double thr, double a_sq)
     return X;
 }
 
-// Block-cooperative build.  par = v, sv, a, z, sz, t, st of the set (v unused).
-template <int KMAX>
+// Cooperative build (a CTA of >= 256 threads, or one warp: every phase runs over 256 "virtual thread ids", one
+// per thread of a CTA, eight per lane of a warp -- the same arithmetic either way, so the tables are bit-identical).
+// par = v, sv, a, z, sz, t, st of the set (v unused).
+template <int KMAX, class Group = BlockGroup>
 __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par[7], const SeriesTable& tab,
-                                              double mix_floor = 0.0)
+                                              double mix_floor = 0.0, Group grp = Group())
 {
-    build_wtables<KMAX>(G.wt, par[3], par[4]);  // ends with __syncthreads()
-    const int tid = threadIdx.x;
+    build_wtables<KMAX>(G.wt, par[3], par[4], grp);  // ends with a barrier
+  for (int vj = 0; vj < virtual_rounds(grp); ++vj) {
+    const int tid = virtual_tid(grp, grp.tid(), vj);
     const double a = par[2], sv = par[1];
     const double a_sq = a * a;
     const double st = par[6] < 1e-3 ? 0.0 : par[6];
@@ -267,15 +270,19 @@ __device__ __forceinline__ void build_gridset(GridSet<KMAX>& G, const double par
         const int r = tid - 160, b = r / (KMAX * 6), k = (r / 6) % KMAX, i = r % 6;
         G.s5[b][k][i] = i < 5 ? G.wt[b].s[k][4 * i] : 0.0;
     }
-    __syncthreads();
+  }
+    grp.sync();
+  for (int vj = 0; vj < virtual_rounds(grp); ++vj) {
+    const int tid = virtual_tid(grp, grp.tid(), vj);
     if (tid < 5) G.rho[tid] = exp(-G.qk * (G.tn[tid] - G.tn[0]));
     if (tid >= 32 && tid < 32 + kThrWin) {
         const int k = tid - 32, i = G.region0 + k;
         double X = __longlong_as_double(0x7ff0000000000000LL);
-        if (G.ok && i < tab.n_thr && tab.thr[i] <= tt_hi) X = xt_threshold(tab.thr[i], a_sq);
+        if (G.ok && i < tab.n_thr && tab.thr[i] <= 128.0) X = xt_threshold(tab.thr[i], par[2] * par[2]);
         G.xwin[k] = (unsigned long long)__double_as_longlong(X);
     }
-    __syncthreads();
+  }
+    grp.sync();
 }
 
 // (branch, K) code for a positive decision time inside the comfortable range: three-step binary

@@ -236,47 +236,15 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         const bool valid = in_range && !(a.cont && a.cont[i] != 0);
         const double x = valid ? __ldg(a.x + i) : 1.0;
         const int b = x > 0 ? 1 : 0;
-        const double ax = fabs(x);
-        const double xt0 = ax - gs.tn[0], xt4 = ax - gs.tn[4];
-        // every node large-time and inside the comfortable range (x_small: signed compare, a negative or -NaN
-        // decision time fails; +NaN fails the second test)
-        const long long bits4 = __double_as_longlong(xt4);
         bool v_fits = true;
-        const LeanTrial c = reg_v_only ? lean_begin_v<KT>(gs, L, b, reg_value(0, valid ? i : begin), xt0, &v_fits)
+        const LeanTrial c = reg_v_only ? lean_begin_v<KT>(gs, L, b, reg_value(0, valid ? i : begin), fabs(x) - gs.tn[0], &v_fits)
                                        : lean_begin(L, b);
-        const bool large = valid & v_fits & (bits4 >= L.x_small[b]) & (xt0 <= L.xhi);
-        // every node small-time (xt0 below the edge) and inside the comfortable range
-        const bool small = valid & v_fits & !large & (bits4 >= L.x_lo_small[b]) & below(xt0, L.x_edge) & (L.ok_small != 0);
-        // Lean or deferred: a lane in neither class (a node at or before the onset, a trial straddling the
-        // small-/large-time edge, ...) goes to the second pass, whose tree evaluates exactly what the reference's
-        // recursion reaches; the first pass then holds no other code for these sets (it was instruction-fetch bound
-        // on onset-mixed data: profiles/r2_v7_ncu_digest_like_B.txt).  A warp with both classes runs both evaluators.
-        // (a trial before the onset has density exactly 0 and costs the reference no pdf_sv: src/pdf.pxi:111-113)
-        const bool before = valid & ((ax - gs.t_onset) < 0);
-        bool nd = valid & !(large | small | before);
-        double d = 0.0;
-        if (__any_sync(0xffffffffu, large)) {
-            const int K = 1 + (int)below(xt4, L.x_k[0]) + (int)below(xt4, L.x_k[1]) + (int)below(xt4, L.x_k[2]);
-            const int wK = __reduce_max_sync(0xffffffffu, large ? K : 1);
-            bool n1 = false;
-            const double dl = lean_trial_large<KT>(gs, L, ebig, c, ax, xt0, xt4, wK, &n1);
-            if (large) {
-                d = dl;
-                nd = n1;
-            }
-        }
-        if (__any_sync(0xffffffffu, small)) {
-            const bool any_four = __any_sync(0xffffffffu, small & !below(xt0, L.x_s4));
-            bool n2 = false;
-            const double ds = lean_trial_small<KT>(gs, L, ebig, c, ax, xt0, xt4, any_four, &n2);
-            if (small) {
-                d = ds;
-                nd = n2;
-            }
-        }
-        nd &= valid;
+        bool nd = false;
+        int made = 0;
+        double d = lean_first_level<KT>(gs, L, ebig, c, x, valid & v_fits, &nd, &made);
+        nd |= valid & !v_fits;
         if (valid & !nd) {
-            evals += before ? 0 : 25;  // 5 decision times x 5 start points, src/integrate.pxi:131-133,187-198
+            evals += made;
             d = d * (1 - p_out) + w_out * p_out;
             hit_zero |= (d == 0);
             add_log(d);
@@ -436,6 +404,169 @@ __global__ void __launch_bounds__(kLikeThreads) k_build_tables(const __grid_cons
     for (int k = threadIdx.x; k < (int)(sizeof(GridSet<KMAX>) / sizeof(uint4)); k += kLikeThreads) dst[k] = src[k];
 }
 
+// The same tables, one WARP per set (a CTA builds kSetsPerCta sets side by side): for launches of many short
+// segments, where a CTA per set spends its life in the table build's serial sections (~40 us against ~2 us of
+// likelihood for a 200-trial node: profiles/r2_v9_bench_paths.jsonl).  Same arithmetic as k_build_tables.
+constexpr int kWarpSets = 4;        // sets per CTA of the warp-per-set kernels
+constexpr int kWarpMaxTrials = 1024;  // longest segment k_like_warp takes (its deferred-trial queue is 16-bit x 1024)
+template <int KMAX>
+__global__ void __launch_bounds__(32 * kWarpSets) k_build_tables_warp(const __grid_constant__ LikeArgs a, void* out)
+{
+    __shared__ GridSet<KMAX> gs[kWarpSets];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t p = (int64_t)blockIdx.x * kWarpSets + warp;
+    if (p >= a.n_sets) return;
+    GridSet<KMAX>& G = gs[warp];
+    double par[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) par[k] = load_par(a, k, p, 0);
+    const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
+    build_gridset<KMAX, WarpGroup>(G, par, a.tab,
+                                   (a.mode != kModeContaminant && p_out >= 0 && p_out <= 1) ? w_out * p_out : 0.0, WarpGroup());
+    if (lane == 0) {
+        if (KMAX == 4) build_leanset(G, G.lean, par[0], a.nm, true);
+        else G.lean.ok = 0;
+    }
+    __syncwarp();
+    const uint4* src = reinterpret_cast<const uint4*>(&G);
+    uint4* dst = reinterpret_cast<uint4*>(out) + p * (sizeof(GridSet<KMAX>) / sizeof(uint4));
+    for (int k = lane; k < (int)(sizeof(GridSet<KMAX>) / sizeof(uint4)); k += 32) dst[k] = src[k];
+}
+
+// Short segments: every trial's mixed density goes to a scratch row dens[p][.] -- from the lean first level, or, for
+// the trials it defers, from the lean tree, or from the complete one-pass evaluator full_pdf_grid<.., 0> for what the
+// tree cannot settle (and for sets the lean evaluators do not take) -- and ONE warp then reduces the row in a fixed
+// order (lane l takes trials l, l + 32, ...; sum of logs = log of the lane's mantissa product + ln2 * exponents; fixed
+// shuffle tree).  So a set's sum does not depend on who produced the densities: the launch gives a set ONE warp when
+// there are many sets (kWarpSets sets per CTA) and the whole CTA when there are few (its four warps take rounds
+// round-robin: a quarter of the latency), and a scalar wiener_like call and any batch give a set the same sum, bit
+// for bit.  Tables come from `set_tables`.  No partials, no final kernel: logp[p] is written here.
+template <int KMAX>
+__global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_constant__ LikeArgs a, int cta_per_set,
+                                                               double* __restrict__ dens_all, int64_t dens_stride)
+{
+    __shared__ GridSet<KMAX> gsw[kWarpSets];
+    __shared__ double ebig[kExpBig];
+    __shared__ unsigned short queue[kWarpSets][kWarpMaxTrials];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int k = threadIdx.x; k < kExpBig; k += 32 * kWarpSets) ebig[k] = g_exp2_big[k];
+    const int64_t p = cta_per_set ? (int64_t)blockIdx.x : (int64_t)blockIdx.x * kWarpSets + warp;
+    const bool live = p < a.n_sets;
+    GridSet<KMAX>& G = gsw[cta_per_set ? 0 : warp];
+    if (live) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.set_tables) + p * (sizeof(GridSet<KMAX>) / sizeof(uint4));
+        uint4* dst = reinterpret_cast<uint4*>(&G);
+        const int first = cta_per_set ? threadIdx.x : lane, step = cta_per_set ? 32 * kWarpSets : 32;
+        for (int k = first; k < (int)(sizeof(GridSet<KMAX>) / sizeof(uint4)); k += step) dst[k] = __ldg(src + k);
+    }
+    __syncthreads();
+    if (!live) return;
+    const LeanSet& L = G.lean;
+    const int64_t node = a.set_node ? a.set_node[p] : p;
+    const int64_t lo = a.seg ? a.seg[node] : 0;
+    const int64_t hi = a.seg ? a.seg[node + 1] : a.n;
+    const int n = (int)(hi - lo);
+    const double v = load_par(a, 0, p, 0);
+    const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
+    if (!((p_out >= 0) & (p_out <= 1))) {  // src/wfpt.pyx:63-64 (CTA-uniform when cta_per_set)
+        if (lane == 0 && (!cta_per_set || warp == 0)) a.logp[p] = -INFINITY;
+        return;
+    }
+    double* __restrict__ dens = dens_all + p * dens_stride;
+    const double* __restrict__ xs = a.x + lo;
+    const int32_t* __restrict__ skip = a.cont ? a.cont + lo : nullptr;
+    auto mixed = [&](double d) { return d * (1 - p_out) + w_out * p_out; };  // src/wfpt.pyx:70 (contaminant: p_out = 0)
+    const bool lean_ok = KMAX == 4 && L.ok != 0 && L.uniform != 0;
+    const bool tree_ok = lean_ok && a.nm.n_st == 2;
+    unsigned long long evals = 0;
+    int queued = 0;  // warp-uniform
+    DBG(10, lane == 0 && (!cta_per_set || warp == 0));
+    DBG(11, lane == 0 && (!cta_per_set || warp == 0) && !lean_ok);
+    DBG(12, lane == 0 && (!cta_per_set || warp == 0) && !lean_ok && !G.support);
+    DBG(13, lane == 0 && (!cta_per_set || warp == 0) && !lean_ok && G.support && !G.ok);
+    DBG(14, lane == 0 && (!cta_per_set || warp == 0) && !lean_ok && G.support && G.ok && (G.st == 0 || G.sz == 0));
+#pragma unroll 1
+    for (int i0 = cta_per_set ? 32 * warp : 0; i0 < n; i0 += cta_per_set ? 32 * kWarpSets : 32) {
+        const int i = i0 + lane;
+        const bool in_range = i < n;
+        const bool valid = in_range && !(skip && skip[i] != 0);
+        const double x = valid ? __ldg(xs + i) : 1.0;
+        bool need = false;
+        if (lean_ok) {
+            int made = 0;
+            const double d = lean_first_level<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
+            evals += made;
+            if (in_range & !need) dens[i] = valid ? mixed(d) : 1.0;  // (a skipped trial adds log 1)
+        } else {
+            need = valid;
+            if (in_range & !valid) dens[i] = 1.0;
+        }
+        DBG(15, need);
+        const unsigned int votes = __ballot_sync(0xffffffffu, need);
+        if (need) queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] = (unsigned short)i;
+        queued += __popc(votes);
+    }
+    __syncwarp();
+    int left = queued;
+    if (tree_ok) {  // the lean tree over the warp's queue; what it cannot settle is compacted in place
+        left = 0;
+#pragma unroll 1
+        for (int k0 = 0; k0 < queued; k0 += 32) {
+            const int k = k0 + lane;
+            const bool on = k < queued;
+            const unsigned short off = on ? queue[warp][k] : 0;
+            const double x = on ? __ldg(xs + off) : 1.0;
+            bool fail = false;
+            int made = 0;
+            const double d = lean_tree<KMAX>(G, L, ebig, x, lean_begin(L, x > 0 ? 1 : 0), on, &fail, &made);
+            fail &= on;
+            if (on & !fail) {
+                evals += made;
+                dens[off] = mixed(d);
+            }
+            const unsigned int votes = __ballot_sync(0xffffffffu, fail);
+            __syncwarp();
+            if (fail) queue[warp][left + __popc(votes & ((1u << lane) - 1u))] = off;
+            left += __popc(votes);
+            __syncwarp();
+        }
+    }
+    for (int k = lane; k < left; k += 32) {  // the complete evaluator (refinement walks, out-of-range fallback)
+        const unsigned short off = queue[warp][k];
+        dens[off] = mixed(full_pdf_grid<KMAX, 0>(__ldg(xs + off), v, G, a.nm, &a.tab, evals));
+    }
+    if (a.evals) {
+        evals = warp_sum_u64(evals);
+        if (lane == 0) atomicAdd(a.evals, evals);
+    }
+    // the row is complete: one warp reduces it
+    if (cta_per_set) {
+        __syncthreads();
+        if (warp != 0) return;
+    } else {
+        __syncwarp();
+    }
+    double acc = 0.0, mant = 1.0;
+    int expo = 0;
+    bool hit_zero = false;
+    static_assert(kWarpMaxTrials / 32 <= 256, "mantissa product must stay finite");
+    for (int i = lane; i < n; i += 32) {
+        const double d = dens[i];
+        hit_zero |= (d == 0);  // src/wfpt.pyx:71-72, :377-379
+        const int hw = __double2hiint(d);
+        if ((unsigned)(hw - 0x00100000) < 0x7fe00000u) {
+            expo += (hw >> 20) - 1023;
+            mant *= __hiloint2double((hw & 0x000fffff) | 0x3ff00000, __double2loint(d));
+        } else {
+            acc += log(d);
+        }
+    }
+    acc += fma((double)expo, 0.693147180559945309417, log(mant));
+    acc = warp_sum(acc);
+    const bool any_zero = __any_sync(0xffffffffu, hit_zero);
+    if (lane == 0) a.logp[p] = any_zero ? -INFINITY : acc;
+}
+
 __global__ void __launch_bounds__(128) k_like_final(const LikeArgs a)
 {
     const int64_t p = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -566,6 +697,28 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
         const cudaError_t e = cudaGetLastError();
         cudaFreeAsync(bits, stream);
         return e;
+    }
+    // Short segments (one chunk each): a warp per set on tables built by a warp per set.  Whatever the number of
+    // sets -- a scalar wiener_like call and a batch give a set the same sum, bit for bit.
+    if (gridk && !varies[0] && g_kernel_choice == 0 && b.tab.max_large_k <= 4 && a.n_reg == 0 && longest <= kWarpMaxTrials &&
+        (a.mode == kModeWienerLike || a.mode == kModeContaminant)) {
+        keep_pool_memory();
+        void* tables = nullptr;
+        const size_t table_bytes = ((size_t)b.n_sets * sizeof(GridSet<4>) + 255) & ~(size_t)255;
+        const int64_t dens_stride = longest > 0 ? longest : 1;
+        if (cudaMallocAsync(&tables, table_bytes + (size_t)b.n_sets * dens_stride * sizeof(double), stream) == cudaSuccess) {
+            const unsigned blocks = (unsigned)((b.n_sets + kWarpSets - 1) / kWarpSets);
+            k_build_tables_warp<4><<<blocks, 32 * kWarpSets, 0, stream>>>(b, tables);
+            b.set_tables = tables;
+            // few sets: a CTA per set (its four warps share the rounds); many: a warp per set.  Same sums either way.
+            const int cta_per_set = b.n_sets <= 148 * 16 ? 1 : 0;
+            k_like_warp<4><<<cta_per_set ? (unsigned)b.n_sets : blocks, 32 * kWarpSets, 0, stream>>>(
+                b, cta_per_set, reinterpret_cast<double*>(reinterpret_cast<char*>(tables) + table_bytes), dens_stride);
+            const cudaError_t e = cudaGetLastError();
+            cudaFreeAsync(tables, stream);
+            return e;
+        }
+        (void)cudaGetLastError();  // no room for the tables: the CTA-per-set kernels build their own
     }
     // Several CTAs per set and more CTAs than the GPU holds at once: build each set's tables once here too.
     void* shared_tables = nullptr;

@@ -451,6 +451,103 @@ __device__ __forceinline__ double lean_trial_small(const GridSet<KMAX>& G, const
     return out;
 }
 
+// A trial whose five decision times do not share one regime (common in observed data, where RTs sit a few hundred
+// ms after the onset): nodes on both sides of the small-/large-time edge (normalised time ~ 0.15) take the evaluator
+// of their own side; a node at or before the onset is exactly 0 (src/pdf.pxi:92-93); a node in (0, xz) is negligible
+// and taken as 0 (GridSet::xt_zero, checked against the result at the end as in full_pdf_grid); a node below the
+// comfortable range otherwise defers the trial.  Looped over the nodes; the outer level accumulates with the Simpson
+// weights.  `mine`: lanes of this class.
+template <int KMAX>
+__device__ __forceinline__ double lean_trial_mixed(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
+                                                   const LeanTrial& c, double ax, bool mine, bool* need)
+{
+    const int b = c.b;
+    int neg = 0;
+    bool bad = false, saw_tiny = false;
+    double S = 0.0, D = 0.0;
+#pragma unroll 1
+    for (int j = 0; j < 5; ++j) {
+        const double xt = ax - G.tn[j];
+        const long long bits = __double_as_longlong(xt);
+        const bool pos = mine & (xt > 0.0);
+        const bool tiny = pos & (xt < L.xz[b]);
+        saw_tiny |= tiny;
+        const bool live = pos & !tiny;
+        bad |= live & !(bits >= L.x_lo_small[b]);
+        const bool sm = live & !bad & (bits < (long long)L.x_edge), lg = live & !bad & !sm;
+        const int K = 1 + (int)below(xt, L.x_k[0]) + (int)below(xt, L.x_k[1]) + (int)below(xt, L.x_k[2]);
+        const int wK = __reduce_max_sync(0xffffffffu, lg ? K : 1);
+        const bool any_four = __any_sync(0xffffffffu, sm & !below(xt, L.x_s4));
+        double v = 0.0;
+        if (lg) v = lean_node_large<KMAX>(G, L, c, T, xt, exp_lean(G.qk * xt, T), wK, neg, bad);
+        if (sm) v = lean_node_small<KMAX>(G, L, c, T, xt, any_four, neg, bad);
+        const double ws = (j & 1) ? 4.0 : (j == 2 ? 2.0 : 1.0), wd = (j & 1) ? 4.0 : (j == 2 ? -6.0 : -1.0);
+        S = fma(ws, v, S);
+        D = fma(wd, v, D);
+    }
+    bad |= !(fabs(D) <= L.thr_out);
+    const double out = fma(D, 1.0 / 15.0, S);
+    if (saw_tiny && !(fabs(out) > 1e-150) && !(fabs(out) <= 1e-150 && G.mix_floor > 1e-120)) bad = true;
+    *need = bad | (neg < 0);
+    return out;
+}
+
+// The lean first level for one warp round (all 32 lanes call it; `valid` masks lanes without a trial).  Lean or
+// deferred: a lane whose five decision times are all large-time or all small-time and inside the comfortable range
+// is evaluated here; a trial before the onset has density exactly 0 and costs the reference no pdf_sv
+// (src/pdf.pxi:111-113); any other lane (a node at or before the onset, a trial straddling the small-/large-time
+// edge, a failed stop test, ...) sets *need and goes to the deferred-trial pass, whose tree evaluates exactly what
+// the reference's recursion reaches -- so the first pass holds no other code for these sets (it was
+// instruction-fetch bound on onset-mixed data: profiles/r2_v7_ncu_digest_like_B.txt).  A warp with both classes runs
+// both evaluators.  *n_evals = pdf_sv evaluations the reference makes for what was settled here (25 or 0).
+template <int KMAX>
+__device__ __forceinline__ double lean_first_level(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
+                                                   const LeanTrial& c, double x, bool valid, bool* need, int* n_evals)
+{
+    const int b = c.b;
+    const double ax = fabs(x);
+    const double xt0 = ax - G.tn[0], xt4 = ax - G.tn[4];
+    // x_small: signed compare, a negative or -NaN decision time fails; +NaN fails the second test
+    const long long bits4 = __double_as_longlong(xt4);
+    const bool large = valid & (bits4 >= L.x_small[b]) & (xt0 <= L.xhi);
+    const bool small = valid & !large & (bits4 >= L.x_lo_small[b]) & below(xt0, L.x_edge) & (L.ok_small != 0);
+    const bool before = valid & ((ax - G.t_onset) < 0);
+    // anything else that starts inside the range: nodes on both sides of the edge, nodes at or before the onset
+    const bool mixed = valid & !large & !small & !before & (xt0 <= L.xhi) & (L.ok_small != 0);
+    bool nd = valid & !(large | small | mixed | before);
+    double d = 0.0;
+    if (__any_sync(0xffffffffu, large)) {
+        const int K = 1 + (int)below(xt4, L.x_k[0]) + (int)below(xt4, L.x_k[1]) + (int)below(xt4, L.x_k[2]);
+        const int wK = __reduce_max_sync(0xffffffffu, large ? K : 1);
+        bool n1 = false;
+        const double dl = lean_trial_large<KMAX>(G, L, T, c, ax, xt0, xt4, wK, &n1);
+        if (large) {
+            d = dl;
+            nd = n1;
+        }
+    }
+    if (__any_sync(0xffffffffu, small)) {
+        const bool any_four = __any_sync(0xffffffffu, small & !below(xt0, L.x_s4));
+        bool n2 = false;
+        const double ds = lean_trial_small<KMAX>(G, L, T, c, ax, xt0, xt4, any_four, &n2);
+        if (small) {
+            d = ds;
+            nd = n2;
+        }
+    }
+    if (__any_sync(0xffffffffu, mixed)) {
+        bool n3 = false;
+        const double dm = lean_trial_mixed<KMAX>(G, L, T, c, ax, mixed, &n3);
+        if (mixed) {
+            d = dm;
+            nd = n3;
+        }
+    }
+    *need = nd;
+    *n_evals = (valid & !nd & !before) ? 25 : 0;  // 5 decision times x 5 start points, src/integrate.pxi:131-133,187-198
+    return d;
+}
+
 // Deferred trials, HDDM numerics (n_st == 2): the whole outer recursion of src/integrate.pxi:143-178 for one trial,
 // lane-synchronous.  Its decision-time nodes are per-set constants (tn17); a lane evaluates a node only if the
 // reference's recursion reaches it (first level m = 0,4,8,12,16; the halves add m = 2,6 / 10,14 when the top stop
