@@ -17,9 +17,10 @@ pytestmark = pytest.mark.gpu
 HDDM = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
 # dmat_cdf_array with sz or st < 1e-3: the reference differences two series 1e-10 apart (src/cdfdif.c:135-148), so
 # its own output moves by `band` under a ONE-ulp nudge of a parameter (tests/util.py:cdf_noise_band); the kernel
-# may differ from the fixture by this many bands there.  Measured need per fixture case: see CDF_BAND_USED below
-# (printed by the test); the factor is twice the largest observed.
-CDF_BAND_FACTOR = 64
+# may differ from the fixture by this many bands there.  Measured need per fixture case (B200, round 2, printed by the
+# test into CDF_BAND_USED): 0 for the eight cases with sz, st >= 1e-3 or where 1e-10 holds anyway, 0.76 / 0.92 / 0.84
+# for cases 3, 4, 8 and 5.38 for case 6 (sz = st = 0); the factor is about twice the largest observed.
+CDF_BAND_FACTOR = 12
 CDF_BAND_USED = {}
 
 
