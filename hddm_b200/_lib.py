@@ -72,6 +72,7 @@ SIGNATURES = {
                              [C.POINTER(C.c_uint64), _l, c_dp, c_dp, c_lp]),
     "hddm_wiener_like_batch_scratch": (_l, [_l, _l]),
     "hddm_wiener_like_batch_dev": (_i, [_v, _l, _v, _l, _v, _l] + _NUM + [_v, _v, _v, _v]),
+    "hddm_wiener_like_batch_dev_static": (_i, [_v, _l, _v, _l, _v, _l] + _NUM + [_v, _v, _v]),
     "hddm_pdf_array_dev": (_i, [_v, _l] + [_d] * 7 + [_d, _i, _i, _i, _i, _d, _d, _d, _v, _v, _v]),
     "hddm_dmat_cdf_array_dev": (_i, [_v, _l] + [_d] * 9 + [_v, _v]),
 }

@@ -725,6 +725,55 @@ int hddm_wiener_like_batch_dev(const double* d_x, int64_t n, const int64_t* d_se
     return HDDM_OK;
 }
 
+// No counterpart in the reference: hddm_wiener_like_batch_dev for callers that may not allocate (include/hddm_b200.h).
+// Nothing here or below it calls cudaMalloc*, cudaFree* or creates a stream: the library must already be bound to
+// the device (hddm_b200_init at set-up), the partial sums live in the static array of wfpt_kernels.cu.
+int hddm_wiener_like_batch_dev_static(const double* d_x, int64_t n, const int64_t* d_seg, int64_t max_seg_len,
+                                      const double* d_params, int64_t P, double err, int n_st, int n_sz,
+                                      int use_adaptive, double simps_err, double* d_logp,
+                                      unsigned long long* d_evals, void* stream)
+{
+    if (n < 0 || P < 0 || (P > 0 && (!d_params || !d_logp)) || (n > 0 && !d_x) || (d_seg && max_seg_len < 0))
+        return fail(HDDM_ERR_ARG, "batch_dev_static: bad buffer or size");
+    {
+        std::lock_guard<std::mutex> lock(g_rt.mu);
+        if (!g_rt.ready)
+            return fail(HDDM_ERR_ARG, "batch_dev_static: call hddm_b200_init(device) at set-up first "
+                                      "(this entry point binds no device and creates nothing)");
+        TRY(ensure_ready());  // bound already: only checks that the bound device is the current one
+    }
+    TRY(check_numerics(n_st, n_sz, use_adaptive));
+    if (P == 0) return HDDM_OK;
+    const int64_t chunks = chunks_for(d_seg ? max_seg_len : n);
+    if (chunks > 65535) return fail(HDDM_ERR_ARG, "more than 65535*2048 trials per parameter set");
+    if (P > kStaticPartialDoubles || P * chunks > kStaticPartialDoubles) {
+        snprintf(g_err, sizeof(g_err), "batch_dev_static: %lld sets x %lld blocks of 2048 trials need %lld doubles of "
+                 "scratch, the static array holds %lld (2 MiB); use hddm_wiener_like_batch_dev with caller scratch",
+                 (long long)P, (long long)chunks, (long long)(P * chunks), (long long)kStaticPartialDoubles);
+        return HDDM_ERR_ARG;
+    }
+    LikeArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = d_x;
+    a.seg = d_seg;
+    for (int k = 0; k < kNumPar; ++k) {
+        a.par[k] = d_params + k * P;
+        a.set_stride[k] = 1;
+        a.trial_stride[k] = 0;
+    }
+    a.n = n;
+    a.n_sets = P;
+    a.max_seg_len = d_seg ? max_seg_len : n;
+    a.chunks = (int)chunks;
+    a.mode = kModeWienerLike;
+    a.nm = make_numerics(err, n_st, n_sz, use_adaptive, simps_err);
+    a.partial = nullptr;  // launch_like_static points it at its array
+    a.logp = d_logp;
+    a.evals = d_evals;
+    CUDA_TRY(launch_like_static(a, (cudaStream_t)stream));
+    return HDDM_OK;
+}
+
 int hddm_pdf_array_dev(const double* d_x, int64_t n, double v, double sv, double a, double z, double sz,
                        double t, double st, double err, int logp, int n_st, int n_sz, int use_adaptive,
                        double simps_err, double p_outlier, double w_outlier, double* d_y,

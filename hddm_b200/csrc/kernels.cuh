@@ -111,6 +111,11 @@ struct LikeArgs {
 };
 
 cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream);
+// Allocation-free variant (hddm_wiener_like_batch_static): same kernels, the per-CTA partial sums in a file-scope
+// __device__ array of kStaticPartialDoubles doubles instead of caller / pool memory; a.partial is ignored.
+// Returns cudaErrorInvalidValue when n_sets * chunks exceeds the array.
+constexpr int64_t kStaticPartialDoubles = 1 << 18;  // 2 MiB per GPU that loads the library
+cudaError_t launch_like_static(const LikeArgs& a, cudaStream_t stream);
 extern int g_kernel_choice;  // 0 auto, 1 generic evaluator only, 2 no grid evaluator, 3 grid evaluator in one pass only,
                              // 4 grid evaluator with both passes in one launch
 

@@ -758,6 +758,87 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     return e;
 }
 
+// ---- allocation-free variant of the batched likelihood ------------------------------------------------------
+// For callers that may not allocate (CUDA graph capture, serving loops): the [n_sets][chunks] partial sums that
+// k_like_partial writes and k_like_final adds up live in this file-scope array instead of caller or pool memory,
+// and the launch takes the route of launch_like that needs nothing else (every CTA builds its set's tables in
+// shared memory; both passes in one launch).  Every GPU that loads the library holds the 2 MiB until exit.
+// Each (set, chunk) slot is written by its CTA before k_like_final reads it, so nothing has to start at zero and
+// the contents left by the previous call are never read; calls that overlap on the GPU (two streams) race on it.
+static __device__ __align__(256) double g_static_partial[kStaticPartialDoubles];
+
+// In host code `g_static_partial` is the host-side stand-in of the symbol, not a device address: the address is
+// asked for once per device, with that device current.
+static cudaError_t static_partial_address(double** out)
+{
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static double* address[kMaxDevices] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!address[dev]) {
+        double* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_static_partial);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        address[dev] = p;
+    }
+    *out = address[dev];
+    return cudaSuccess;
+}
+
+cudaError_t launch_like_static(const LikeArgs& a, cudaStream_t stream)
+{
+    if (a.n_sets <= 0) return cudaSuccess;
+    if (a.chunks < 1 || (int64_t)a.n_sets * a.chunks > kStaticPartialDoubles) return cudaErrorInvalidValue;
+    {
+        const cudaError_t e = ensure_exp_table();  // one upload per process, no allocation
+        if (e != cudaSuccess) return e;
+    }
+    LikeArgs b = a;
+    {
+        const cudaError_t e = static_partial_address(&b.partial);
+        if (e != cudaSuccess) return e;
+    }
+    b.tab = series_table_for(a.nm.err);
+    b.trials_per_block = kTrialsPerBlock;  // chunks stays as the caller gave it: 2048 trials per CTA
+    b.defer_bits = nullptr;
+    b.partial2 = nullptr;
+    b.chunks2 = 0;
+    b.set_tables = nullptr;
+    const dim3 grid((unsigned)b.n_sets, (unsigned)b.chunks);
+    bool varies[7];
+    for (int k = 0; k < 7; ++k) varies[k] = a.trial_stride[k] != 0;
+    for (int r = 0; r < a.n_reg; ++r) varies[a.reg[r].outcome] = true;
+    const bool fast = a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 && b.tab.max_large_k <= 8 && !varies[3] && !varies[4];
+    bool uniform = true;
+    for (int k = 1; k < 7; ++k) uniform &= !varies[k];
+    const bool gridk = fast && uniform;
+    const int64_t longest = a.max_seg_len > 0 ? a.max_seg_len : a.n;
+    const bool two_pass = gridk && longest > 2 * kLikeThreads;
+    if (two_pass && b.tab.max_large_k <= 4)
+        k_like_partial<4, true, kTwoPass><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (two_pass)
+        k_like_partial<8, true, kTwoPass><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (gridk && b.tab.max_large_k <= 4)
+        k_like_partial<4, true, kOnePass><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (gridk)
+        k_like_partial<8, true><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (fast && b.tab.max_large_k <= 4)
+        k_like_partial<4, false><<<grid, kLikeThreads, 0, stream>>>(b);
+    else if (fast)
+        k_like_partial<8, false><<<grid, kLikeThreads, 0, stream>>>(b);
+    else
+        k_like_partial<0, false><<<grid, kLikeThreads, 0, stream>>>(b);
+    if (b.chunks == 1) return cudaGetLastError();  // k_like_partial wrote logp itself
+    const int sets_per_block = 128 / 32;
+    k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(b);
+    return cudaGetLastError();
+}
+
 // pdf_array (src/wfpt.pyx:32-48): per-trial density, outlier mix, optional log.
 template <int KMAX, bool GRID>
 __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)

@@ -311,6 +311,23 @@ int hddm_wiener_like_batch_dev(const double *d_x, int64_t n, const int64_t *d_se
                                const double *d_params, int64_t P, double err, int n_st, int n_sz,
                                int use_adaptive, double simps_err, double *d_logp, double *d_scratch,
                                unsigned long long *d_evals, void *stream);
+/* No counterpart in the reference.  hddm_wiener_like_batch_dev
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc): same inputs and outputs, no d_scratch argument -- the per-block partial sums go to a static
+ * __device__ array inside the library (2 MiB = 262144 doubles, held by every GPU that loads the library until
+ * exit).  The call allocates nothing, frees nothing and creates nothing: the library must already be bound to the
+ * current device (hddm_b200_init at set-up, else HDDM_ERR_ARG); the first call per device also looks up the
+ * array's device address and uploads the 16 KB exponential table, so make one call before a capture.
+ * LIMIT: P * ceil(longest segment / 2048) <= 262144, else HDDM_ERR_ARG with the sizes in hddm_b200_last_error().
+ * All calls share the one array.  Nothing in it has to start at zero (each slot is written before it is read,
+ * the previous call's contents are never read), but two calls that OVERLAP on the GPU (different streams)
+ * race on it: keep calls to this entry point on one stream, or order them with events.
+ * Sums are taken per 2048-trial block, then over blocks in ascending order: equal to hddm_wiener_like_batch_dev
+ * within the summation tolerance (1e-9 relative), not bit for bit (that entry point picks other block sizes). */
+int hddm_wiener_like_batch_dev_static(const double *d_x, int64_t n, const int64_t *d_seg, int64_t max_seg_len,
+                                      const double *d_params, int64_t P, double err, int n_st, int n_sz,
+                                      int use_adaptive, double simps_err, double *d_logp,
+                                      unsigned long long *d_evals, void *stream);
 int hddm_pdf_array_dev(const double *d_x, int64_t n, double v, double sv, double a, double z,
                        double sz, double t, double st, double err, int logp, int n_st, int n_sz,
                        int use_adaptive, double simps_err, double p_outlier, double w_outlier,
