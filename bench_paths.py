@@ -154,7 +154,7 @@ def main():
         from hddm_b200 import likelihoods as L
         S, Tn = 20, 200
         nodes = L.BatchedNodes([rts(rng, Tn, 0.45) for _ in range(S)])
-        for per_node in (1, 16, 205):
+        for per_node in (1, 16, 205, 4096):
             P = S * per_node
             params = np.concatenate([draw(rng, P), np.full((1, P), 0.05), np.full((1, P), 0.1)])
             set_node = np.tile(np.arange(S, dtype=np.int64), per_node)

@@ -32,6 +32,7 @@ int ppc_slab(const double* d_grid, int64_t m, const double* h_params, int64_t D,
     const size_t off_u = h_u ? L.reserve((size_t)Dn * S * sizeof(double)) : 0;
     const size_t off_r = L.reserve((size_t)Dn * S * sizeof(double));
     const size_t off_st = L.reserve((size_t)Dn * kPpcStats * sizeof(double));
+    const size_t off_last = L.reserve((size_t)Dn * sizeof(double));
     // the grid lives at the front of the arena (reserved by the caller): keep it there
     const size_t grid_bytes = align_up((size_t)m * sizeof(double));
     char* base = g_rt.arena + grid_bytes;
@@ -57,9 +58,9 @@ int ppc_slab(const double* d_grid, int64_t m, const double* h_params, int64_t D,
     pa.n_sets = Dn;
     pa.x_set_stride = 0;
     CUDA_TRY(launch_pdf_array(pa, s));
-    CUDA_TRY(launch_cumsum_normalise_batch(at(off_tab), m, Dn, s));
+    CUDA_TRY(launch_cumsum_batch(at(off_tab), m, Dn, at(off_last), s));
     CUDA_TRY(launch_sample_rts_batch(pa.x, at(off_tab), m, h_f ? at(off_f) : nullptr, h_u ? at(off_u) : nullptr,
-                                     S, Dn, at(off_tt), at(off_tt) + Dn, seed, first_draw + d0, at(off_r), s));
+                                     S, Dn, at(off_tt), at(off_tt) + Dn, seed, first_draw + d0, at(off_last), at(off_r), s));
     if (h_stats) {
         CUDA_TRY(launch_ppc_stats(at(off_r), S, Dn, at(off_st), s));
         CUDA_TRY(cudaMemcpyAsync(h_stats + (size_t)d0 * kPpcStats, at(off_st),
@@ -90,7 +91,7 @@ int ppc_impl(const double* xgrid, int64_t m, const double* params, int64_t D, co
     if (slab < 1) slab = 1;
     if (slab > 32768) slab = 32768;
     if (slab > D) slab = D;
-    const size_t per_draw = (size_t)m * 8 + (size_t)S * 8 * 3 + (kNumPar + 2 + kPpcStats) * 8;
+    const size_t per_draw = (size_t)m * 8 + (size_t)S * 8 * 3 + (kNumPar + 3 + kPpcStats) * 8;
     TRY(ensure_arena(align_up((size_t)m * sizeof(double)) + (size_t)slab * per_draw + (16 << 10)));
     cudaStream_t s = g_rt.stream;
     CUDA_TRY(cudaMemcpyAsync(g_rt.arena, xgrid, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, s));

@@ -47,8 +47,15 @@ constexpr int kTrialsPerBlock = 2048;  // one CTA reduces this many trials of on
 #define HDDM_UNROLL_J 5
 #endif
 constexpr int kTrialsPerBigBlock = HDDM_BIG_BLOCK;  // ... or this many when the grid is large enough anyway (launch_like)
-constexpr int kBlocksPerDeferredCta = 8;  // second launch of a split sweep: blocks of trials per CTA (one table build)
+#ifndef HDDM_DEFER_SPAN
+#define HDDM_DEFER_SPAN 1
+#endif
+constexpr int kBlocksPerDeferredCta = HDDM_DEFER_SPAN;  // second launch of a split sweep: blocks of trials per CTA (one table build)
 constexpr int kUnrollJ = HDDM_UNROLL_J;  // first pass: the five decision-time nodes of a trial are unrolled (5) or looped (1)
+#ifndef HDDM_PDF_ILP
+#define HDDM_PDF_ILP 2
+#endif
+constexpr int kPdfIlp = HDDM_PDF_ILP;  // k_pdf_array, one decision time per point: points per thread in flight
 #ifndef HDDM_LIKE_THREADS
 #define HDDM_LIKE_THREADS 256
 #endif
@@ -160,14 +167,15 @@ cudaError_t launch_sample_rts(const double* xgrid, const double* table, int64_t 
                               double* rts, cudaStream_t stream);
 
 // Posterior-predictive batch (ppc_kernels.cu): D draws share the grid; tables is [D][m] densities in,
-// normalised rectangle-rule cumulative tables out (src/wfpt.pyx:333-340 per draw).
-cudaError_t launch_cumsum_normalise_batch(double* tables, int64_t m, int64_t D, cudaStream_t stream);
+// rectangle-rule running sums out (src/wfpt.pyx:333-336 per draw) with last[d] = the final entry: the lookup
+// below divides the entries it probes by it (:337-340).
+cudaError_t launch_cumsum_batch(double* tables, int64_t m, int64_t D, double* last, cudaStream_t stream);
 // rts[d][s] by inverse-CDF lookup (src/wfpt.pyx:344-353); t / st per draw; uniforms either supplied
 // (f, u_delay: [D][S]) or, when f == nullptr, drawn on the device from Philox(seed, draw0 + d, s).
 cudaError_t launch_sample_rts_batch(const double* xgrid, const double* tables, int64_t m, const double* f,
                                     const double* u_delay, int64_t S, int64_t D, const double* t,
-                                    const double* st, unsigned long long seed, int64_t draw0, double* rts,
-                                    cudaStream_t stream);
+                                    const double* st, unsigned long long seed, int64_t draw0,
+                                    const double* last, double* rts, cudaStream_t stream);
 // Summary statistics of hddm/utils.py:241-267 (gen_ppc_stats) per draw: stats[d][15] = accuracy,
 // mean_ub, std_ub, 10/30/50/70/90 q_ub, mean_lb, std_lb, 10/30/50/70/90 q_lb.  S <= kPpcMaxSamples.
 constexpr int kPpcStats = 15;

@@ -17,11 +17,21 @@ namespace hddm {
 namespace {
 
 constexpr int kScanThreads = 1024;
+constexpr int kScanCols = 8;                    // slice elements staged per round (two CTAs per SM)
+constexpr int kScanPitch = kScanCols + 1;       // odd pitch: the row-wise pass is free of bank conflicts
+constexpr size_t kScanTileBytes = (size_t)kScanThreads * kScanPitch * sizeof(double);
 
-// Rectangle-rule running sum from index 1 with table[0] = 0, then division by the last entry
-// (src/wfpt.pyx:333-340).  Same fixed-order blocked scan as gen_kernels.cu, one CTA per draw.
-__global__ void __launch_bounds__(kScanThreads) k_cumsum_batch(double* tables, int64_t m)
+// Rectangle-rule running sum from index 1 with table[0] = 0 (src/wfpt.pyx:333-336), one CTA per draw.  The
+// arithmetic is that of k_scan_normalise<1> (gen_kernels.cu), element for element: thread j owns the contiguous
+// slice j and adds it in ascending order, slice totals are combined in ascending order -- so a batch and D single
+// calls give the same tables.  What differs is how the numbers travel: slices are staged through a shared-memory
+// tile, 8 elements of every slice per round, read and written as 64-byte runs (a thread walking its own slice
+// in global memory costs a sector per element and lane), and the division by the last entry (:337-340) is left to
+// the lookup, which divides the entries it probes by last[d] -- the same quotient, 17 of them per simulated trial
+// instead of one pass over the table.
+__global__ void __launch_bounds__(kScanThreads) k_cumsum_batch(double* tables, int64_t m, double* __restrict__ last)
 {
+    extern __shared__ double tile[];  // [kScanThreads][kScanPitch]
     __shared__ double slice_total[kScanThreads];
     __shared__ double slice_offset[kScanThreads];
     double* table = tables + (int64_t)blockIdx.x * m;
@@ -29,8 +39,25 @@ __global__ void __launch_bounds__(kScanThreads) k_cumsum_batch(double* tables, i
     const int64_t per = (m - 1 + kScanThreads - 1) / kScanThreads;
     const int64_t lo = 1 + (int64_t)j * per;
     const int64_t hi = lo + per < m ? lo + per : m;
+    const int mine = hi > lo ? (int)(hi - lo) : 0;  // elements of this thread's slice
+    auto stage = [&](int64_t c0, bool store) {      // tile <-> slices' elements [c0, c0 + kScanCols)
+        for (int idx = j; idx < kScanThreads * kScanCols; idx += kScanThreads) {
+            const int row = idx / kScanCols, col = idx % kScanCols;
+            const int64_t i = 1 + (int64_t)row * per + c0 + col;
+            if (c0 + col < per && i < m) {
+                if (store) table[i] = tile[row * kScanPitch + col];
+                else tile[row * kScanPitch + col] = table[i];
+            }
+        }
+    };
     double run = 0.0;
-    for (int64_t i = lo; i < hi; ++i) run += table[i];
+    for (int64_t c0 = 0; c0 < per; c0 += kScanCols) {
+        stage(c0, false);
+        __syncthreads();
+        const int n = mine - (int)c0 < kScanCols ? mine - (int)c0 : kScanCols;
+        for (int c = 0; c < n; ++c) run += tile[j * kScanPitch + c];
+        __syncthreads();
+    }
     slice_total[j] = run;
     __syncthreads();
     if (j == 0) {
@@ -42,15 +69,21 @@ __global__ void __launch_bounds__(kScanThreads) k_cumsum_batch(double* tables, i
     }
     __syncthreads();
     run = slice_offset[j];
-    for (int64_t i = lo; i < hi; ++i) {
-        run += table[i];
-        table[i] = run;
+    for (int64_t c0 = 0; c0 < per; c0 += kScanCols) {
+        stage(c0, false);
+        __syncthreads();
+        const int n = mine - (int)c0 < kScanCols ? mine - (int)c0 : kScanCols;
+        for (int c = 0; c < n; ++c) {
+            run += tile[j * kScanPitch + c];
+            tile[j * kScanPitch + c] = run;
+        }
+        __syncthreads();
+        stage(c0, true);
+        __syncthreads();
     }
     if (j == 0) table[0] = 0.0;
-    __syncthreads();
-    const double last = table[m - 1];
-    __syncthreads();
-    for (int64_t i = j; i < m; i += kScanThreads) table[i] = table[i] / last;
+    if (hi == m && mine > 0) last[blockIdx.x] = run;  // the thread that owns table[m - 1]
+    if (m == 1 && j == 0) last[blockIdx.x] = 0.0;     // (a one-point grid: 0 / 0, as the reference)
 }
 
 // rt = x[searchsorted(table_d, f, 'left')] + sign(rt) * (t_d | u * st_d + (t_d - st_d/2))
@@ -62,13 +95,14 @@ __global__ void __launch_bounds__(256) k_sample_batch(const double* __restrict__
                                                       const double* __restrict__ t_par,
                                                       const double* __restrict__ st_par,
                                                       unsigned long long seed, int64_t draw0,
-                                                      double* __restrict__ rts)
+                                                      const double* __restrict__ last, double* __restrict__ rts)
 {
     const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t d = blockIdx.y;
     if (s >= S) return;
     const double* table = tables + d * m;
     const double t = t_par[d], st = st_par[d];
+    const double total = last[d];  // table[m - 1] of the running sum: entries are normalised as they are probed
     double target, u = 0.0;
     if (f) {
         target = f[d * S + s];
@@ -83,7 +117,7 @@ __global__ void __launch_bounds__(256) k_sample_batch(const double* __restrict__
     int64_t lo = 0, hi = m;
     while (lo < hi) {
         const int64_t mid = lo + ((hi - lo) >> 1);
-        if (table[mid] < target) lo = mid + 1; else hi = mid;
+        if (table[mid] / total < target) lo = mid + 1; else hi = mid;
     }
     if (lo >= m) lo = m - 1;
     const double rt = xgrid[lo];
@@ -198,22 +232,29 @@ __global__ void __launch_bounds__(kStatThreads) k_ppc_stats(const double* __rest
 
 }  // namespace
 
-cudaError_t launch_cumsum_normalise_batch(double* tables, int64_t m, int64_t D, cudaStream_t stream)
+cudaError_t launch_cumsum_batch(double* tables, int64_t m, int64_t D, double* last, cudaStream_t stream)
 {
     if (m <= 0 || D <= 0) return cudaSuccess;
-    k_cumsum_batch<<<(unsigned)D, kScanThreads, 0, stream>>>(tables, m);
+    static bool opted_in = false;  // (one device per process: hddm_b200_init)
+    if (!opted_in) {
+        cudaError_t e = cudaFuncSetAttribute(k_cumsum_batch, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kScanTileBytes);
+        if (e != cudaSuccess) return e;
+        opted_in = true;
+    }
+    k_cumsum_batch<<<(unsigned)D, kScanThreads, kScanTileBytes, stream>>>(tables, m, last);
     return cudaGetLastError();
 }
 
 cudaError_t launch_sample_rts_batch(const double* xgrid, const double* tables, int64_t m, const double* f,
                                     const double* u_delay, int64_t S, int64_t D, const double* t,
-                                    const double* st, unsigned long long seed, int64_t draw0, double* rts,
-                                    cudaStream_t stream)
+                                    const double* st, unsigned long long seed, int64_t draw0,
+                                    const double* last, double* rts, cudaStream_t stream)
 {
     if (S <= 0 || D <= 0) return cudaSuccess;
     if (D > 65535) return cudaErrorInvalidValue;
     dim3 grid((unsigned)((S + 255) / 256), (unsigned)D);
-    k_sample_batch<<<grid, 256, 0, stream>>>(xgrid, tables, m, f, u_delay, S, t, st, seed, draw0, rts);
+    k_sample_batch<<<grid, 256, 0, stream>>>(xgrid, tables, m, f, u_delay, S, t, st, seed, draw0, last, rts);
     return cudaGetLastError();
 }
 

@@ -122,7 +122,8 @@ struct alignas(16) LeanSet {
     // reference's midpoint rule, src/integrate.pxi:153-155): the deferred-trial tree of wfpt_lean.cuh
     double tn17[17];
     double v;              // the set's drift (boundary flip applied per trial)
-    int uniform, pad_u;    // the drift-dependent constants above belong to the set (else: per trial, lean_begin_v)
+    int uniform;           // the drift-dependent constants above belong to the set (else: per trial, lean_begin_v)
+    int ok1;               // st == 0 (one decision time, src/pdf.pxi:137-141): bit 0 lean_single applies, bit 1 to small-time nodes too
     double xz[2];          // decision times in (0, xz[b]) are negligible nodes (GridSet::xt_zero; 0: none are)
     double pad17;
 };

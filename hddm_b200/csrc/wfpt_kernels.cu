@@ -408,6 +408,7 @@ __global__ void __launch_bounds__(kLikeThreads) k_build_tables(const __grid_cons
 // segments, where a CTA per set spends its life in the table build's serial sections (~40 us against ~2 us of
 // likelihood for a 200-trial node: profiles/r2_v9_bench_paths.jsonl).  Same arithmetic as k_build_tables.
 constexpr int kWarpSets = 4;        // sets per CTA of the warp-per-set kernels
+constexpr int kWarpOneLaunchSets = 1024;  // k_like_warp: up to this many sets run all phases in one launch (latency path)
 constexpr int kWarpMaxTrials = 1024;  // longest segment k_like_warp takes (its deferred-trial queue is 16-bit x 1024)
 template <int KMAX>
 __global__ void __launch_bounds__(32 * kWarpSets) k_build_tables_warp(const __grid_constant__ LikeArgs a, void* out)
@@ -441,17 +442,26 @@ __global__ void __launch_bounds__(32 * kWarpSets) k_build_tables_warp(const __gr
 // there are many sets (kWarpSets sets per CTA) and the whole CTA when there are few (its four warps take rounds
 // round-robin: a quarter of the latency), and a scalar wiener_like call and any batch give a set the same sum, bit
 // for bit.  Tables come from `set_tables`.  No partials, no final kernel: logp[p] is written here.
-template <int KMAX>
+// PHASE 0: everything in one launch (a handful of sets: the latency path of a single chain).  Otherwise two launches,
+// so that the warps of an SM are not spread over the lean level, the tree and the complete evaluator at once (the
+// one-launch flavour of a 4100-set batch spent 4.7 cycles per issue waiting for instructions,
+// profiles/r2_v12_ncu_digest_nodes4096.txt): PHASE 1 runs the lean level, leaves kDeferred in the row where a trial
+// needs more, reduces the sets it completed and flags the others in `pending`; PHASE 2 looks only at flagged sets,
+// rebuilds each warp's queue from the marks (same trials, same order as PHASE 0) and finishes them.
+constexpr double kDeferred = -1.0;  // never a mixed density (those are >= 0 or NaN)
+template <int KMAX, int PHASE>
 __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_constant__ LikeArgs a, int cta_per_set,
-                                                               double* __restrict__ dens_all, int64_t dens_stride)
+                                                               double* __restrict__ dens_all, int64_t dens_stride,
+                                                               int* __restrict__ pending)
 {
     __shared__ GridSet<KMAX> gsw[kWarpSets];
     __shared__ double ebig[kExpBig];
     __shared__ unsigned short queue[kWarpSets][kWarpMaxTrials];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int k = threadIdx.x; k < kExpBig; k += 32 * kWarpSets) ebig[k] = g_exp2_big[k];
     const int64_t p = cta_per_set ? (int64_t)blockIdx.x : (int64_t)blockIdx.x * kWarpSets + warp;
-    const bool live = p < a.n_sets;
+    const bool live = p < a.n_sets && (PHASE != 2 || pending[p] != 0);
+    if (PHASE == 2 && !__syncthreads_or(live)) return;  // nothing left over in this CTA's sets
+    for (int k = threadIdx.x; k < kExpBig; k += 32 * kWarpSets) ebig[k] = g_exp2_big[k];
     GridSet<KMAX>& G = gsw[cta_per_set ? 0 : warp];
     if (live) {
         const uint4* src = reinterpret_cast<const uint4*>(a.set_tables) + p * (sizeof(GridSet<KMAX>) / sizeof(uint4));
@@ -469,7 +479,10 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
     const double v = load_par(a, 0, p, 0);
     const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
     if (!((p_out >= 0) & (p_out <= 1))) {  // src/wfpt.pyx:63-64 (CTA-uniform when cta_per_set)
-        if (lane == 0 && (!cta_per_set || warp == 0)) a.logp[p] = -INFINITY;
+        if (lane == 0 && (!cta_per_set || warp == 0)) {
+            a.logp[p] = -INFINITY;
+            if (PHASE == 1) pending[p] = 0;
+        }
         return;
     }
     double* __restrict__ dens = dens_all + p * dens_stride;
@@ -492,7 +505,9 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
         const bool valid = in_range && !(skip && skip[i] != 0);
         const double x = valid ? __ldg(xs + i) : 1.0;
         bool need = false;
-        if (lean_ok) {
+        if (PHASE == 2) {
+            need = in_range && dens[i] == kDeferred;
+        } else if (lean_ok) {
             int made = 0;
             const double d = lean_first_level<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
             evals += made;
@@ -503,12 +518,27 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
         }
         DBG(15, need);
         const unsigned int votes = __ballot_sync(0xffffffffu, need);
-        if (need) queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] = (unsigned short)i;
+        if (PHASE == 1) {
+            if (need) dens[i] = kDeferred;
+        } else if (need) {
+            queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] = (unsigned short)i;
+        }
         queued += __popc(votes);
     }
     __syncwarp();
-    int left = queued;
-    if (tree_ok) {  // the lean tree over the warp's queue; what it cannot settle is compacted in place
+    if (PHASE == 1) {  // anything left over in this set?  (CTA-wide when the CTA shares the set)
+        const bool some = cta_per_set ? __syncthreads_or(queued > 0) : queued > 0;
+        if (lane == 0 && (!cta_per_set || warp == 0)) pending[p] = some ? 1 : 0;
+        if (some) {
+            if (a.evals) {
+                evals = warp_sum_u64(evals);
+                if (lane == 0) atomicAdd(a.evals, evals);
+            }
+            return;
+        }
+    }
+    int left = PHASE == 1 ? 0 : queued;
+    if (PHASE != 1 && tree_ok) {  // the lean tree over the warp's queue; what it cannot settle is compacted in place
         left = 0;
 #pragma unroll 1
         for (int k0 = 0; k0 < queued; k0 += 32) {
@@ -531,6 +561,7 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
             __syncwarp();
         }
     }
+    if (PHASE != 1)
     for (int k = lane; k < left; k += 32) {  // the complete evaluator (refinement walks, out-of-range fallback)
         const unsigned short off = queue[warp][k];
         dens[off] = mixed(full_pdf_grid<KMAX, 0>(__ldg(xs + off), v, G, a.nm, &a.tab, evals));
@@ -706,14 +737,22 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
         void* tables = nullptr;
         const size_t table_bytes = ((size_t)b.n_sets * sizeof(GridSet<4>) + 255) & ~(size_t)255;
         const int64_t dens_stride = longest > 0 ? longest : 1;
-        if (cudaMallocAsync(&tables, table_bytes + (size_t)b.n_sets * dens_stride * sizeof(double), stream) == cudaSuccess) {
+        const size_t dens_bytes = (((size_t)b.n_sets * dens_stride * sizeof(double)) + 255) & ~(size_t)255;
+        if (cudaMallocAsync(&tables, table_bytes + dens_bytes + (size_t)b.n_sets * sizeof(int), stream) == cudaSuccess) {
             const unsigned blocks = (unsigned)((b.n_sets + kWarpSets - 1) / kWarpSets);
             k_build_tables_warp<4><<<blocks, 32 * kWarpSets, 0, stream>>>(b, tables);
             b.set_tables = tables;
             // few sets: a CTA per set (its four warps share the rounds); many: a warp per set.  Same sums either way.
             const int cta_per_set = b.n_sets <= 148 * 16 ? 1 : 0;
-            k_like_warp<4><<<cta_per_set ? (unsigned)b.n_sets : blocks, 32 * kWarpSets, 0, stream>>>(
-                b, cta_per_set, reinterpret_cast<double*>(reinterpret_cast<char*>(tables) + table_bytes), dens_stride);
+            const unsigned grid_w = cta_per_set ? (unsigned)b.n_sets : blocks;
+            double* dens = reinterpret_cast<double*>(reinterpret_cast<char*>(tables) + table_bytes);
+            int* pending = reinterpret_cast<int*>(reinterpret_cast<char*>(tables) + table_bytes + dens_bytes);
+            if (b.n_sets <= kWarpOneLaunchSets) {  // (the same sums, bit for bit, either way)
+                k_like_warp<4, 0><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+            } else {
+                k_like_warp<4, 1><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+                k_like_warp<4, 2><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+            }
             const cudaError_t e = cudaGetLastError();
             cudaFreeAsync(tables, stream);
             return e;
@@ -859,6 +898,66 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
         build_wtables<KT>(wt, par[3], par[4]);
     unsigned long long evals = 0;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // One decision time per point (st == 0: the density tables of gen_rts_from_cdf / gen_cdf_using_pdf): the lean
+    // single-node evaluator, whole warps in step; a point that needs more than the first level takes the complete one.
+    constexpr bool LEAN1 = GRID && KMAX == 4;
+    __shared__ double ebig[LEAN1 ? kExpBig : 1];
+    if (LEAN1) {
+        if (threadIdx.x == 0) build_leanset(gs, gs.lean, par[0], a.nm, true);
+        for (int k = threadIdx.x; k < kExpBig; k += kLikeThreads) ebig[k] = g_exp2_big[k];
+        __syncthreads();
+    }
+    if (LEAN1 && (gs.lean.ok1 & 1)) {
+        const LeanSet& L = gs.lean;
+        constexpr int NP = kPdfIlp;  // points per thread and round: independent nodes for the FP64 pipe to overlap
+        auto finish = [&](int64_t i, double x, double d, bool need, int made) {
+            if (need) d = full_pdf_grid<KT>(x, par[0], gs, a.nm, &a.tab, evals);
+            else evals += made;
+            d = d * (1 - par[7]) + (par[8] * par[7]);
+            ys[i] = a.logp == 1 ? log(d) : d;
+        };
+        for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x * NP; i0 < a.n; i0 += stride * NP) {
+            double x[NP], xt[NP];
+            bool all_large = true;
+            int K = 1;
+#pragma unroll
+            for (int u = 0; u < NP; ++u) {
+                const int64_t i = i0 + (int64_t)u * blockDim.x + threadIdx.x;
+                x[u] = i < a.n ? __ldg(xs + i) : NAN;
+                xt[u] = fabs(x[u]) - gs.t;
+                // large-time, inside the comfortable range of its boundary (signed compare: negative / NaN fail)
+                all_large &= (__double_as_longlong(xt[u]) >= L.x_small[x[u] > 0 ? 1 : 0]) & (xt[u] <= L.xhi);
+                K = max(K, 1 + (int)below(xt[u], L.x_k[0]) + (int)below(xt[u], L.x_k[1]) + (int)below(xt[u], L.x_k[2]));
+            }
+            if (__all_sync(0xffffffffu, all_large)) {  // the bulk of a density table: NP nodes in one basic block
+                const int wK = __reduce_max_sync(0xffffffffu, K);
+                double v[NP];
+                int neg[NP];
+                bool bad[NP];
+#pragma unroll
+                for (int u = 0; u < NP; ++u) {
+                    neg[u] = 0;
+                    bad[u] = false;
+                    v[u] = lean_node_large<KT>(gs, L, lean_begin(L, x[u] > 0 ? 1 : 0), ebig, xt[u],
+                                               exp_lean(gs.qk * xt[u], ebig), wK, neg[u], bad[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < NP; ++u)
+                    finish(i0 + (int64_t)u * blockDim.x + threadIdx.x, x[u], 12.0 * v[u], bad[u] | (neg[u] < 0), 5);
+                continue;
+            }
+#pragma unroll 1
+            for (int u = 0; u < NP; ++u) {  // small-time nodes, the edge, the onset, the tail of the table
+                const int64_t i = i0 + (int64_t)u * blockDim.x + threadIdx.x;
+                const bool valid = i < a.n;
+                const double xu = valid ? x[u] : 1.0;
+                bool need = false;
+                int made = 0;
+                const double d = lean_single<KT>(gs, L, ebig, lean_begin(L, xu > 0 ? 1 : 0), xu, valid, &need, &made);
+                if (valid) finish(i, xu, d, need, made);
+            }
+        }
+    } else
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
         double d;
         if (GRID)
@@ -888,9 +987,19 @@ cudaError_t launch_pdf_array(const PdfArgs& a, cudaStream_t stream)
     }
     if (b.n_sets <= 0) return cudaSuccess;
     if (b.n_sets > 65535) return cudaErrorInvalidValue;
+    {
+        const cudaError_t e = ensure_exp_table();
+        if (e != cudaSuccess) return e;
+    }
     // one CTA builds the per-set tables once, so with many sets give each CTA >= 2048 points
     int64_t blocks = (a.n + kLikeThreads - 1) / kLikeThreads;
-    if (b.n_sets > 1) blocks = (a.n + kTrialsPerBlock - 1) / kTrialsPerBlock;
+    if (b.n_sets > 1) {
+        // ... and with thousands of sets (the density tables of a posterior-predictive batch) no more CTAs per set
+        // than fill the GPU a few times over: the table build costs about as much as 2048 points
+        blocks = (a.n + kTrialsPerBlock - 1) / kTrialsPerBlock;
+        const int64_t enough = (148 * 16 + b.n_sets - 1) / b.n_sets;
+        if (blocks > enough) blocks = enough;
+    }
     if (blocks > 148 * 64) blocks = 148 * 64;
     b.tab = series_table_for(a.nm.err);
     const bool fast = g_kernel_choice != 1 && a.nm.use_adaptive != 0 && b.tab.n_thr >= 0 &&

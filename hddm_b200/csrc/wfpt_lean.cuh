@@ -139,10 +139,11 @@ __device__ __noinline__ void build_leanset(GS& G, LeanSet& L, double v, const Nu
     L.g4_one = 2.0 * G.a_sq;
     L.k1s = 1.0 / ((144.0 * G.a_sq) * sqrt(2.0 * kPi));
     L.uniform = drift_uniform ? 1 : 0;
-    L.ok = G.ok && G.support && mono && G.sz != 0 && G.st != 0 && nm.n_sz > 0 && nm.n_st > 0 &&
-           nm.simps_err >= 0.0 && asw * asw <= 50.0 && xhi > 0.0 && (!drift_uniform || isfinite(v)) && isfinite(L.k1) &&
-           L.k1 > 0.0 ? 1 : 0;
+    const bool inner_ok = G.ok && G.support && mono && G.sz != 0 && nm.n_sz > 0 && nm.simps_err >= 0.0 &&
+                          asw * asw <= 50.0 && xhi > 0.0 && (!drift_uniform || isfinite(v)) && isfinite(L.k1) && L.k1 > 0.0;
+    L.ok = inner_ok && G.st != 0 && nm.n_st > 0 ? 1 : 0;
     L.ok_small = L.ok && small_ok && isfinite(L.k1s) ? 1 : 0;
+    L.ok1 = inner_ok && G.st == 0 && drift_uniform ? (small_ok && isfinite(L.k1s) ? 3 : 1) : 0;
     L.tn17[0] = G.tn[0];
     L.tn17[16] = G.tn[4];
     for (int step = 8; step >= 1; step >>= 1)  // (lb + ub) / 2. recursively: tn17[4 j] == tn[j] bit for bit
@@ -490,6 +491,59 @@ __device__ __forceinline__ double lean_trial_mixed(const GridSet<KMAX>& G, const
     if (saw_tiny && !(fabs(out) > 1e-150) && !(fabs(out) <= 1e-150 && G.mix_floor > 1e-120)) bad = true;
     *need = bad | (neg < 0);
     return out;
+}
+
+// st == 0 (after the snap of src/pdf.pxi:122-123) and sz != 0: full_pdf is the integral over the start point at the
+// ONE decision time xt = |rt| - t (src/pdf.pxi:137-141) -- the density tables of gen_rts_from_cdf / gen_cdf_using_pdf
+// (src/wfpt.pyx:335,403) are made of such points.  The lean nodes carry k1 = pi / (144 a^2), i.e. the 1/12 of an
+// outer level that does not exist here: the value is 12 I''; the stop test is the inner one (thr_in) as it stands.
+// All 32 lanes call it (L.ok1 & 1 is set); a lane that needs more than the first level sets *need.
+// *n_evals: pdf_sv evaluations of the reference for what was settled here (5; 0 before the onset).
+template <int KMAX>
+__device__ __forceinline__ double lean_single(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
+                                              const LeanTrial& c, double x, bool valid, bool* need, int* n_evals)
+{
+    const int b = c.b;
+    const double ax = fabs(x);
+    const double xt = ax - G.t;
+    const long long bits = __double_as_longlong(xt);
+    const bool before = valid & ((ax - G.t_onset) < 0);      // src/pdf.pxi:111-113: 0, no pdf_sv
+    const bool at_onset = valid & !before & (xt <= 0.0);     // five pdf_sv calls that return 0 (src/pdf.pxi:92-93)
+    const bool live = valid & (xt > 0.0);
+    const bool in_range = live & (bits >= L.x_lo_small[b]) & (xt <= L.xhi);
+    const bool sm = in_range & (bits < (long long)L.x_edge) & ((L.ok1 & 2) != 0);
+    const bool lg = in_range & !(bits < (long long)L.x_edge);
+    bool bad = valid & !(before | at_onset | sm | lg);       // out of range, NaN, a negligible node: complete evaluator
+    int neg = 0;
+    double v = 0.0;
+    if (__any_sync(0xffffffffu, lg)) {
+        const int K = 1 + (int)below(xt, L.x_k[0]) + (int)below(xt, L.x_k[1]) + (int)below(xt, L.x_k[2]);
+        const int wK = __reduce_max_sync(0xffffffffu, lg ? K : 1);
+        bool b1 = false;
+        int n1 = 0;
+        const double xs = lg ? xt : L.xhi;  // (lanes of other classes: a harmless argument)
+        const double vl = lean_node_large<KMAX>(G, L, c, T, xs, exp_lean(G.qk * xs, T), wK, n1, b1);
+        if (lg) {
+            v = vl;
+            bad |= b1;
+            neg |= n1;
+        }
+    }
+    if (__any_sync(0xffffffffu, sm)) {
+        const bool any_four = __any_sync(0xffffffffu, sm & !below(xt, L.x_s4));
+        bool b2 = false;
+        int n2 = 0;
+        const double xs = sm ? xt : __longlong_as_double(L.x_lo_small[b]);
+        const double vs = lean_node_small<KMAX>(G, L, c, T, xs, any_four, n2, b2);
+        if (sm) {
+            v = vs;
+            bad |= b2;
+            neg |= n2;
+        }
+    }
+    *need = bad | (neg < 0);
+    *n_evals = (valid & !*need & !before) ? 5 : 0;
+    return 12.0 * v;
 }
 
 // The lean first level for one warp round (all 32 lanes call it; `valid` masks lanes without a trial).  Lean or

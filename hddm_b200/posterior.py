@@ -171,7 +171,8 @@ def gen_rts_from_simulated_drift(params, samples=1000, dt=1e-4, intra_sv=1., see
     return simulate_drift_batch(col, 1 if samples is None else samples, dt, intra_sv, seed, switch=switch)[0]
 
 
-def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=0, evaluate=None, group=None):
+def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=0, evaluate=None, group=None,
+                            timings=None):
     """Posterior predictive statistics for D draws with the draws sharded over the ranks of `group` (one
     process per GPU, contiguous blocks as hddm_b200.batch.shard_bounds); every rank returns the full
     float64 [D, 15] table.  The only collective is one all_gather of the per-draw statistics (120 bytes per
@@ -179,7 +180,10 @@ def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=
     index, so the table does not depend on the world size.
 
     `evaluate(params_block, first_draw) -> float64 [block, 15]` defaults to the CUDA path; tests pass a
-    stand-in to exercise the partition / gather logic over gloo on CPU."""
+    stand-in to exercise the partition / gather logic over gloo on CPU.  `timings` (a dict, optional) receives
+    this rank's wall-clock seconds per stage: "evaluate" (host staging + kernels + statistics back on the host),
+    "gather" (to the device, all_gather, full table back to the host)."""
+    import time
     import torch
     import torch.distributed as dist
     from .batch import gather_rows, shard_bounds
@@ -194,8 +198,14 @@ def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=
     if evaluate is None:
         evaluate = lambda b, first: gen_rts_from_cdf_batch(b, samples, cdf_lb, cdf_ub, dt, seed=seed, return_rts=False,
                                                            return_stats=True, first_draw=first)
+    t0 = time.perf_counter()
     local = evaluate(block, lo) if hi > lo else np.empty((0, len(STAT_NAMES)))
+    t1 = time.perf_counter()
     local = torch.from_numpy(np.ascontiguousarray(local, dtype=np.float64))
     if world > 1 and dist.get_backend(group) == "nccl":
         local = local.cuda()
-    return gather_rows(local, D, group).cpu().numpy()
+    table = gather_rows(local, D, group).cpu().numpy()
+    if timings is not None:
+        timings["evaluate"] = t1 - t0
+        timings["gather"] = time.perf_counter() - t1
+    return table
