@@ -52,6 +52,10 @@ constexpr int kTrialsPerBigBlock = HDDM_BIG_BLOCK;  // ... or this many when the
 #endif
 constexpr int kBlocksPerDeferredCta = HDDM_DEFER_SPAN;  // second launch of a split sweep: blocks of trials per CTA (one table build)
 constexpr int kUnrollJ = HDDM_UNROLL_J;  // first pass: the five decision-time nodes of a trial are unrolled (5) or looped (1)
+#ifndef HDDM_PAIR_LOADS
+#define HDDM_PAIR_LOADS 0
+#endif
+constexpr bool kPairLoads = HDDM_PAIR_LOADS != 0;  // first pass: adjacent trials per thread, one 16-byte RT load per two rounds
 #ifndef HDDM_PDF_ILP
 #define HDDM_PDF_ILP 2
 #endif

@@ -91,6 +91,16 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         }
         return;
     }
+    // Layout of a block's trials over (round, thread) in the two-pass flavours: thread t owns the ADJACENT trials
+    // 2t and 2t + 1 of every 2 * kLikeThreads tile -- rounds 2k and 2k + 1 -- so that one 16-byte load brings both
+    // RTs (coalesced: a warp reads 512 contiguous bytes).  The defer bitmap is indexed by (round, warp, lane).
+    // (kPairLoads: measured 6 % slower on the headline sweep -- the pair carried across two rounds costs registers
+    //  the first level does not have -- so the default stays one 8-byte load per trial and round, 256 contiguous
+    //  bytes per warp; HDDM_PAIR_LOADS=1 builds the paired flavour.)
+    auto trial_of = [](int r, int t) { return kPairLoads ? (r >> 1) * (2 * kLikeThreads) + 2 * t + (r & 1) : r * kLikeThreads + t; };
+    auto rounds_for = [](int64_t cnt) {
+        return kPairLoads ? 2 * (int)((cnt + 2 * kLikeThreads - 1) / (2 * kLikeThreads)) : (int)((cnt + kLikeThreads - 1) / kLikeThreads);
+    };
     const int64_t span = (int64_t)kSpan * a.trials_per_block;
     const int64_t end = begin + span < hi ? begin + span : hi;
     const int words_per_block = a.trials_per_block / 32;
@@ -101,7 +111,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
             const int64_t b0 = begin + (int64_t)c * a.trials_per_block;
             const int64_t left = end - b0;
             const int64_t cnt = left < a.trials_per_block ? left : a.trials_per_block;
-            const int words = cnt > 0 ? (int)((cnt + kLikeThreads - 1) / kLikeThreads) * (kLikeThreads / 32) : 0;
+            const int words = cnt > 0 ? rounds_for(cnt) * (kLikeThreads / 32) : 0;
             const unsigned int* w = a.defer_bits + (p * a.chunks + (int64_t)chunk * kSpan + c) * words_per_block;
             for (int k = threadIdx.x; k < words; k += kLikeThreads) any |= w[k];
         }
@@ -198,6 +208,8 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
                   "table build needs 256 threads; mantissa product must stay finite (two passes)");
     unsigned long long evals = 0;
     bool hit_zero = false;
+    // src/wfpt.pyx:70, spelled out so that every instantiation of this kernel rounds it the same way
+    const double keep_mass = 1 - p_out, floor_mass = __dmul_rn(w_out, p_out);
     // One trial: load, evaluate, mix, accumulate.  Returns true when the trial was deferred.
     auto score = [&](int64_t i, int stage) {
         const double x = __ldg(a.x + i);
@@ -212,7 +224,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         if (multi) {
             if (a.mode == kModeMultiRL || fabs(x) != 999.) {  // src/wfpt.pyx:261-266
                 d = density(x, evals, stage, &need);
-                d = d * (1 - p_out) + w_out * p_out;
+                d = fma(d, keep_mass, floor_mass);
             } else if (x == 999.) {  // :267-268
                 d = prob_ub(par[0], GRID ? gs.raw[2] : par[2], GRID ? gs.raw[3] : par[3]);
             } else {  // :269-270
@@ -223,7 +235,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
             if (a.cont && a.cont[i] != 0) return false;  // src/wfpt.pyx:374; :134 (first trial of a condition)
             d = density(x, evals, stage, &need);
             if (!need) {
-                d = d * (1 - p_out) + w_out * p_out;  // src/wfpt.pyx:70 (contaminant: p_out = 0)
+                d = fma(d, keep_mass, floor_mass);  // src/wfpt.pyx:70 (contaminant: p_out = 0)
                 hit_zero |= (d == 0);                 // :71-72, :377-379
                 add_log(d);
             }
@@ -231,10 +243,10 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         return need;
     };
     // Lean first level for one warp round (lean_ok sets): *need is set per lane; always returns true.
-    auto lean_round = [&](int64_t i, bool in_range, bool* need) {
+    auto lean_round = [&](int64_t i, bool in_range, bool* need, double x_loaded) {
         const LeanSet& L = gs.lean;
         const bool valid = in_range && !(a.cont && a.cont[i] != 0);
-        const double x = valid ? __ldg(a.x + i) : 1.0;
+        const double x = valid ? x_loaded : 1.0;
         const int b = x > 0 ? 1 : 0;
         bool v_fits = true;
         const LeanTrial c = reg_v_only ? lean_begin_v<KT>(gs, L, b, reg_value(0, valid ? i : begin), fabs(x) - gs.tn[0], &v_fits)
@@ -245,7 +257,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         nd |= valid & !v_fits;
         if (valid & !nd) {
             evals += made;
-            d = d * (1 - p_out) + w_out * p_out;
+            d = fma(d, keep_mass, floor_mass);
             hit_zero |= (d == 0);
             add_log(d);
         }
@@ -286,7 +298,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
                     fail = (fail | !v_fits) & on;
                     if (on & !fail) {
                         evals += made;
-                        d = d * (1 - p_out) + w_out * p_out;
+                        d = fma(d, keep_mass, floor_mass);
                         hit_zero |= (d == 0);
                         add_log(d);
                     }
@@ -319,7 +331,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
                 const int64_t b0 = begin + (int64_t)c * a.trials_per_block;
                 if (b0 >= end) break;
                 const int64_t cnt = end - b0 < a.trials_per_block ? end - b0 : a.trials_per_block;
-                const int rounds = (int)((cnt + kLikeThreads - 1) / kLikeThreads);
+                const int rounds = rounds_for(cnt);
                 const unsigned int* w = a.defer_bits + (p * a.chunks + (int64_t)chunk * kSpan + c) * words_per_block;
                 // lane r fetches the warp's word of round r: one load per block instead of one per round
                 static_assert(kMaxRounds <= 32, "a warp's words of one block fit one per lane");
@@ -329,21 +341,33 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
                     if (votes == 0) continue;  // warp-uniform
                     if ((votes >> lane) & 1u)
                         queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] =
-                            (unsigned short)(c * a.trials_per_block + r * kLikeThreads + threadIdx.x);
+                            (unsigned short)(c * a.trials_per_block + trial_of(r, threadIdx.x));
                     queued += __popc(votes);
                     if (queued > kMaxRounds * 32 - 32) drain();
                 }
             }
             drain();
         } else {
-            const int rounds = (int)((end - begin + kLikeThreads - 1) / kLikeThreads);
+            const int rounds = rounds_for(end - begin);
             unsigned int* const bits = PASSES == kSplitFirst
                                            ? a.defer_bits + (p * a.chunks + chunk) * words_per_block : nullptr;
             unsigned int* const my_bits = bits ? bits + warp : nullptr;
+            const bool vec = (reinterpret_cast<uintptr_t>(a.x + begin) & 15) == 0;  // CTA-uniform
+            double2 xx = make_double2(1.0, 1.0);
             for (int r = 0; r < rounds; ++r) {
-                const int off = r * kLikeThreads + threadIdx.x;
+                const int off = trial_of(r, threadIdx.x);
+                if (!kPairLoads) {
+                    if (LEAN && lean_ok) xx.x = begin + off < end ? __ldg(a.x + begin + off) : 1.0;
+                } else if (LEAN && lean_ok && !(r & 1)) {  // even round: the thread's pair of RTs
+                    if (vec && begin + off + 1 < end) {
+                        xx = __ldg(reinterpret_cast<const double2*>(a.x + begin + off));
+                    } else {
+                        xx.x = begin + off < end ? __ldg(a.x + begin + off) : 1.0;
+                        xx.y = begin + off + 1 < end ? __ldg(a.x + begin + off + 1) : 1.0;
+                    }
+                }
                 bool need = false;
-                if (!(LEAN && lean_ok && lean_round(begin + off, begin + off < end, &need)))
+                if (!(LEAN && lean_ok && lean_round(begin + off, begin + off < end, &need, (kPairLoads && (r & 1)) ? xx.y : xx.x)))
                     need = (begin + off < end) ? score(begin + off, 0) : false;
                 const unsigned int votes = __ballot_sync(0xffffffffu, need);
                 if (PASSES == kSplitFirst) {
@@ -488,7 +512,10 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
     double* __restrict__ dens = dens_all + p * dens_stride;
     const double* __restrict__ xs = a.x + lo;
     const int32_t* __restrict__ skip = a.cont ? a.cont + lo : nullptr;
-    auto mixed = [&](double d) { return d * (1 - p_out) + w_out * p_out; };  // src/wfpt.pyx:70 (contaminant: p_out = 0)
+    // src/wfpt.pyx:70 (contaminant: p_out = 0).  Spelled out: which of the two products the compiler fuses into the
+    // addition must not depend on the instantiation (the one- and two-launch flavours give a set the same bits)
+    const double keep = 1 - p_out, floor_wp = __dmul_rn(w_out, p_out);
+    auto mixed = [&](double d) { return fma(d, keep, floor_wp); };
     const bool lean_ok = KMAX == 4 && L.ok != 0 && L.uniform != 0;
     const bool tree_ok = lean_ok && a.nm.n_st == 2;
     unsigned long long evals = 0;
@@ -909,21 +936,31 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
     }
     if (LEAN1 && (gs.lean.ok1 & 1)) {
         const LeanSet& L = gs.lean;
-        constexpr int NP = kPdfIlp;  // points per thread and round: independent nodes for the FP64 pipe to overlap
-        auto finish = [&](int64_t i, double x, double d, bool need, int made) {
+        constexpr int NP = kPdfIlp;  // ADJACENT points per thread and round: independent nodes for the FP64 pipe to
+                                     // overlap, and (NP == 2) one 16-byte load of the RTs and one 16-byte store
+        auto finish = [&](double x, double d, bool need, int made) {
             if (need) d = full_pdf_grid<KT>(x, par[0], gs, a.nm, &a.tab, evals);
             else evals += made;
             d = d * (1 - par[7]) + (par[8] * par[7]);
-            ys[i] = a.logp == 1 ? log(d) : d;
+            return a.logp == 1 ? log(d) : d;
         };
+        const bool vec = NP == 2 && ((reinterpret_cast<uintptr_t>(xs) | reinterpret_cast<uintptr_t>(ys)) & 15) == 0;
         for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x * NP; i0 < a.n; i0 += stride * NP) {
-            double x[NP], xt[NP];
+            const int64_t ib = i0 + (int64_t)threadIdx.x * NP;
+            const bool pair = vec && ib + 1 < a.n;
+            double x[NP], xt[NP], y[NP];
+            if (pair) {
+                const double2 t = __ldg(reinterpret_cast<const double2*>(xs + ib));
+                x[0] = t.x;
+                x[NP - 1] = t.y;
+            } else {
+#pragma unroll
+                for (int u = 0; u < NP; ++u) x[u] = ib + u < a.n ? __ldg(xs + ib + u) : NAN;
+            }
             bool all_large = true;
             int K = 1;
 #pragma unroll
             for (int u = 0; u < NP; ++u) {
-                const int64_t i = i0 + (int64_t)u * blockDim.x + threadIdx.x;
-                x[u] = i < a.n ? __ldg(xs + i) : NAN;
                 xt[u] = fabs(x[u]) - gs.t;
                 // large-time, inside the comfortable range of its boundary (signed compare: negative / NaN fail)
                 all_large &= (__double_as_longlong(xt[u]) >= L.x_small[x[u] > 0 ? 1 : 0]) & (xt[u] <= L.xhi);
@@ -942,19 +979,24 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
                                                exp_lean(gs.qk * xt[u], ebig), wK, neg[u], bad[u]);
                 }
 #pragma unroll
-                for (int u = 0; u < NP; ++u)
-                    finish(i0 + (int64_t)u * blockDim.x + threadIdx.x, x[u], 12.0 * v[u], bad[u] | (neg[u] < 0), 5);
-                continue;
-            }
+                for (int u = 0; u < NP; ++u) y[u] = finish(x[u], 12.0 * v[u], bad[u] | (neg[u] < 0), 5);
+            } else {
 #pragma unroll 1
-            for (int u = 0; u < NP; ++u) {  // small-time nodes, the edge, the onset, the tail of the table
-                const int64_t i = i0 + (int64_t)u * blockDim.x + threadIdx.x;
-                const bool valid = i < a.n;
-                const double xu = valid ? x[u] : 1.0;
-                bool need = false;
-                int made = 0;
-                const double d = lean_single<KT>(gs, L, ebig, lean_begin(L, xu > 0 ? 1 : 0), xu, valid, &need, &made);
-                if (valid) finish(i, xu, d, need, made);
+                for (int u = 0; u < NP; ++u) {  // small-time nodes, the edge, the onset, the tail of the table
+                    const bool valid = ib + u < a.n;
+                    const double xu = valid ? x[u] : 1.0;
+                    bool need = false;
+                    int made = 0;
+                    const double d = lean_single<KT>(gs, L, ebig, lean_begin(L, xu > 0 ? 1 : 0), xu, valid, &need, &made);
+                    y[u] = valid ? finish(xu, d, need, made) : 0.0;
+                }
+            }
+            if (pair) {
+                *reinterpret_cast<double2*>(ys + ib) = make_double2(y[0], y[NP - 1]);
+            } else {
+#pragma unroll
+                for (int u = 0; u < NP; ++u)
+                    if (ib + u < a.n) ys[ib + u] = y[u];
             }
         }
     } else

@@ -57,9 +57,10 @@ __device__ __forceinline__ double exp_lean(double x, const double* __restrict__ 
     const double p = fma(r * r, c, r);
     const double tv = T[n & (kExpBig - 1)];
     const double m = fma(tv, p, tv);
-    const int e = n >> kExpBigBits;
-    int hi = __double2hiint(m) + (e << 20), lo = __double2loint(m);
-    if (CLAMP && e < -1021) hi = lo = 0;
+    // 2^(n >> 11) goes into the exponent field: (n >> 11) << 20 == (n with its 11 index bits cleared) * 2^9, one
+    // mask and one multiply-add
+    int hi = (n & -kExpBig) * (1 << (20 - kExpBigBits)) + __double2hiint(m), lo = __double2loint(m);
+    if (CLAMP && n < -1021 * kExpBig) hi = lo = 0;
     return __hiloint2double(hi, lo);
 }
 
@@ -156,6 +157,14 @@ __device__ __forceinline__ bool below(double xt, unsigned long long edge)
     return (unsigned long long)__double_as_longlong(xt) < edge;
 }
 
+// The same for a decision time known to be positive (or a lane whose result is discarded), as one FP64 compare
+// instead of two integer ones: positive doubles order like their bit patterns, +inf as an edge takes every finite xt,
+// NaN fails both.
+__device__ __forceinline__ bool below_pos(double xt, unsigned long long edge)
+{
+    return xt < __longlong_as_double((long long)edge);
+}
+
 // Per-trial constants of the lean evaluators (boundary-dependent table entries, read once per trial).
 struct LeanTrial {
     int b;
@@ -216,22 +225,25 @@ __device__ __forceinline__ double lean_node_large(const GridSet<KMAX>& G, const 
                                                   bool& bad)
 {
     // series / q: sin(pi w_i) + sum_{k>=2} q^(k^2-1) k sin(k pi w_i), ascending k (src/pdf.pxi:60-62)
+    // (the k = 2 term is evaluated whatever wK says: nine nodes in ten of the headline sweep have it, a node without
+    //  it gets a zero coefficient, and the first sines, which the five nodes of a trial share, need no copy)
     double p[5], s[5];
-    load5(L.ks[c.b][0], p);
-    if (wK >= 2) {
+    {
+        double s1[5];
+        load5(L.ks[c.b][0], s1);
         const double q2 = q * q, q3 = q2 * q;
-        const double e2 = below(xt, L.x_k[0]) ? q3 : 0.0;
+        const double e2 = below_pos(xt, L.x_k[0]) ? q3 : 0.0;
         load5(L.ks[c.b][1], s);
 #pragma unroll
-        for (int i = 0; i < 5; ++i) p[i] = fma(e2, s[i], p[i]);
+        for (int i = 0; i < 5; ++i) p[i] = fma(e2, s[i], s1[i]);
         if (wK >= 3) {
             const double q4 = q2 * q2, q8 = q4 * q4;
-            const double e3 = below(xt, L.x_k[1]) ? q8 : 0.0;
+            const double e3 = below_pos(xt, L.x_k[1]) ? q8 : 0.0;
             load5(L.ks[c.b][2], s);
 #pragma unroll
             for (int i = 0; i < 5; ++i) p[i] = fma(e3, s[i], p[i]);
             if (wK >= 4) {
-                const double e4 = below(xt, L.x_k[2]) ? (q8 * q4) * q3 : 0.0;
+                const double e4 = below_pos(xt, L.x_k[2]) ? (q8 * q4) * q3 : 0.0;
                 load5(L.ks[c.b][3], s);
 #pragma unroll
                 for (int i = 0; i < 5; ++i) p[i] = fma(e4, s[i], p[i]);

@@ -535,6 +535,46 @@ def test_nodes_batch_vs_oracle(W, O):
         W.wiener_like_nodes(x, node_off, np.full(P, 7), params, **HDDM)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("P", [1500, 5000])
+def test_many_short_sets_two_launches_equal_one(W, O, P):
+    """More than 1024 short segments run the lean level and the leftovers as two launches (a CTA per set up to
+    2368 sets, a warp per set above): every set must get the sum, bit for bit, that the one-launch flavour gives
+    it in a small batch, the same pdf_sv count, and the oracle's value."""
+    rng = np.random.default_rng(9500 + P)
+    lens = [0, 37, 200, 64, 311, 1000, 1]
+    xs = [draw_rts(rng, n, 0.40) for n in lens]
+    x = np.concatenate(xs)
+    node_off = np.concatenate([[0], np.cumsum(lens)])
+    set_node = rng.integers(0, len(lens), P)
+    par = draw_params(rng, P)
+    params = np.concatenate([par, np.full((1, P), 0.05), np.full((1, P), 0.1)])
+    params[7, ::7] = 0.0      # no outlier mass: -inf where a trial lies before the onset
+    params[4, ::11] = 0.0     # sz = 0 / st = 0 sets: not lean, everything left to the second launch
+    params[6, ::13] = 0.0
+    h = W.Trials(x)
+    got, evals = h.wiener_like_nodes(node_off, set_node, params, return_evals=True, **HDDM)
+    small, small_evals = [], 0
+    for lo in range(0, P, 500):
+        g, e = h.wiener_like_nodes(node_off, set_node[lo:lo + 500], np.ascontiguousarray(params[:, lo:lo + 500]),
+                                   return_evals=True, **HDDM)
+        small.append(g)
+        small_evals += e
+    h.close()
+    small = np.concatenate(small)
+    assert np.array_equal(np.isnan(got), np.isnan(small))
+    assert np.array_equal(got[~np.isnan(got)], small[~np.isnan(small)])
+    assert evals == small_evals
+    # the oracle on 40 random sets and on up to 8 that must come out -inf (no outlier mass, onset past the first RTs)
+    sure = np.where((params[7] == 0) & (params[5] - params[6] / 2 > 0.45) & (np.array(lens)[set_node] > 30))[0][:8]
+    assert sure.size > 0
+    pick = np.union1d(rng.choice(P, 40, replace=False), sure)
+    want = np.array([O.wiener_like(xs[set_node[p]], *params[:7, p], p_outlier=params[7, p], w_outlier=params[8, p], **HDDM)
+                     for p in pick])
+    assert np.isneginf(want).any()
+    assert_parity(got[pick], want, RTOL_SUM, what="many short sets")
+
+
 def test_likelihood_glue_vs_oracle(W, O, gpu):
     """hddm_b200/likelihoods.py: wfpt_like (incl. the +-999 missing-response branch), pdf / cdf members and
     the chi-square / quantile methods of the stochastic class against the oracle through the same formulas."""
