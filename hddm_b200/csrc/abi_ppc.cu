@@ -1,6 +1,7 @@
 // abi_ppc.cu -- extern "C" entry points of the posterior-predictive batch (BASELINE
 // config 5): simulated data sets and their summary statistics for many posterior draws, and the cdfdif
 // quantile probabilities of many parameter sets, one launch sequence per slab of draws.
+#include <cstring>
 #include <vector>
 
 #include "abi_runtime.cuh"
@@ -94,7 +95,19 @@ int ppc_impl(const double* xgrid, int64_t m, const double* params, int64_t D, co
     const size_t per_draw = (size_t)m * 8 + (size_t)S * 8 * 3 + (kNumPar + 3 + kPpcStats) * 8;
     TRY(ensure_arena(align_up((size_t)m * sizeof(double)) + (size_t)slab * per_draw + (16 << 10)));
     cudaStream_t s = g_rt.stream;
-    CUDA_TRY(cudaMemcpyAsync(g_rt.arena, xgrid, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, s));
+    // A posterior-predictive loop passes the same grid call after call (np.arange(lb, ub, dt): 960 KB at dt = 1e-4):
+    // it stays at the front of the arena as long as nobody else carved the arena in between and the bytes are equal.
+    static std::vector<double> grid_seen;
+    static unsigned long long grid_epoch = 0;
+    static const char* grid_arena = nullptr;
+    const bool resident = grid_arena == g_rt.arena && grid_epoch + 1 == g_rt.arena_epoch && (int64_t)grid_seen.size() == m &&
+                          memcmp(grid_seen.data(), xgrid, (size_t)m * sizeof(double)) == 0;
+    if (!resident) {
+        CUDA_TRY(cudaMemcpyAsync(g_rt.arena, xgrid, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, s));
+        grid_seen.assign(xgrid, xgrid + m);
+        grid_arena = g_rt.arena;
+    }
+    grid_epoch = g_rt.arena_epoch;
     for (int64_t d0 = 0; d0 < D; d0 += slab) {
         const int64_t Dn = D - d0 < slab ? D - d0 : slab;
         TRY(ppc_slab(reinterpret_cast<const double*>(g_rt.arena), m, params, D, d0, Dn, f, u, seed, first_draw, S, rts,

@@ -44,6 +44,7 @@ struct Runtime {
     cudaStream_t stream = nullptr;
     char* arena = nullptr;  // grow-only device scratch, carved per call
     size_t arena_bytes = 0;
+    unsigned long long arena_epoch = 0;  // counts ensure_arena calls: whoever keeps data there across calls checks it
     char* pinned = nullptr;  // grow-only page-locked staging for the small per-call inputs / outputs
     size_t pinned_bytes = 0;
 };
@@ -77,6 +78,7 @@ inline int ensure_ready()
 
 inline int ensure_arena(size_t bytes)
 {
+    ++g_rt.arena_epoch;
     if (bytes <= g_rt.arena_bytes) return HDDM_OK;
     if (g_rt.arena) {
         CUDA_TRY(cudaStreamSynchronize(g_rt.stream));

@@ -12,6 +12,8 @@ Draws are independent, so under torch.distributed they are sharded in contiguous
 """
 import ctypes as C
 
+import functools
+
 import numpy as np
 
 from . import _lib
@@ -29,6 +31,14 @@ def _params7(params):
     return params
 
 
+@functools.lru_cache(maxsize=8)
+def _rt_grid(cdf_lb, cdf_ub, dt):
+    """np.arange(cdf_lb, cdf_ub, dt) of src/wfpt.pyx:331, kept between calls (read-only)."""
+    x = np.arange(cdf_lb, cdf_ub, dt)
+    x.setflags(write=False)
+    return x
+
+
 def gen_rts_from_cdf_batch(params, samples=1000, cdf_lb=-6, cdf_ub=6, dt=1e-2, f=None, u_delay=None, seed=None,
                            return_rts=True, return_stats=False, first_draw=0):
     """gen_rts_from_cdf (src/wfpt.pyx:323-354) for D posterior draws in one pass.
@@ -40,7 +50,7 @@ def gen_rts_from_cdf_batch(params, samples=1000, cdf_lb=-6, cdf_ub=6, dt=1e-2, f
     calls would.  Returns rts [D, samples] and/or stats [D, 15] (columns STAT_NAMES)."""
     params = _params7(params)
     D = params.shape[1]
-    x = np.arange(cdf_lb, cdf_ub, dt)
+    x = _rt_grid(float(cdf_lb), float(cdf_ub), float(dt))
     rts = np.empty((D, samples), dtype=np.double) if return_rts else None
     stats = np.empty((D, len(STAT_NAMES)), dtype=np.double) if return_stats else None
     rp = dptr(rts) if rts is not None else None
