@@ -219,3 +219,31 @@ def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=
         timings["evaluate"] = t1 - t0
         timings["gather"] = time.perf_counter() - t1
     return table
+
+
+def dmat_cdf_sharded(x, params, evaluate=None, group=None):
+    """dmat_cdf_batch (cdfdif quantile probabilities of D parameter sets, src/cdfdif_wrapper.pyx:16-52) with the sets
+    sharded over the ranks of `group` like post_pred_stats_sharded: every rank evaluates its contiguous block of
+    rows of x [D, n] / columns of params [9, D] and returns the full [D, n] table after one all_gather (8 n bytes
+    per set).  Rows the reference would refuse are NaN.  `evaluate(x_block, params_block) -> [block, n]` defaults
+    to the CUDA path; tests pass a stand-in to exercise the partition / gather logic over gloo on CPU."""
+    import torch
+    import torch.distributed as dist
+    from .batch import gather_rows, shard_bounds
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    if x.ndim != 2 or params.ndim != 2 or params.shape != (9, x.shape[0]):
+        raise ValueError("x must be [D, n] and params [9, D]")
+    D, n = x.shape
+    if dist.is_available() and dist.is_initialized():
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+    else:
+        world, rank = 1, 0
+    lo, hi = shard_bounds(D, world, rank)
+    if evaluate is None:
+        evaluate = dmat_cdf_batch
+    local = evaluate(x[lo:hi], np.ascontiguousarray(params[:, lo:hi])) if hi > lo else np.empty((0, n))
+    local = torch.from_numpy(np.ascontiguousarray(local, dtype=np.float64).reshape(hi - lo, n))
+    if world > 1 and dist.get_backend(group) == "nccl":
+        local = local.cuda()
+    return gather_rows(local, D, group).cpu().numpy()

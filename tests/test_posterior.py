@@ -279,6 +279,68 @@ def test_sharded_post_pred_stats_over_gloo_world2(D):
         assert np.array_equal(got[r][~np.isnan(want)], want[~np.isnan(want)])
 
 
+def _cdf_standin(x_block, params_block):
+    """Stand-in for the CUDA launch (tests only): a cheap function of each row's own inputs."""
+    return np.tanh(x_block * params_block[0][:, None]) + params_block[2][:, None]
+
+
+def _cdf_gloo_worker(rank, world, port, D, q):
+    import os
+    import sys
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from hddm_b200 import posterior
+    x, params = _cdf_inputs(D)
+    q.put((rank, posterior.dmat_cdf_sharded(x, params, evaluate=_cdf_standin).copy()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _cdf_inputs(D):
+    rng = np.random.default_rng(78)
+    par = np.concatenate([draw_params(rng, D), np.full((1, D), 0.05), np.full((1, D), 0.1)])
+    return rng.uniform(-3, 3, (D, 11)), np.ascontiguousarray(par)
+
+
+@pytest.mark.parametrize("D", [7, 1, 8])
+def test_sharded_cdf_quantiles_over_gloo_world2(D):
+    """N>1 host path of the cdfdif quantile batch: parameter sets split over 2 ranks (uneven, a rank with nothing,
+    even), one all_gather of the [D, n] probabilities, every rank sees the single-process table bit for bit."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_cdf_gloo_worker, args=(r, 2, port, D, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = _cdf_standin(*_cdf_inputs(D))
+    for r in range(2):
+        assert got[r].shape == (D, 11)
+        assert np.array_equal(got[r], want)
+
+
+@pytest.mark.gpu
+def test_sharded_cdf_single_process_equals_batch(gpu):
+    from hddm_b200 import posterior
+    x, params = _cdf_inputs(40)
+    params[4] = np.maximum(params[4], 0.02)
+    params[6] = np.maximum(params[6], 0.02)
+    x = np.clip(x, -4.9, 4.9)
+    a, b = posterior.dmat_cdf_sharded(x, params), posterior.dmat_cdf_batch(x, params)
+    assert np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(a[~np.isnan(a)], b[~np.isnan(b)])
+
+
 @pytest.mark.gpu
 def test_batch_edge_cases(gpu):
     """Empty and maximum sizes of the batched entry points (the reference's own edge behaviour: an empty
