@@ -433,6 +433,10 @@ __global__ void __launch_bounds__(kLikeThreads) k_build_tables(const __grid_cons
 // likelihood for a 200-trial node: profiles/r2_v9_bench_paths.jsonl).  Same arithmetic as k_build_tables.
 constexpr int kWarpSets = 4;        // sets per CTA of the warp-per-set kernels
 constexpr int kWarpOneLaunchSets = 1024;  // k_like_warp: up to this many sets run all phases in one launch (latency path)
+#ifndef HDDM_WARP_CTA_TRIALS
+#define HDDM_WARP_CTA_TRIALS 512
+#endif
+constexpr int kWarpCtaTrials = HDDM_WARP_CTA_TRIALS;  // k_like_warp: segments this long get a CTA per set whatever the number of sets
 constexpr int kWarpMaxTrials = 1024;  // longest segment k_like_warp takes (its deferred-trial queue is 16-bit x 1024)
 template <int KMAX>
 __global__ void __launch_bounds__(32 * kWarpSets) k_build_tables_warp(const __grid_constant__ LikeArgs a, void* out)
@@ -770,7 +774,9 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
             k_build_tables_warp<4><<<blocks, 32 * kWarpSets, 0, stream>>>(b, tables);
             b.set_tables = tables;
             // few sets: a CTA per set (its four warps share the rounds); many: a warp per set.  Same sums either way.
-            const int cta_per_set = b.n_sets <= 148 * 16 ? 1 : 0;
+            // (long segments too: a CTA's four warps then share >= 16 rounds, and the GPU sees four times as many,
+            //  four times shorter units -- 1e4 sets of 1000 trials are 4.2 waves of warp-per-set CTAs)
+            const int cta_per_set = (b.n_sets <= 148 * 16 || longest >= kWarpCtaTrials) ? 1 : 0;
             const unsigned grid_w = cta_per_set ? (unsigned)b.n_sets : blocks;
             double* dens = reinterpret_cast<double*>(reinterpret_cast<char*>(tables) + table_bytes);
             int* pending = reinterpret_cast<int*>(reinterpret_cast<char*>(tables) + table_bytes + dens_bytes);
