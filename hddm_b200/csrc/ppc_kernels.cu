@@ -17,7 +17,10 @@ namespace hddm {
 namespace {
 
 constexpr int kScanThreads = 1024;
-constexpr int kScanCols = 8;                    // slice elements staged per round (two CTAs per SM)
+#ifndef HDDM_SCAN_COLS
+#define HDDM_SCAN_COLS 8
+#endif
+constexpr int kScanCols = HDDM_SCAN_COLS;       // slice elements staged per round (8: two CTAs per SM)
 constexpr int kScanPitch = kScanCols + 1;       // odd pitch: the row-wise pass is free of bank conflicts
 constexpr size_t kScanTileBytes = (size_t)kScanThreads * kScanPitch * sizeof(double);
 
@@ -40,13 +43,22 @@ __global__ void __launch_bounds__(kScanThreads) k_cumsum_batch(double* tables, i
     const int64_t lo = 1 + (int64_t)j * per;
     const int64_t hi = lo + per < m ? lo + per : m;
     const int mine = hi > lo ? (int)(hi - lo) : 0;  // elements of this thread's slice
-    auto stage = [&](int64_t c0, bool store) {      // tile <-> slices' elements [c0, c0 + kScanCols)
-        for (int idx = j; idx < kScanThreads * kScanCols; idx += kScanThreads) {
-            const int row = idx / kScanCols, col = idx % kScanCols;
-            const int64_t i = 1 + (int64_t)row * per + c0 + col;
-            if (c0 + col < per && i < m) {
-                if (store) table[i] = tile[row * kScanPitch + col];
-                else tile[row * kScanPitch + col] = table[i];
+    // tile <-> the slices' elements [c0, c0 + kScanCols).  Thread j moves column j % kScanCols of the rows
+    // j / kScanCols + k * (kScanThreads / kScanCols): one column test per round, one add and one bound test per
+    // element (the index arithmetic of the obvious loop was half of this kernel's instructions)
+    constexpr int kRowsPerStep = kScanThreads / kScanCols;
+    const int col = j % kScanCols, row0 = j / kScanCols;
+    const int64_t g0 = 1 + (int64_t)row0 * per + col, gstep = (int64_t)kRowsPerStep * per;
+    double* const t0 = tile + row0 * kScanPitch + col;
+    auto stage = [&](int64_t c0, bool store) {
+        if (!(c0 + col < per)) return;
+        const int64_t i0 = g0 + c0;
+#pragma unroll
+        for (int k = 0; k < kScanCols; ++k) {
+            const int64_t i = i0 + k * gstep;
+            if (i < m) {
+                if (store) table[i] = t0[k * kRowsPerStep * kScanPitch];
+                else t0[k * kRowsPerStep * kScanPitch] = table[i];
             }
         }
     };
