@@ -342,6 +342,37 @@ def test_sharded_cdf_single_process_equals_batch(gpu):
 
 
 @pytest.mark.gpu
+def test_density_table_points_make_the_reference_decisions(gpu, O):
+    """The points of a gen_rts_from_cdf table (t = st = 0: one decision time each) go through the lean single-node
+    evaluator: densities at 1e-10 and, through the device-pointer entry point's counter, exactly the pdf_sv
+    evaluations the reference's recursion makes (first level, refinements, the points around zero)."""
+    import ctypes as C
+    import torch
+    from hddm_b200 import _lib
+    from tests.util import RTOL_TRIAL, assert_parity
+    L = _lib.lib()
+    _lib.check(L.hddm_b200_init(0))
+    dev = torch.device("cuda", 0)
+    x = np.arange(-4, 4, 1e-3)
+    xd = torch.from_numpy(x).to(dev)
+    rng = np.random.default_rng(31)
+    for k in range(6):
+        v, sv, a, z = rng.uniform(-4, 4), rng.uniform(0, 2.5), rng.uniform(0.5, 2.0), rng.uniform(0.4, 0.6)
+        sz = (0.0, 0.05, 0.2, 0.39, 0.3, 0.1)[k]
+        y = torch.empty_like(xd)
+        ev = torch.zeros(1, dtype=torch.int64, device=dev)
+        _lib.check(L.hddm_pdf_array_dev(C.c_void_p(xd.data_ptr()), x.size, v, sv, a, z, sz, 0.0, 0.0, 1e-4, 0, 2, 2, 1, 1e-3,
+                                        0.0, 0.0, C.c_void_p(y.data_ptr()), C.c_void_p(ev.data_ptr()),
+                                        C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
+        torch.cuda.synchronize(dev)
+        O.pdfsv_calls(reset=True)
+        want = O.pdf_array(x, v, sv, a, z, sz, 0.0, 0.0, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
+        calls = O.pdfsv_calls(reset=True)
+        assert_parity(y.cpu().numpy(), want, RTOL_TRIAL, what="table set %d" % k)
+        assert int(ev.item()) == calls, (k, int(ev.item()), calls)
+
+
+@pytest.mark.gpu
 def test_batch_edge_cases(gpu):
     """Empty and maximum sizes of the batched entry points (the reference's own edge behaviour: an empty
     trial vector gives 0.0, src/wfpt.pyx:62-75; empty batches give empty results)."""
