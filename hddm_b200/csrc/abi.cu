@@ -153,6 +153,15 @@ int like_impl(const double* h_x, const double* d_x, int64_t n, const int64_t* h_
     a.chunks = (int)chunks;
     a.mode = mode;
     a.nm = nm;
+    {   // simple-DDM sweeps (no sz, no st in any set) have a kernel of their own: the host can see it
+        bool simple = (mode == kModeWienerLike || mode == kModeContaminant) && spec[4].trial_stride == 0 && spec[6].trial_stride == 0;
+        for (int64_t p = 0; p < P && simple; ++p)
+            for (int k = 4; k <= 6; k += 2) {
+                const double val = static_cast<const double*>(uploads[spec[k].upload].host)[spec[k].offset + p * spec[k].set_stride];
+                simple = simple && (val < 1e-3);
+            }
+        a.all_simple = simple ? 1 : 0;
+    }
     a.partial = L.at<double>(off_partial);
     double* host_out = reinterpret_cast<double*>(g_rt.pinned + align_up(in_bytes));  // zero-copy result block
     a.logp = zero_copy ? host_out : L.at<double>(off_logp);

@@ -117,6 +117,7 @@ struct LikeArgs {
     double* partial2 = nullptr;          // [n_sets * chunks2]
     int chunks2 = 0;                     // ceil(chunks / kBlocksPerDeferredCta)
     const void* set_tables = nullptr;    // [n_sets] GridSet tables built once per set by k_build_tables (else per CTA)
+    int all_simple = 0;                  // the host saw every set's sz and st below the 1e-3 snap (src/pdf.pxi:122-125): k_like_simple
     int n_reg = 0;                       // regression terms (0: none); the outcomes' par[] entries are then ignored
     RegTerm reg[kMaxRegTerms] = {};
 };

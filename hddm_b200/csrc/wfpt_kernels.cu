@@ -403,6 +403,124 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
     }
 }
 
+// Sweeps whose sets ALL have neither sz nor st (the simple DDM of BASELINE config 1, with or without sv; the host
+// entry points see the parameters and say so in LikeArgs::all_simple): one pdf_sv per trial through lean_simple, one
+// pass, no bitmap and no second launch -- the few trials outside the comfortable range (or a set the lean constants do
+// not cover) take the complete evaluator in place.  Same grid, partial sums and reduction order as k_like_partial.
+template <int KMAX>
+__global__ void __launch_bounds__(kLikeThreads, 2) k_like_simple(const __grid_constant__ LikeArgs a)
+{
+    __shared__ GridSet<KMAX> gs;
+    __shared__ double ebig[kExpBig];
+    const int64_t p = blockIdx.x;
+    const int chunk = blockIdx.y;
+    const int64_t node = a.set_node ? a.set_node[p] : p;
+    const int64_t lo = a.seg ? a.seg[node] : 0;
+    const int64_t hi = a.seg ? a.seg[node + 1] : a.n;
+    const int64_t begin = lo + (int64_t)chunk * a.trials_per_block;
+    double* const slot = a.partial + p * a.chunks + chunk;
+    const bool single = a.chunks == 1;
+    const double p_out = load_par(a, 7, p, 0), w_out = load_par(a, 8, p, 0);
+    const bool range_ok = (p_out >= 0) & (p_out <= 1);  // src/wfpt.pyx:63-64
+    if (begin >= hi || !range_ok) {
+        if (threadIdx.x == 0) {
+            *slot = range_ok ? 0.0 : -INFINITY;
+            if (single) a.logp[p] = range_ok ? 0.0 : -INFINITY;
+        }
+        return;
+    }
+    const int64_t end = begin + a.trials_per_block < hi ? begin + a.trials_per_block : hi;
+    double par[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) par[k] = load_par(a, k, p, 0);
+    if (a.set_tables) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.set_tables) + p * (sizeof(GridSet<KMAX>) / sizeof(uint4));
+        uint4* dst = reinterpret_cast<uint4*>(&gs);
+        for (int k = threadIdx.x; k < (int)(sizeof(GridSet<KMAX>) / sizeof(uint4)); k += kLikeThreads) dst[k] = __ldg(src + k);
+    } else {
+        build_gridset<KMAX>(gs, par, a.tab, (a.mode != kModeContaminant) ? w_out * p_out : 0.0);
+        if (threadIdx.x == 0) build_leanset(gs, gs.lean, par[0], a.nm, true);
+    }
+    for (int k = threadIdx.x; k < kExpBig; k += kLikeThreads) ebig[k] = g_exp2_big[k];
+    __syncthreads();
+    const LeanSet& L = gs.lean;
+    const bool simple_ok = (L.ok1 & 4) != 0 && L.uniform != 0;
+    const double keep_mass = 1 - p_out, floor_mass = __dmul_rn(w_out, p_out);  // src/wfpt.pyx:70
+    double acc = 0.0, mant = 1.0;
+    int expo = 0;
+    bool hit_zero = false;
+    unsigned int made_fast = 0;          // pdf_sv evaluations settled in the loop (<= 32 per thread)
+    unsigned long long evals_slow = 0;   // ... and by the complete evaluator (its counter is passed by reference:
+                                         // kept apart so that nothing of the loop lives in local memory)
+    static_assert(kTrialsPerBigBlock / kLikeThreads <= 256, "mantissa product must stay finite");
+    auto add_log = [&](double d) {       // sum of logs = log of the mantissa product + ln2 * exponents
+        d = fma(d, keep_mass, floor_mass);
+        hit_zero |= (d == 0);            // src/wfpt.pyx:71-72, :377-379
+        const int hw = __double2hiint(d);
+        if ((unsigned)(hw - 0x00100000) < 0x7fe00000u) {
+            expo += (hw >> 20) - 1023;
+            mant *= __hiloint2double((hw & 0x000fffff) | 0x3ff00000, __double2loint(d));
+        } else {
+            acc += log(d);
+        }
+    };
+    // trials the lean evaluator does not take are queued per warp (ballot order) and scored after the loop
+    constexpr int kQueue = 256;
+    __shared__ unsigned short queue[kLikeThreads / 32][kQueue];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int queued = 0;  // warp-uniform
+    auto drain = [&]() {
+        __syncwarp();
+        for (int k = lane; k < queued; k += 32) {
+            const int64_t i = begin + queue[warp][k];
+            add_log(full_pdf_grid<KMAX, 0>(__ldg(a.x + i), par[0], gs, a.nm, &a.tab, evals_slow));
+        }
+        __syncwarp();
+        queued = 0;
+    };
+    const int rounds = (int)((end - begin + kLikeThreads - 1) / kLikeThreads);
+#pragma unroll 1
+    for (int r = 0; r < rounds; ++r) {
+        const int off = r * kLikeThreads + threadIdx.x;
+        const int64_t i = begin + off;
+        const bool valid = i < end && !(a.cont && a.cont[i] != 0);
+        const double x = valid ? __ldg(a.x + i) : 1.0;
+        bool need = valid;
+        int made = 0;
+        double d = 0.0;
+        if (simple_ok) d = lean_simple<KMAX>(gs, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
+        if (valid & !need) {
+            made_fast += made;
+            add_log(d);
+        }
+        const unsigned int votes = __ballot_sync(0xffffffffu, need);
+        if (votes) {  // warp-uniform, rare
+            if (need) queue[warp][queued + __popc(votes & ((1u << lane) - 1u))] = (unsigned short)off;
+            queued += __popc(votes);
+            if (queued > kQueue - 32) drain();
+        }
+    }
+    drain();
+    unsigned long long evals = evals_slow + made_fast;
+    acc += fma((double)expo, 0.693147180559945309417, log(mant));
+    __shared__ double warp_part[kLikeThreads / 32];
+    acc = warp_sum(acc);
+    if (lane == 0) warp_part[warp] = acc;
+    const int any_zero = __syncthreads_or(hit_zero ? 1 : 0);
+    if (a.evals) {
+        evals = warp_sum_u64(evals);
+        if (lane == 0) atomicAdd(a.evals, evals);
+    }
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kLikeThreads / 32; ++w) s += warp_part[w];
+        if (any_zero) s = -INFINITY;
+        *slot = s;
+        if (single) a.logp[p] = s;
+    }
+}
+
 // The per-set tables of the grid evaluator, once per set (split sweeps: every CTA of the set, in both
 // launches, copies them instead of rebuilding them).
 template <int KMAX>
@@ -522,6 +640,7 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
     auto mixed = [&](double d) { return fma(d, keep, floor_wp); };
     const bool lean_ok = KMAX == 4 && L.ok != 0 && L.uniform != 0;
     const bool tree_ok = lean_ok && a.nm.n_st == 2;
+    const bool simple_ok = KMAX == 4 && (L.ok1 & 4) != 0 && L.uniform != 0;  // neither sz nor st: lean_simple
     unsigned long long evals = 0;
     int queued = 0;  // warp-uniform
     DBG(10, lane == 0 && (!cta_per_set || warp == 0));
@@ -538,9 +657,10 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
         bool need = false;
         if (PHASE == 2) {
             need = in_range && dens[i] == kDeferred;
-        } else if (lean_ok) {
+        } else if (lean_ok || simple_ok) {
             int made = 0;
-            const double d = lean_first_level<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
+            const double d = simple_ok ? lean_simple<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made)
+                                       : lean_first_level<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
             evals += made;
             if (in_range & !need) dens[i] = valid ? mixed(d) : 1.0;  // (a skipped trial adds log 1)
         } else {
@@ -722,6 +842,30 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
     // two passes when threads own several trials each (segments longer than two rounds of the CTA)
     const int64_t longest = a.max_seg_len > 0 ? a.max_seg_len : a.n;
     const bool two_pass = gridk && g_kernel_choice != 3 && longest > 2 * kLikeThreads;
+    // Every set is a simple DDM (no sz, no st): the one-pass kernel of its own.
+    if (gridk && a.all_simple && !varies[0] && g_kernel_choice == 0 && b.tab.max_large_k <= 4 && a.n_reg == 0 &&
+        (a.mode == kModeWienerLike || a.mode == kModeContaminant) && longest > kWarpMaxTrials) {
+        // (shorter segments: the warp-per-set kernels below, which take such sets through lean_simple too)
+        void* tables = nullptr;
+        if (b.chunks >= 2 && (int64_t)b.n_sets * b.chunks >= 148 * 2 * 2) {  // tables once per set, not per CTA
+            keep_pool_memory();
+            if (cudaMallocAsync(&tables, (size_t)b.n_sets * sizeof(GridSet<4>), stream) == cudaSuccess) {
+                k_build_tables<4><<<(unsigned)b.n_sets, kLikeThreads, 0, stream>>>(b, tables);
+                b.set_tables = tables;
+            } else {
+                (void)cudaGetLastError();
+                tables = nullptr;
+            }
+        }
+        k_like_simple<4><<<grid, kLikeThreads, 0, stream>>>(b);
+        if (b.chunks > 1) {
+            const int sets_per_block = 128 / 32;
+            k_like_final<<<(unsigned)((a.n_sets + sets_per_block - 1) / sets_per_block), 128, 0, stream>>>(b);
+        }
+        const cudaError_t e = cudaGetLastError();
+        if (tables) cudaFreeAsync(tables, stream);
+        return e;
+    }
     // Big sweeps run the two passes as two launches: the first-pass code and the complete evaluator
     // together overflow the instruction cache when warps of one SM are in different passes (onset-mixed
     // data spent half of its cycles waiting for instructions).  One bit per trial travels between them.
@@ -1004,6 +1148,21 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? 2 : 1)
                 for (int u = 0; u < NP; ++u)
                     if (ib + u < a.n) ys[ib + u] = y[u];
             }
+        }
+    } else if (LEAN1 && (gs.lean.ok1 & 4)) {  // neither sz nor st: one pdf_sv per point
+        const LeanSet& L = gs.lean;
+        for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x; i0 < a.n; i0 += stride) {
+            const int64_t i = i0 + threadIdx.x;
+            const bool valid = i < a.n;
+            const double x = valid ? __ldg(xs + i) : 1.0;
+            bool need = false;
+            int made = 0;
+            double d = lean_simple<KT>(gs, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
+            if (!valid) continue;
+            if (need) d = full_pdf_grid<KT>(x, par[0], gs, a.nm, &a.tab, evals);
+            else evals += made;
+            d = d * (1 - par[7]) + (par[8] * par[7]);
+            ys[i] = a.logp == 1 ? log(d) : d;
         }
     } else
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {

@@ -145,6 +145,11 @@ __device__ __noinline__ void build_leanset(GS& G, LeanSet& L, double v, const Nu
     L.ok = inner_ok && G.st != 0 && nm.n_st > 0 ? 1 : 0;
     L.ok_small = L.ok && small_ok && isfinite(L.k1s) ? 1 : 0;
     L.ok1 = inner_ok && G.st == 0 && drift_uniform ? (small_ok && isfinite(L.k1s) ? 3 : 1) : 0;
+    // neither sz nor st (after the snaps of src/pdf.pxi:122-125): full_pdf is pdf_sv at the one start point and the one
+    // decision time (src/pdf.pxi:127-128) -- lean_simple; bits 2 (applies) and 3 (to small-time decision times too)
+    const bool point_ok = G.ok && G.support && mono && G.sz == 0 && G.st == 0 && asw * asw <= 50.0 && xhi > 0.0 &&
+                          drift_uniform && isfinite(v) && isfinite(L.k1) && L.k1 > 0.0;
+    if (point_ok) L.ok1 |= small_ok && isfinite(L.k1s) ? 12 : 4;
     L.tn17[0] = G.tn[0];
     L.tn17[16] = G.tn[4];
     for (int step = 8; step >= 1; step >>= 1)  // (lb + ub) / 2. recursively: tn17[4 j] == tn[j] bit for bit
@@ -556,6 +561,73 @@ __device__ __forceinline__ double lean_single(const GridSet<KMAX>& G, const Lean
     *need = bad | (neg < 0);
     *n_evals = (valid & !*need & !before) ? 5 : 0;
     return 12.0 * v;
+}
+
+// sz == 0 and st == 0 (the simple DDM, with or without sv): full_pdf = pdf_sv(|rt| - t, v, sv, a, z) (src/pdf.pxi:127-128,
+// :87-102; sv == 0: pdf, :74-85 -- the same expression with r = 1) -- one series value, one exponential for the drift
+// / sv marginal, one more for q (large time) or two for the images (small time).  The node constants are those of the
+// lean level (k1 = pi / (144 a^2) carries two Simpson levels that do not exist here: times 144).  All 32 lanes
+// call it (L.ok1 & 4 is set); a lane outside the comfortable range or with a negative series value sets *need.
+// *n_evals: 1 (0 before the onset).
+template <int KMAX>
+__device__ __forceinline__ double lean_simple(const GridSet<KMAX>& G, const LeanSet& L, const double* __restrict__ T,
+                                              const LeanTrial& c, double x, bool valid, bool* need, int* n_evals)
+{
+    const int b = c.b;
+    const double ax = fabs(x);
+    const double xt = ax - G.t;
+    const long long bits = __double_as_longlong(xt);
+    const bool before = valid & ((ax - G.t_onset) < 0);      // src/pdf.pxi:111-113
+    const bool at_onset = valid & !before & (xt <= 0.0);     // pdf_sv(0, ...) = 0 (src/pdf.pxi:92-93)
+    const bool live = valid & (xt > 0.0);
+    const bool in_range = live & (bits >= L.x_lo_small[b]) & (xt <= L.xhi);
+    const bool sm = in_range & (bits < (long long)L.x_edge) & ((L.ok1 & 8) != 0);
+    const bool lg = in_range & !(bits < (long long)L.x_edge);
+    bool bad = valid & !(before | at_onset | sm | lg);
+    int neg = 0;
+    double v = 0.0;
+    if (__any_sync(0xffffffffu, lg)) {
+        const double xs = lg ? xt : L.xhi;
+        const int K = 1 + (int)below_pos(xs, L.x_k[0]) + (int)below_pos(xs, L.x_k[1]) + (int)below_pos(xs, L.x_k[2]);
+        const int wK = __reduce_max_sync(0xffffffffu, lg ? K : 1);
+        const double q = exp_lean(G.qk * xs, T);
+        const double q2 = q * q, q3 = q2 * q;
+        // series / q at the set's start point: ascending k (src/pdf.pxi:60-62)
+        double p = fma(below_pos(xs, L.x_k[0]) ? q3 : 0.0, L.ks[b][1][0], L.ks[b][0][0]);
+        if (wK >= 3) {
+            const double q4 = q2 * q2, q8 = q4 * q4;
+            p = fma(below_pos(xs, L.x_k[1]) ? q8 : 0.0, L.ks[b][2][0], p);
+            if (wK >= 4) p = fma(below_pos(xs, L.x_k[2]) ? (q8 * q4) * q3 : 0.0, L.ks[b][3][0], p);
+        }
+        const double r = rsqrt_fast(fma(G.sv_sq, xs, 1.0));
+        const double e = exp_lean(fma(-c.v2h, xs, c.c0h) * (r * r), T);
+        if (lg) {
+            v = (p * e) * ((r * q) * (144.0 * L.k1));
+            neg |= __double2hiint(p);
+        }
+    }
+    if (__any_sync(0xffffffffu, sm)) {
+        const double xs = sm ? xt : __longlong_as_double(L.x_lo_small[b]);
+        const bool any_four = __any_sync(0xffffffffu, sm & !below(xs, L.x_s4));
+        const double rc = rcp_fast(xs);
+        const double r = rsqrt_fast(fma(G.sv_sq, xs, 1.0));
+        const double u = G.a_sq * rc;
+        const double scale = (((u * u) * rsqrt_fast(u)) * r) * (144.0 * L.k1s);
+        double C2 = 0.0;
+        if (any_four) {  // warp-uniform
+            const double C = exp_lean<true>(-L.g4_one * rc, T);
+            C2 = below(xs, L.x_s4) ? 0.0 : C * C;
+        }
+        int n2 = 0;
+        const double vs = lean_point_small<KMAX>(G, L, c, T, xs, G.w5[b][0], rc, r * r, scale, C2, n2);
+        if (sm) {
+            v = vs;
+            neg |= n2;
+        }
+    }
+    *need = bad | (neg < 0);
+    *n_evals = (valid & !*need & !before) ? 1 : 0;
+    return v;
 }
 
 // The lean first level for one warp round (all 32 lanes call it; `valid` masks lanes without a trial).  Lean or

@@ -424,6 +424,41 @@ def test_split_sweep_equals_one_launch(W, O, evaluator, onset):
         assert_parity(got["auto"][0][p], want, RTOL_SUM, what="split sweep, set %d" % p)
 
 
+@pytest.mark.parametrize("shape", [(3000, 48), (600, 64), (400, 1500), (16500, 800)])
+def test_simple_ddm_sets_vs_oracle(W, O, shape):
+    """Sets with neither sz nor st -- the simple DDM of BASELINE config 1, with and without sv -- take one pdf_sv per
+    trial (lean_simple) in every likelihood kernel: two passes in one launch, the warp-per-set kernels in one and
+    in two launches, the split sweep.  Summed parity, the reference's pdf_sv count, exact -inf classes, and the
+    scalar entry point bit for bit on the shapes where it runs the same kernel."""
+    T, P = shape
+    rng = np.random.default_rng(9700 + T)
+    par = draw_params(rng, P, sv_on=True, sz_on=False, st_on=False)
+    par[1, ::3] = 0.0                      # sv == 0: src/pdf.pxi:74-85
+    par[4, 1::5] = 5e-4                    # below the 1e-3 snap of src/pdf.pxi:124-125: still the simple case
+    x = draw_rts(rng, T, 0.30)             # onset-mixed: trials before t, small- and large-time decision times
+    params = np.concatenate([par, np.full((1, P), 0.05), np.full((1, P), 0.1)])
+    params[7, ::4] = 0.0                   # no outlier mass: -inf when a trial lies before the onset
+    got, evals = W.wiener_like_batch(x, params, return_evals=True, **HDDM)
+    pick = np.arange(P) if T * P <= 200000 else np.unique(np.concatenate([np.arange(0, P, max(1, P // 24)), [P - 1]]))
+    want, calls = [], []
+    for p in pick:
+        O.pdfsv_calls(reset=True)
+        want.append(O.wiener_like(x, *params[:7, p], p_outlier=params[7, p], w_outlier=params[8, p], **HDDM))
+        calls.append(O.pdfsv_calls(reset=True))
+    want, calls = np.array(want), np.array(calls)
+    assert np.isneginf(want).any() and np.isfinite(want).any()
+    assert_parity(got[pick], want, RTOL_SUM, what="simple DDM %d x %d" % shape)
+    # decisions: the reference stops a set at its first zero density (src/wfpt.pyx:71-72), so counts are compared on
+    # the sets that come out finite
+    fin = pick[np.isfinite(want)]
+    _, evals_fin = W.wiener_like_batch(x, np.ascontiguousarray(params[:, fin]), return_evals=True, **HDDM)
+    assert evals_fin == int(calls[np.isfinite(want)].sum()), (evals_fin, int(calls[np.isfinite(want)].sum()))
+    assert evals >= evals_fin
+    if T > 1024 and P <= 64:               # (short segments: the scalar call and the batch share the warp kernels too)
+        for p in (0, 1, P - 1):
+            assert W.wiener_like(x, *params[:7, p], p_outlier=params[7, p], w_outlier=params[8, p], **HDDM) == got[p]
+
+
 @pytest.mark.parametrize("outcomes", [("v",), ("a",), ("t",), ("v", "a"), ("z", "v"), ("sv", "st"), ("sz",)])
 def test_regression_on_any_outcome(W, O, outcomes):
     """HDDMRegressor regresses any of v, sv, a, z, sz, t, st (hddm/models/hddm_regression.py:26-36; its own slow
