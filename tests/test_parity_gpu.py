@@ -459,6 +459,22 @@ def test_simple_ddm_sets_vs_oracle(W, O, shape):
             assert W.wiener_like(x, *params[:7, p], p_outlier=params[7, p], w_outlier=params[8, p], **HDDM) == got[p]
 
 
+@pytest.mark.parametrize("n", [700, 3000, 20000])
+def test_simple_ddm_contaminant_vs_oracle(W, O, n):
+    """wiener_like_contaminant (src/wfpt.pyx:357-386) on simple-DDM parameters: the contaminant flags skip trials in
+    the warp-per-set kernels (n <= 1024) and in the simple-DDM kernel (longer vectors) as in the reference."""
+    rng = np.random.default_rng(9800 + n)
+    x = draw_rts(rng, n, 0.55)
+    cont = (rng.random(n) < 0.07).astype(np.int32)
+    for sv in (0.0, 0.9):
+        args = (1.1, sv, 1.4, 0.52, 0.0, 0.31, 0.0, 0.1, 5.0, 1e-4)
+        kw = dict(n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3)
+        got = W.wiener_like_contaminant(x, cont, *args, **kw)
+        want = O.wiener_like_contaminant(x, cont, *args, **kw)
+        assert np.isfinite(want)
+        assert_parity(got, want, RTOL_SUM, what="contaminant, simple DDM, n=%d sv=%g" % (n, sv))
+
+
 @pytest.mark.parametrize("outcomes", [("v",), ("a",), ("t",), ("v", "a"), ("z", "v"), ("sv", "st"), ("sz",)])
 def test_regression_on_any_outcome(W, O, outcomes):
     """HDDMRegressor regresses any of v, sv, a, z, sz, t, st (hddm/models/hddm_regression.py:26-36; its own slow

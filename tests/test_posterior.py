@@ -342,6 +342,29 @@ def test_sharded_cdf_single_process_equals_batch(gpu):
 
 
 @pytest.mark.gpu
+def test_batch_with_simple_and_single_time_draws(gpu, O):
+    """Posterior draws without sz (at or below the 1e-3 snap) take the one-pdf_sv path, draws with sz the single-node
+    path: the batch still equals one scalar call per draw bit for bit, and the reference's lookup on >= 99.5 %."""
+    from hddm_b200 import posterior, wfpt
+    rng = np.random.default_rng(43)
+    D, S = 12, 400
+    params = _draws(rng, D)
+    params[4, 0::3] = 0.0
+    params[4, 1::3] = 5e-4
+    params[1, 0::4] = 0.0          # sv == 0 as well
+    f, u = rng.random((D, S)), rng.random((D, S))
+    rts = posterior.gen_rts_from_cdf_batch(params, S, -5.0, 5.0, 1e-3, f=f, u_delay=u)
+    exact = 0
+    for d in range(D):
+        one = wfpt.gen_rts_from_cdf(*params[:, d], S, -5.0, 5.0, 1e-3, f=f[d], u_delay=u[d])
+        assert np.array_equal(one, rts[d]), d
+        want = O.gen_rts_from_cdf(*params[:, d], S, -5.0, 5.0, 1e-3, f=f[d], u_delay=u[d])
+        exact += (np.abs(rts[d] - want) <= 1e-12).sum()
+        assert np.max(np.abs(rts[d] - want)) <= 1e-3 + 1e-12
+    assert exact >= 0.995 * D * S
+
+
+@pytest.mark.gpu
 def test_density_table_points_make_the_reference_decisions(gpu, O):
     """The points of a gen_rts_from_cdf table (t = st = 0: one decision time each) go through the lean single-node
     evaluator: densities at 1e-10 and, through the device-pointer entry point's counter, exactly the pdf_sv
