@@ -595,7 +595,10 @@ __global__ void __launch_bounds__(32 * kWarpSets) k_build_tables_warp(const __gr
 // needs more, reduces the sets it completed and flags the others in `pending`; PHASE 2 looks only at flagged sets,
 // rebuilds each warp's queue from the marks (same trials, same order as PHASE 0) and finishes them.
 constexpr double kDeferred = -1.0;  // never a mixed density (those are >= 0 or NaN)
-template <int KMAX, int PHASE>
+// SIMPLE: the host saw that every set is a simple DDM (LikeArgs::all_simple): the lean level of this instantiation is
+// lean_simple and nothing else; the other instantiation does not carry it (its sets without sz and st go to the
+// complete evaluator, as every set the lean constants do not cover).
+template <int KMAX, int PHASE, bool SIMPLE>
 __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_constant__ LikeArgs a, int cta_per_set,
                                                                double* __restrict__ dens_all, int64_t dens_stride,
                                                                int* __restrict__ pending)
@@ -638,9 +641,9 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
     // addition must not depend on the instantiation (the one- and two-launch flavours give a set the same bits)
     const double keep = 1 - p_out, floor_wp = __dmul_rn(w_out, p_out);
     auto mixed = [&](double d) { return fma(d, keep, floor_wp); };
-    const bool lean_ok = KMAX == 4 && L.ok != 0 && L.uniform != 0;
+    const bool lean_ok = !SIMPLE && KMAX == 4 && L.ok != 0 && L.uniform != 0;
     const bool tree_ok = lean_ok && a.nm.n_st == 2;
-    const bool simple_ok = KMAX == 4 && (L.ok1 & 4) != 0 && L.uniform != 0;  // neither sz nor st: lean_simple
+    const bool simple_ok = SIMPLE && KMAX == 4 && (L.ok1 & 4) != 0 && L.uniform != 0;  // neither sz nor st: lean_simple
     unsigned long long evals = 0;
     int queued = 0;  // warp-uniform
     DBG(10, lane == 0 && (!cta_per_set || warp == 0));
@@ -659,8 +662,9 @@ __global__ void __launch_bounds__(32 * kWarpSets, 4) k_like_warp(const __grid_co
             need = in_range && dens[i] == kDeferred;
         } else if (lean_ok || simple_ok) {
             int made = 0;
-            const double d = simple_ok ? lean_simple<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made)
-                                       : lean_first_level<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
+            double d;
+            if (SIMPLE) d = lean_simple<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
+            else d = lean_first_level<KMAX>(G, L, ebig, lean_begin(L, x > 0 ? 1 : 0), x, valid, &need, &made);
             evals += made;
             if (in_range & !need) dens[i] = valid ? mixed(d) : 1.0;  // (a skipped trial adds log 1)
         } else {
@@ -925,10 +929,14 @@ cudaError_t launch_like(const LikeArgs& a, cudaStream_t stream)
             double* dens = reinterpret_cast<double*>(reinterpret_cast<char*>(tables) + table_bytes);
             int* pending = reinterpret_cast<int*>(reinterpret_cast<char*>(tables) + table_bytes + dens_bytes);
             if (b.n_sets <= kWarpOneLaunchSets) {  // (the same sums, bit for bit, either way)
-                k_like_warp<4, 0><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+                if (a.all_simple) k_like_warp<4, 0, true><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+                else k_like_warp<4, 0, false><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+            } else if (a.all_simple) {
+                k_like_warp<4, 1, true><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+                k_like_warp<4, 2, true><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
             } else {
-                k_like_warp<4, 1><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
-                k_like_warp<4, 2><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+                k_like_warp<4, 1, false><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
+                k_like_warp<4, 2, false><<<grid_w, 32 * kWarpSets, 0, stream>>>(b, cta_per_set, dens, dens_stride, pending);
             }
             const cudaError_t e = cudaGetLastError();
             cudaFreeAsync(tables, stream);
