@@ -181,40 +181,6 @@ def gen_rts_from_simulated_drift(params, samples=1000, dt=1e-4, intra_sv=1., see
     return simulate_drift_batch(col, 1 if samples is None else samples, dt, intra_sv, seed, switch=switch)[0]
 
 
-_PINNED = {}
-
-
-def _pinned(shape, tag):
-    """Page-locked staging tensors, kept per shape (allocating one costs more than the copies it speeds up)."""
-    import torch
-    key = (tag,) + tuple(shape)
-    if key not in _PINNED:
-        if len(_PINNED) > 16:
-            _PINNED.clear()
-        _PINNED[key] = torch.empty(shape, dtype=torch.float64).pin_memory()
-    return _PINNED[key]
-
-
-def _gather_to_host(local, n_rows, group):
-    """All-gather the ranks' row blocks (numpy [rows, cols]) into the full [n_rows, cols] table on the host.  Over NCCL
-    the block goes up and the table comes down through page-locked staging (one asynchronous copy each way)."""
-    import torch
-    import torch.distributed as dist
-    from .batch import gather_rows
-    t = torch.from_numpy(local)
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
-        return gather_rows(t, n_rows, group).numpy()
-    if dist.get_backend(group) != "nccl":
-        return gather_rows(t, n_rows, group).cpu().numpy()
-    up = _pinned(tuple(t.shape), "up")
-    up.copy_(t)
-    table = gather_rows(up.cuda(non_blocking=True), n_rows, group)
-    down = _pinned(tuple(table.shape), "down")
-    down.copy_(table, non_blocking=True)
-    torch.cuda.current_stream().synchronize()
-    return down.numpy().copy()
-
-
 def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=0, evaluate=None, group=None,
                             timings=None):
     """Posterior predictive statistics for D draws with the draws sharded over the ranks of `group` (one
@@ -245,7 +211,10 @@ def post_pred_stats_sharded(params, samples, cdf_lb=-6, cdf_ub=6, dt=1e-4, seed=
     t0 = time.perf_counter()
     local = evaluate(block, lo) if hi > lo else np.empty((0, len(STAT_NAMES)))
     t1 = time.perf_counter()
-    table = _gather_to_host(np.ascontiguousarray(local, dtype=np.float64), D, group)
+    local = torch.from_numpy(np.ascontiguousarray(local, dtype=np.float64))
+    if world > 1 and dist.get_backend(group) == "nccl":
+        local = local.cuda()
+    table = gather_rows(local, D, group).cpu().numpy()
     if timings is not None:
         timings["evaluate"] = t1 - t0
         timings["gather"] = time.perf_counter() - t1
@@ -274,4 +243,7 @@ def dmat_cdf_sharded(x, params, evaluate=None, group=None):
     if evaluate is None:
         evaluate = dmat_cdf_batch
     local = evaluate(x[lo:hi], np.ascontiguousarray(params[:, lo:hi])) if hi > lo else np.empty((0, n))
-    return _gather_to_host(np.ascontiguousarray(local, dtype=np.float64).reshape(hi - lo, n), D, group)
+    local = torch.from_numpy(np.ascontiguousarray(local, dtype=np.float64).reshape(hi - lo, n))
+    if world > 1 and dist.get_backend(group) == "nccl":
+        local = local.cuda()
+    return gather_rows(local, D, group).cpu().numpy()
