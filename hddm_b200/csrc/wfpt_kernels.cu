@@ -132,6 +132,11 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
     // regression terms: this set's coefficients, once per CTA
     __shared__ double s_coef[kMaxRegTerms][kMaxRegK];
     const bool reg_v_only = a.n_reg == 1 && a.reg[0].outcome == 0 && !per_trial;  // the lean evaluators take it
+    // ... and a drift COLUMN (one value per trial: the Q-learning scan of the RL-DDM, wiener_like_multi with 'v')
+    bool col_v_only = a.n_reg == 0 && a.trial_stride[0] != 0;
+#pragma unroll
+    for (int k = 1; k < 7; ++k) col_v_only = col_v_only && a.trial_stride[k] == 0;
+    const bool v_per_trial = reg_v_only || col_v_only;
     if (a.n_reg > 0) {
         for (int k = threadIdx.x; k < a.n_reg * kMaxRegK; k += kLikeThreads) {
             const RegTerm& t = a.reg[k / kMaxRegK];
@@ -148,6 +153,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         else if (t.link == kLinkExp) acc = exp(acc);
         return acc;
     };
+    auto trial_drift = [&](int64_t i) { return reg_v_only ? reg_value(0, i) : load_par(a, 0, p, i); };
 
     if (GRID && a.set_tables) {  // split sweep: the set's tables were built once, by k_build_tables
         static_assert(sizeof(GridSet<KT>) % sizeof(uint4) == 0, "tables are copied 16 bytes at a time");
@@ -168,7 +174,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
     __shared__ double ebig[(LEAN || TREE) ? kExpBig : 1];
     // (uniform drift, or a drift regressed per trial; wiener_like / contaminant / wiener_like_multi semantics)
     const bool lean_ok = (LEAN || TREE) && gs.lean.ok != 0 && a.mode != kModeMultiRL &&
-                         (reg_v_only ? gs.lean.uniform == 0 : (!per_trial && gs.lean.uniform != 0));
+                         (v_per_trial ? gs.lean.uniform == 0 : (!per_trial && gs.lean.uniform != 0));
     const bool tree_ok = TREE && lean_ok && a.nm.n_st == 2;
     if (lean_ok) {
         for (int k = threadIdx.x; k < kExpBig; k += kLikeThreads) ebig[k] = g_exp2_big[k];
@@ -249,7 +255,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
         const double x = valid ? x_loaded : 1.0;
         const int b = x > 0 ? 1 : 0;
         bool v_fits = true;
-        const LeanTrial c = reg_v_only ? lean_begin_v<KT>(gs, L, b, reg_value(0, valid ? i : begin), fabs(x) - gs.tn[0], &v_fits)
+        const LeanTrial c = v_per_trial ? lean_begin_v<KT>(gs, L, b, trial_drift(valid ? i : begin), fabs(x) - gs.tn[0], &v_fits)
                                        : lean_begin(L, b);
         bool nd = false;
         int made = 0;
@@ -291,7 +297,7 @@ __global__ void __launch_bounds__(kLikeThreads, KMAX > 0 ? (PASSES == kSplitSeco
                     bool fail = false, v_fits = true;
                     int made = 0;
                     const int bb = x > 0 ? 1 : 0;
-                    const LeanTrial c = reg_v_only ? lean_begin_v<KT>(gs, gs.lean, bb, reg_value(0, begin + (on ? off : 0)),
+                    const LeanTrial c = v_per_trial ? lean_begin_v<KT>(gs, gs.lean, bb, trial_drift(begin + (on ? off : 0)),
                                                                       fabs(x) - gs.tn[0], &v_fits)
                                                    : lean_begin(gs.lean, bb);
                     double d = lean_tree<KT>(gs, gs.lean, ebig, x, c, on & v_fits, &fail, &made);
