@@ -99,11 +99,35 @@ int rlddm_impl(const double* x, const int64_t* response, const double* feedback,
     if (chunks > 65535) return fail(HDDM_ERR_ARG, "more than 65535*2048 trials per parameter set");
     if ((double)P * (double)n * 8.0 > 64e9) return fail(HDDM_ERR_ARG, "rlddm: P x n drift table above 64 GB");
     const int64_t n_runs = (int64_t)t.run_off.size() - 1;
+    // The scan walks the task in run order; the densities do not care about order, and their kernel wants the
+    // trials boundary-major and by |rt| (a warp then shares its series branch and evaluator class, sort_kernels.cu):
+    // the scan scatters each trial's drift to the trial's place in that layout.
+    std::vector<int32_t> pos((size_t)n), head_sorted((size_t)n);
+    std::vector<double> x_sorted((size_t)n);
+    {
+        std::vector<int32_t> by_rt((size_t)n);
+        std::iota(by_rt.begin(), by_rt.end(), 0);
+        auto key = [&](int32_t j) {
+            const double v = t.x[(size_t)j];
+            uint64_t bits;
+            const double mag = fabs(v);
+            memcpy(&bits, &mag, sizeof(bits));
+            return bits | (v > 0 ? (uint64_t)1 << 63 : (uint64_t)0);
+        };
+        std::stable_sort(by_rt.begin(), by_rt.end(), [&](int32_t l, int32_t r) { return key(l) < key(r); });
+        for (int64_t k = 0; k < n; ++k) {
+            const int32_t j = by_rt[(size_t)k];
+            pos[(size_t)j] = (int32_t)k;
+            x_sorted[(size_t)k] = t.x[(size_t)j];
+            head_sorted[(size_t)k] = t.head[(size_t)j];
+        }
+    }
 
     Stager S;
-    const int s_x = S.add(t.x.data(), (size_t)n * sizeof(double));
+    const int s_x = S.add(x_sorted.data(), (size_t)n * sizeof(double));
     const int s_resp = S.add(t.resp.data(), (size_t)n * sizeof(int32_t));
-    const int s_head = S.add(t.head.data(), (size_t)n * sizeof(int32_t));
+    const int s_head = S.add(head_sorted.data(), (size_t)n * sizeof(int32_t));
+    const int s_pos = S.add(pos.data(), (size_t)n * sizeof(int32_t));
     const int s_fb = S.add(t.fb.data(), (size_t)n * sizeof(double));
     const int s_run = S.add(t.run_off.data(), t.run_off.size() * sizeof(int64_t));
     const int s_par = S.add(params, (size_t)P * kRlRows * sizeof(double));
@@ -130,6 +154,7 @@ int rlddm_impl(const double* x, const int64_t* response, const double* feedback,
     sc.pos_alpha = d_par + 11 * P;
     sc.q_stride = sc.alpha_set_stride = sc.pos_stride = sc.v_set_stride = 1;
     sc.drift = S.dev<double>(s_drift);
+    sc.pos = n > 0 ? S.dev<int32_t>(s_pos) : nullptr;
     CUDA_TRY(launch_rl_scan(sc, s));
 
     LikeArgs a;

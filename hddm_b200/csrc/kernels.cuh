@@ -202,6 +202,7 @@ struct RlScanArgs {
     const double* v;           // drift scale: per set or per trial
     int64_t q_stride, alpha_set_stride, alpha_trial_stride, pos_stride, v_set_stride, v_trial_stride;
     double* drift;             // out [n_sets][n]: v * (Q_upper - Q_lower) BEFORE the trial's update
+    const int32_t* pos = nullptr;  // optional [n]: trial i's drift goes to column pos[i] (the likelihood's |rt| layout)
 };
 cudaError_t launch_rl_scan(const RlScanArgs& a, cudaStream_t stream);
 

@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(128) k_rl_scan(const RlScanArgs a)
     double* out = a.drift + p * a.n;
     for (int64_t i = lo; i < hi; ++i) {
         const double v = a.v[p * a.v_set_stride + i * a.v_trial_stride];
-        out[i] = __dmul_rn(__dadd_rn(s.q1, -s.q0), v);  // (qs[1] - qs[0]) * v, src/wfpt.pyx:135
+        out[a.pos ? a.pos[i] : i] = __dmul_rn(__dadd_rn(s.q1, -s.q0), v);  // (qs[1] - qs[0]) * v, src/wfpt.pyx:135
         if (alpha_per_trial) rate_neg = rl_rate(a.alpha[p * a.alpha_set_stride + i * a.alpha_trial_stride]);
         rl_update(s, a.response[i], a.feedback[i], rate_neg);
     }
