@@ -477,6 +477,14 @@ def run_ours(args):
 
     evals_per_step = float(T) * P * world
     value = evals_per_step * args.steps / (total_ms * 1e-3)
+    # every rank's own kernel time per step (weak scaling: each rank has its own 1e4 sets; the step ends with the
+    # slowest rank's all-gather contribution)
+    k_rank = torch.tensor([float(np.mean(kern_ms))], dtype=torch.float64, device=dev)
+    if world > 1:
+        k_ranks = [torch.zeros_like(k_rank) for _ in range(world)]
+        dist.all_gather(k_ranks, k_rank)
+        k_rank = torch.cat(k_ranks)
+    kernel_ms_per_rank = [round(float(v), 4) for v in k_rank.cpu().tolist()]
 
     # ---- e2e: public host-buffer API, pinned host inputs, H2D + D2H inside the timed region
     xh = torch.from_numpy(x).pin_memory().numpy()
@@ -629,7 +637,8 @@ def run_ours(args):
         launches = (4 if split_sweep(T, P) else 2) * args.steps
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "warmup": warm, "ms_per_step": total_ms / args.steps, "kernel_ms_per_rank": kernel_ms_per_rank,
+            "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(x.nbytes + params.nbytes),
